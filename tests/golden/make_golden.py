@@ -1,0 +1,123 @@
+"""Generate the golden fixtures by running the UNMODIFIED reference in the build container.
+
+    python tests/golden/make_golden.py        (needs /root/reference and cv2; CPU only)
+
+* matcher_*.npz  : outputs of the reference ``GATsSuperGlue.forward``
+  (/root/reference/src/models/GATsSPG_architectures/GATs_SuperGlue.py:203-278) on the seeded inputs
+  of ``onepose_b200.synth`` with weights ``synth.make_weights(seed, damped)`` loaded through
+  ``load_state_dict(strict=True)``.  Only seeds + outputs are stored.
+* layer_*.npz    : outputs of the reference sub-modules ``GraphAttentionLayer`` (GATs.py:62-104)
+  and ``AttentionPropagation`` (GATs_SuperGlue.py:123-132) on seeded inputs.
+* pnp_*.npz      : outputs of the reference ``ransac_PnP`` (src/utils/eval_utils.py:18-42, i.e.
+  cv2.solvePnPRansac of this image, cv2 4.13.0) on ``synth.make_pnp_problem`` inputs, plus
+  per-sample ``cv2.solvePnP(EPNP)`` poses on all-inlier 5-point samples.
+The reference has no tests or golden vectors of its own; these fixtures, made from
+the live reference, are what pins the oracle.
+"""
+import io
+import contextlib
+import os
+import sys
+
+sys.dont_write_bytecode = True
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, "/root/reference")
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+import numpy as np
+import torch
+
+from onepose_b200 import synth
+
+MATCHER_CASES = {
+    # name: (weights seed, damped, object id, n2, n3, leaves, frames, hparam overrides)
+    "matcher_random": (0, False, 0, 96, 160, 8, 2, {}),
+    "matcher_damped": (1, True, 1, 128, 192, 8, 2, {}),
+    "matcher_ragged": (2, True, 2, 33, 47, 3, 1, {}),
+    "matcher_lowthr": (0, False, 3, 64, 96, 4, 1, {"match_threshold": 0.0}),
+    "matcher_flags_lt": (3, True, 4, 40, 56, 4, 1, {"with_linear_transform": True}),
+    "matcher_flags_noself": (4, True, 5, 40, 56, 4, 1, {"include_self": False}),
+    "matcher_flags_add": (5, True, 6, 40, 56, 4, 1, {"additional": True, "with_linear_transform": True}),
+}
+
+PNP_CASES = {
+    # name: (seed, ncorr, inlier_ratio, scale)
+    "pnp_300": (0, 300, 0.8, 1000.0),
+    "pnp_1000": (1, 1000, 0.5, 1000.0),
+    "pnp_2000": (2, 2000, 0.3, 1.0),
+    "pnp_60": (3, 60, 0.9, 1000.0),
+}
+
+
+def matcher_inputs(case):
+    wseed, damped, oid, n2, n3, leaves, frames, over = MATCHER_CASES[case]
+    hp = dict(synth.DEFAULT_HPARAMS); hp.update(over)
+    w = synth.make_weights(wseed, damped=damped)
+    obj = synth.make_object(oid, n3, leaves)
+    fr = [synth.make_frame(obj, f, n2) for f in range(frames)]
+    return hp, w, obj, fr, synth.pack_batch(obj, fr)
+
+
+def main():
+    from src.models.GATsSPG_architectures.GATs_SuperGlue import GATsSuperGlue, AttentionPropagation
+    from src.models.GATsSPG_architectures.GATs import GraphAttentionLayer
+    from src.utils.eval_utils import ransac_PnP
+    import cv2
+
+    torch.set_grad_enabled(False)
+    for case in MATCHER_CASES:
+        hp, w, obj, fr, data = matcher_inputs(case)
+        ref = GATsSuperGlue(hp).eval()
+        ref.load_state_dict(w, strict=True)
+        pred, conf = ref(data)
+        np.savez_compressed(
+            os.path.join(HERE, case + ".npz"), conf=conf.numpy(),
+            matches0=pred["matches0"].numpy(), matches1=pred["matches1"].numpy(),
+            matching_scores0=pred["matching_scores0"].numpy(), matching_scores1=pred["matching_scores1"].numpy())
+        print(case, "conf", tuple(conf.shape), "matches", int((pred["matches0"] > -1).sum()))
+
+    # sub-module fixtures: one GATs layer (shipped flags) and one AttentionPropagation
+    rng = np.random.default_rng(77)
+    w = synth.make_weights(6)
+    leaves = torch.from_numpy(rng.standard_normal((2, 24, 5, 256)).astype(np.float32))
+    h3 = torch.from_numpy(rng.standard_normal((2, 24, 256)).astype(np.float32))
+    gat = GraphAttentionLayer(256, 256, 0.6, 0.2, True, True, False, False)
+    gat.load_state_dict({"W": w["gnn.layers.0.W"], "a": w["gnn.layers.0.a"]})
+    out_gat = gat(leaves.reshape(2, 24 * 5, 256), h3)
+    x = torch.from_numpy(rng.standard_normal((2, 256, 40)).astype(np.float32))
+    src = torch.from_numpy(rng.standard_normal((2, 256, 72)).astype(np.float32))
+    ap = AttentionPropagation(256, 4)
+    ap.load_state_dict({k[len("gnn.layers.1."):]: v for k, v in w.items() if k.startswith("gnn.layers.1.")})
+    out_ap = ap(x, src)
+    np.savez_compressed(os.path.join(HERE, "layer_units.npz"), gats_out=out_gat.numpy(), attn_out=out_ap.numpy())
+
+    for case, (seed, n, ratio, scale) in PNP_CASES.items():
+        pr = synth.make_pnp_problem(seed, n, ratio)
+        pose, pose_h, inl = ransac_PnP(pr["K"], pr["pts2d"], pr["pts3d"], scale=scale)
+        # per-sample EPnP poses on all-inlier minimal samples (well-posed => library-independent)
+        X32 = (pr["pts3d"] * scale).astype(np.float32); uv32 = pr["pts2d"].astype(np.float32)
+        ids = np.nonzero(pr["is_inlier"])[0]
+        srng = np.random.default_rng(seed)
+        samples = np.stack([srng.choice(ids, 5, replace=False) for _ in range(16)]).astype(np.int32)
+        rts = []
+        for s in samples:
+            ok, rv, tv = cv2.solvePnP(X32[s], uv32[s], pr["K"], np.zeros((8, 1)), flags=cv2.SOLVEPNP_EPNP)
+            rts.append(np.concatenate([rv.ravel(), tv.ravel()]))
+        np.savez_compressed(os.path.join(HERE, case + ".npz"), pose=pose, inliers=np.asarray(inl).ravel(),
+                            samples=samples, sample_rt=np.stack(rts))
+        print(case, "inliers", len(inl))
+
+    # edge cases of the wrapper (SURVEY.md appendix B caveats): n = 0, 3, 4, 5, 6(all outliers)
+    edge = {}
+    rng = np.random.default_rng(5)
+    for n in (0, 3, 4, 5):
+        pr = synth.make_pnp_problem(10 + n, max(n, 1), 1.0)
+        with contextlib.redirect_stdout(io.StringIO()):
+            pose, _, inl = ransac_PnP(pr["K"], pr["pts2d"][:n], pr["pts3d"][:n], scale=1000)
+        edge[f"pose_{n}"] = pose; edge[f"inl_{n}"] = np.asarray(inl).ravel()
+        print("edge n=%d inliers=%d" % (n, len(inl)))
+    np.savez_compressed(os.path.join(HERE, "pnp_edge.npz"), **edge)
+
+
+if __name__ == "__main__":
+    main()
