@@ -1,0 +1,133 @@
+/*
+ * onepose_b200 -- C ABI of the B200 (sm_100a) GATsSPG matching + PnP hot path.
+ *
+ * The reference (huanghaoran111/OnePose) is pure Python and has no FFI of its own; the functions
+ * below are the operator boundary a maintainer binds (ctypes stub in INTEGRATION.md) to replace
+ *   - GATsSuperGlue.forward      src/models/GATsSPG_architectures/GATs_SuperGlue.py:203-278
+ *   - GraphAttentionLayer.forward src/models/GATsSPG_architectures/GATs.py:62-123
+ *   - ransac_PnP                 src/utils/eval_utils.py:18-42
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host; the caller owns all memory
+ *     (including workspaces); nothing here allocates, frees or synchronises the device;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*);
+ *   - return value 0 = success, negative = error; op_last_error() gives the message of the last
+ *     failure on the calling thread; nothing throws or exits across the ABI;
+ *   - activations are fp32 "point-major" [B, N, C] (row = one keypoint), indices int64 as in the
+ *     reference (-1 = unmatched), poses float64.
+ */
+#ifndef ONEPOSE_B200_H
+#define ONEPOSE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OPB_OK 0
+#define OPB_ERR_ARG (-1)
+#define OPB_ERR_CUDA (-2)
+#define OPB_ERR_WORKSPACE (-3)
+
+const char *op_last_error(void);
+int op_abi_version(void);
+
+/* ---- layout --------------------------------------------------------------------------------
+ * Public tensors are channel-major [B, C, N] (GATs_SuperGlue.py:209-218).  Convert to the internal
+ * point-major [B, N, C].  bstride_in (in elements) may be 0 for an expand()-ed static DB. */
+int op_channel_major_to_point_major(const float *in, float *out, int B, int C, int N,
+                                    long long bstride_in, void *stream);
+
+/* ---- (1) GATs leaf aggregation: GATs.py:62-123 ------------------------------------------------
+ * For every 3D point n (and frame b): logits over its (include_self ? 1 : 0) + L entries,
+ *   t = h3L[b,n].v2 ; s_0 = t (the self entry re-uses the a[256:] projection, GATs.py:115-120) ;
+ *   s_j = leaf[n,j].v1 ; e = LeakyReLU_alpha(t + s)
+ *   att = softmax(e) ; out = att_0*h3L[b,n] + sum_j att_j*leaf[n,j]      (include_self)
+ *                      out = sum_j att_j*leaf[n,j] / 2 + h3L[b,n]         (!include_self)
+ *   if (h3_add) out += h3_add[b,n] ; if (apply_elu) out = ELU(out)
+ * leaf: [Bl, N3, L, 256] with batch stride leaf_bstride elements (0 = one DB shared by all frames).
+ * h3L and out: [B, N3, 256]; out may alias h3L (each point reads only its own row).
+ * With the shipped flags v1 = W a[:256], v2 = W a[256:] (the 256x256 GEMM collapses, GATs.py:68-69,113-115). */
+int op_gats_leaf_aggregate(const float *leaf, long long leaf_bstride, const float *h3L, const float *h3_add,
+                           const float *v1, const float *v2, float *out, int B, int N3, int L,
+                           float alpha, int include_self, int apply_elu, void *stream);
+
+/* ---- (2) self/cross AttentionPropagation building blocks: GATs_SuperGlue.py:88-147 -----------
+ * Generic fused linear: C[b,n,:] = epi( [A1[b,n,:K1] | A2[b,n,:K2]] . W^T + bias ), W is [Cout, K1+K2]
+ * row-major.  Rows are addressed as b*rows_per_batch + n.  Flags select the fusions:
+ *   OPB_LIN_ELU1      : elu(x)+1 on output columns < elu_cols          (linear attention feature map, :90-91)
+ *   OPB_LIN_RESIDUAL  : C += result (residual add, :78,83)
+ *   OPB_LIN_STATS     : per (b, column) sum / sum of squares of the result in float64 partials
+ *                       stats_partial[b][row_tile][Cout][2] (InstanceNorm1d statistics, :144)
+ *   OPB_LIN_NORM_RELU : A1 is read as relu((a - mean[b,k]) * rstd[b,k])  (InstanceNorm + ReLU, :144-146)
+ */
+#define OPB_LIN_ELU1 1
+#define OPB_LIN_RESIDUAL 2
+#define OPB_LIN_STATS 4
+#define OPB_LIN_NORM_RELU 8
+int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
+              float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,
+              const float *mean, const float *rstd, double *stats_partial, void *stream);
+/* number of row tiles op_linear uses per batch element (sizes stats_partial) */
+int op_linear_row_tiles(int rows_per_batch);
+/* mean / rstd [B, C] from the float64 partials; biased variance, eps as InstanceNorm1d */
+int op_instnorm_finalize(const double *stats_partial, int B, int row_tiles, int C, int rows_per_batch,
+                         float eps, float *mean, float *rstd, void *stream);
+
+/* KV reduction of linear attention (:93-97).  kv: [B, M, 512] = [K' (elu+1 applied) | V], channels
+ * head-major (c = h*64 + d).  Outputs KV[b,h,d,q] = sum_m K'[m,h,d] * V[m,h,q] / M and
+ * Ksum[b,h,d] = sum_m K'[m,h,d].  workspace: op_kv_reduce_workspace_bytes(B, M). */
+size_t op_kv_reduce_workspace_bytes(int B, int M);
+int op_kv_reduce(const float *kv, float *KV, float *Ksum, int B, int M, void *workspace,
+                 size_t workspace_bytes, void *stream);
+/* out[b,n,h*64+q] = (sum_d Q'[b,n,h,d] KV[b,h,d,q]) * M / (sum_d Q'[b,n,h,d] Ksum[b,h,d] + 1e-6)  (:97-98) */
+int op_attn_apply(const float *Qp, const float *KV, const float *Ksum, float *out, int B, int N, int M,
+                  void *stream);
+
+/* row-wise L2 normalisation x / max(||x||, 1e-12)  (F.normalize, :245-246); in place allowed */
+int op_l2_normalize_rows(const float *x, float *out, long long rows, int C, void *stream);
+
+/* ---- (3) similarity + dual-softmax + mutual-NN: GATs_SuperGlue.py:251-274 -----------------------
+ * m2 [B,N2,256], m3 [B,N3,256] unit rows.  conf[b,n,m] = softmax_n(s)*softmax_m(s), s = m2.m3/scale.
+ * Pass 1 accumulates the row/column exp sums, pass 2 recomputes the tile and writes conf exactly
+ * once, tracking row/column maxima; the selection kernel applies the mutual / threshold logic.
+ * Outputs are batched: matches0 [B,N2] int64, matches1 [B,N3] int64, scores0 [B,N2], scores1 [B,N3]. */
+size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3);
+int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+                        float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                        float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
+                        void *stream);
+
+/* valid-match gather (inference.py:147-152): per frame, ascending query index.
+ * pts2d [B,N2,2] fp32, pts3d [Bk,N3,3] fp32 (kp3_bstride elements, 0 = shared), out2d [B,N2,2] / out3d [B,N2,3] float64
+ * (out3d scaled by `scale`), out_conf [B,N2], out_query_idx [B,N2] int32, count [B] int32. */
+int op_gather_matches(const int64_t *matches0, const float *scores0, const float *kpts2d, const float *kpts3d,
+                      long long kp3_bstride, int B, int N2, int N3, double scale, double *out2d, double *out3d,
+                      float *out_conf, int32_t *out_query_idx, int32_t *count, void *stream);
+
+/* ---- (4) batched PnP-RANSAC: eval_utils.py:18-42 (cv2.solvePnPRansac, EPnP, 5 px, 10000 it) ---
+ * Correspondences of frame f are rows [f*stride, f*stride + count[f]) of pts2d/pts3d (float64,
+ * converted to float32 inside as cv2 does).  samples: [n_samples_sets, H, 5] int32 minimal-sample
+ * indices (host-generated cv::RNG stream); frame f uses sample set sample_set[f].
+ * Stage 1 solves one 5-point EPnP per hypothesis and counts inliers (float32 squared reprojection
+ * error <= thr^2); stage 2 replays cv2's sequential accept / adaptive-niters rule, recomputes the
+ * winner's inlier mask, refits EPnP on all inliers and converts to [R|t/scale].
+ * Outputs: pose [F,3,4] float64, inlier_mask [F,stride] uint8, n_inliers [F] int32,
+ * iters_run [F] int32, hyp_counts [F,H] int32 (diagnostic), hyp_pose [F,H,6] float64 (rvec,tvec). */
+size_t op_pnp_workspace_bytes(int F, int stride, int H);
+/* cv2's own minimal-sample stream, generated on the device: for frame f the first H index quintuples that
+ * RANSACPointSetRegistrator::getSubset draws from cv::RNG((uint64)-1) for count[f] correspondences
+ * (multiply-with-carry, redraw on duplicate).  samples [F,H,5] int32, sample_set [F] = 0..F-1. */
+int op_pnp_cv_samples(const int32_t *count, int F, int H, int32_t *samples, int32_t *sample_set, void *stream);
+int op_pnp_ransac(const double *pts2d, const double *pts3d, const int32_t *count, int F, int stride,
+                  const double *K /* [F,3,3] */, const int32_t *samples, const int32_t *sample_set, int H,
+                  double reproj_thr, double confidence, int max_iters, double scale,
+                  double *pose, uint8_t *inlier_mask, int32_t *n_inliers, int32_t *iters_run,
+                  int32_t *hyp_counts, double *hyp_pose, void *workspace, size_t workspace_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ONEPOSE_B200_H */

@@ -1,0 +1,119 @@
+"""ctypes binding of ``libonepose_b200.so`` -- the C ABI declared in ``include/onepose_b200.h``.
+
+There is no CPU or PyTorch fallback: if the CUDA library is missing or fails to load, importing this
+module raises.  (``torch`` is imported first so the CUDA runtime the library links against is the one
+already in the process.)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch  # noqa: F401  (loads libcudart before our library)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libonepose_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build the sm_100a CUDA library first "
+        "(python -m onepose_b200.build, or __graft_entry__.build()). onepose_b200 has no CPU fallback.")
+
+lib = C.CDLL(LIB_PATH)
+
+vp, i32, i64, f32, f64, sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
+
+_SIGS = {
+    "op_last_error": (C.c_char_p, []),
+    "op_abi_version": (i32, []),
+    "op_channel_major_to_point_major": (i32, [vp, vp, i32, i32, i32, i64, vp]),
+    "op_gats_leaf_aggregate": (i32, [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp]),
+    "op_linear": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
+    "op_linear_row_tiles": (i32, [i32]),
+    "op_instnorm_finalize": (i32, [vp, i32, i32, i32, i32, f32, vp, vp, vp]),
+    "op_kv_reduce_workspace_bytes": (sz, [i32, i32]),
+    "op_kv_reduce": (i32, [vp, vp, vp, i32, i32, vp, sz, vp]),
+    "op_attn_apply": (i32, [vp, vp, vp, vp, i32, i32, i32, vp]),
+    "op_l2_normalize_rows": (i32, [vp, vp, i64, i32, vp]),
+    "op_sim_dual_softmax_workspace_bytes": (sz, [i32, i32, i32]),
+    "op_sim_dual_softmax": (i32, [vp, vp, i32, i32, i32, f32, f32, vp, vp, vp, vp, vp, vp, sz, vp]),
+    "op_gather_matches": (i32, [vp, vp, vp, vp, i64, i32, i32, i32, f64, vp, vp, vp, vp, vp, vp]),
+    "op_pnp_workspace_bytes": (sz, [i32, i32, i32]),
+    "op_pnp_cv_samples": (i32, [vp, i32, i32, vp, vp, vp]),
+    "op_pnp_ransac": (i32, [vp, vp, vp, i32, i32, vp, vp, vp, i32, f64, f64, i32, f64,
+                            vp, vp, vp, vp, vp, vp, vp, sz, vp]),
+}
+EXPORTS = tuple(_SIGS)
+
+for _name, (_res, _args) in _SIGS.items():
+    _fn = getattr(lib, _name)          # AttributeError here = the library does not match the header
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+class OpError(RuntimeError):
+    pass
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise OpError(f"{what} failed (code {rc}): {lib.op_last_error().decode()}")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+# kernels launched by each entry point (for the bench's gpu_launches claim)
+LAUNCHES = {
+    "op_channel_major_to_point_major": 1, "op_gats_leaf_aggregate": 1, "op_linear": 1, "op_instnorm_finalize": 1,
+    "op_kv_reduce": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 7,
+    "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 3,
+}
+
+
+class Timeline:
+    """Optional per-call CUDA-event timing on the launching stream (used by bench.py only)."""
+
+    def __init__(self):
+        self.enabled = False
+        self.records = []        # (name, tag, start_event, end_event)
+        self.launches = 0
+        self.tag = ""
+
+    def reset(self):
+        self.records.clear()
+        self.launches = 0
+
+    def summary(self):
+        """name -> (total ms, calls); events must have completed (synchronize first)."""
+        out = {}
+        for name, tag, s, e in self.records:
+            key = name if not tag else f"{name}:{tag}"
+            ms, n = out.get(key, (0.0, 0))
+            out[key] = (ms + s.elapsed_time(e), n + 1)
+        return out
+
+
+timeline = Timeline()
+
+
+def call(name, *args, tag=None):
+    """Invoke an ABI entry point, raise on a non-zero return code, optionally time it with CUDA events."""
+    fn = getattr(lib, name)
+    if timeline.enabled:
+        s = torch.cuda.Event(enable_timing=True)
+        e = torch.cuda.Event(enable_timing=True)
+        s.record()
+        rc = fn(*args)
+        e.record()
+        timeline.records.append((name, tag if tag is not None else timeline.tag, s, e))
+        timeline.launches += LAUNCHES.get(name, 1)
+    else:
+        rc = fn(*args)
+    check(rc, name)

