@@ -85,18 +85,19 @@ class Timeline:
         self.records = []        # (name, tag, start_event, end_event)
         self.launches = 0
         self.tag = ""
+        self.work = 0.0          # algorithmic flops / bytes of the next call (set by the host code)
 
     def reset(self):
         self.records.clear()
         self.launches = 0
 
     def summary(self):
-        """name -> (total ms, calls); events must have completed (synchronize first)."""
+        """name -> (total ms, calls, total work); events must have completed (synchronize first)."""
         out = {}
-        for name, tag, s, e in self.records:
+        for name, tag, s, e, work in self.records:
             key = name if not tag else f"{name}:{tag}"
-            ms, n = out.get(key, (0.0, 0))
-            out[key] = (ms + s.elapsed_time(e), n + 1)
+            ms, n, w = out.get(key, (0.0, 0, 0.0))
+            out[key] = (ms + s.elapsed_time(e), n + 1, w + work)
         return out
 
 
@@ -112,8 +113,9 @@ def call(name, *args, tag=None):
         s.record()
         rc = fn(*args)
         e.record()
-        timeline.records.append((name, tag if tag is not None else timeline.tag, s, e))
+        timeline.records.append((name, tag if tag is not None else timeline.tag, s, e, timeline.work))
         timeline.launches += LAUNCHES.get(name, 1)
     else:
         rc = fn(*args)
+    timeline.work = 0.0
     check(rc, name)

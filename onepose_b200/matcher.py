@@ -17,7 +17,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from ._lib import call, lib, ptr, stream_ptr
+from ._lib import call, lib, ptr, stream_ptr, timeline
 
 GNN_LAYER_KINDS = ("GATs", "self", "cross") * 4      # GATs_SuperGlue.py:184
 _D = 256
@@ -189,33 +189,34 @@ class GATsSuperGlue(nn.Module):
     def _linear(self, A1, W, bias, C, B, rows, *, A2=None, flags=0, elu_cols=0, mean=None, rstd=None, stats=None, tag=""):
         K1 = A1.shape[-1]
         K2 = 0 if A2 is None else A2.shape[-1]
+        timeline.work = 2.0 * B * rows * (K1 + K2) * W.shape[0]           # algorithmic flops of this call
         call("op_linear", ptr(A1), K1, ptr(A2), K2, ptr(W), ptr(bias), ptr(C), B, rows, W.shape[0], flags,
                             elu_cols, ptr(mean), ptr(rstd), ptr(stats), stream_ptr(), tag=tag)
 
     def _kv(self, src, B, M, lw, tag):
         """K/V projection of the source stream + the KV / Ksum reduction (GATs_SuperGlue.py:90-97)."""
         dev = src.device
-        kv = self._ws.get("kv", (B, M, 2 * _D), torch.float32, dev)
+        kv = self._ws.get(f"kv{M}", (B, M, 2 * _D), torch.float32, dev)
         self._linear(src, lw["Wkv"], lw["bkv"], kv, B, M, flags=1, elu_cols=_D, tag="kv")      # OPB_LIN_ELU1 on K
         KV = self._ws.get("KV" + tag, (B, _HEADS, 64, 64), torch.float32, dev)
         Ks = self._ws.get("Ks" + tag, (B, _HEADS, 64), torch.float32, dev)
         nbytes = lib.op_kv_reduce_workspace_bytes(B, M)
-        w = self._ws.get("kvws", (nbytes,), torch.uint8, dev)
+        w = self._ws.get(f"kvws{M}", (nbytes,), torch.uint8, dev)
         call("op_kv_reduce", ptr(kv), ptr(KV), ptr(Ks), B, M, ptr(w), nbytes, stream_ptr())
         return KV, Ks
 
     def _propagate(self, x, B, N, M, KV, Ks, lw):
         """x-side of AttentionPropagation (GATs_SuperGlue.py:112-147); x [B,N,256] is updated in place."""
         dev = x.device
-        q = self._ws.get("q", (B, N, _D), torch.float32, dev)
+        q = self._ws.get(f"q{N}", (B, N, _D), torch.float32, dev)
         self._linear(x, lw["Wq"], lw["bq"], q, B, N, flags=1, elu_cols=_D, tag="q")
-        att = self._ws.get("att", (B, N, _D), torch.float32, dev)
+        att = self._ws.get(f"att{N}", (B, N, _D), torch.float32, dev)
         call("op_attn_apply", ptr(q), ptr(KV), ptr(Ks), ptr(att), B, N, M, stream_ptr())
         msg = q                                                     # q is dead: reuse as the merge output
         self._linear(att, lw["Wm"], lw["bm"], msg, B, N, tag="merge")
-        h = self._ws.get("h", (B, N, 2 * _D), torch.float32, dev)
+        h = self._ws.get(f"h{N}", (B, N, 2 * _D), torch.float32, dev)
         tiles = lib.op_linear_row_tiles(N)
-        stats = self._ws.get("stats", (B, tiles, 2 * _D, 2), torch.float64, dev)
+        stats = self._ws.get(f"stats{N}", (B, tiles, 2 * _D, 2), torch.float64, dev)
         self._linear(x, lw["W0"], lw["b0"], h, B, N, A2=msg, flags=4, stats=stats, tag="mlp0")  # OPB_LIN_STATS
         mean = self._ws.get("mean", (B, 2 * _D), torch.float32, dev)
         rstd = self._ws.get("rstd", (B, 2 * _D), torch.float32, dev)
@@ -240,6 +241,7 @@ class GATsSuperGlue(nn.Module):
             leaf_src, h3L, v1, v2 = wh_leaf, wh3, lw["a1"], lw["a2"]
         else:
             leaf_src, h3L, v1, v2 = leaves, x3, lw["v1"], lw["v2"]
+        timeline.work = 4.0 * _D * (Bl * N3 * L + 2 * B * N3)               # algorithmic bytes: leaves once, h3 in/out
         call("op_gats_leaf_aggregate", ptr(leaf_src), leaf_bstride, ptr(h3L), ptr(h3_add), ptr(v1), ptr(v2), ptr(x3),
                                          B, N3, L, 0.2, int(inc), 1, stream_ptr())
 
@@ -323,6 +325,7 @@ class GATsSuperGlue(nn.Module):
         s1 = torch.empty(B, N3, dtype=torch.float32, device=dev)
         nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
         w = self._ws.get("simws", (nbytes,), torch.uint8, dev)
+        timeline.work = B * (4.0 * _D * (N2 + N3) + 4.0 * N2 * N3 + 24.0 * (N2 + N3))   # bytes, SURVEY.md 8(d)
         call("op_sim_dual_softmax", ptr(m2), ptr(m3), B, N2, N3, float(self.hparams["scale_factor"]),
                                       float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
                                       ptr(s1), ptr(w), nbytes, stream_ptr())
