@@ -99,6 +99,12 @@ int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3,
                         float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                         float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
                         void *stream);
+/* Same contract on fp32 CUDA cores (exact fp32 dot products, no tensor cores): kept as the on-device
+ * cross-check of the tcgen05 split-precision kernel, not used by the product path. */
+int op_sim_dual_softmax_simt(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+                             float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                             float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
+                             void *stream);
 
 /* valid-match gather (inference.py:147-152): per frame, ascending query index.
  * pts2d [B,N2,2] fp32, pts3d [Bk,N3,3] fp32 (kp3_bstride elements, 0 = shared), out2d [B,N2,2] / out3d [B,N2,3] float64

@@ -8,6 +8,7 @@
 // 64-bit keys (value bits high, inverted index low => ties resolve to the smallest index).  All
 // cross-tile reductions go through per-tile partials folded in a fixed order (deterministic).
 #include "common.cuh"
+#include "sim_tc.cuh"
 
 namespace opb {
 
@@ -221,6 +222,7 @@ __global__ void k_mutual_select(const int *__restrict__ idx0, const float *__res
 
 struct SimWorkspace {
     float *rowsum_part, *colsum_part, *invR, *invC, *val0, *val1;
+    __half *m2h, *m2l, *m3h, *m3l;
     unsigned long long *rowmax_part, *colmax_part;
     int *idx0, *idx1;
     size_t bytes;
@@ -241,6 +243,10 @@ static SimWorkspace carve(void *base, int B, int N2, int N3) {
     w.val1 = (float *)take((size_t)B * N3 * 4);
     w.idx0 = (int *)take((size_t)B * N2 * 4);
     w.idx1 = (int *)take((size_t)B * N3 * 4);
+    w.m2h = (__half *)take((size_t)B * N2 * kD * 2);
+    w.m2l = (__half *)take((size_t)B * N2 * kD * 2);
+    w.m3h = (__half *)take((size_t)B * N3 * kD * 2);
+    w.m3l = (__half *)take((size_t)B * N3 * kD * 2);
     w.bytes = off;
     return w;
 }
@@ -251,10 +257,10 @@ extern "C" size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3) {
     return opb::carve(nullptr, B > 0 ? B : 1, N2 > 0 ? N2 : 1, N3 > 0 ? N3 : 1).bytes;
 }
 
-extern "C" int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
-                                   float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
-                                   float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
-                                   void *stream) {
+static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+                    float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                    float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
+                    void *stream) {
     using namespace opb;
     OPB_CHECK_ARG(m2 && m3 && conf && matches0 && matches1 && scores0 && scores1 && workspace, "op_sim_dual_softmax: null pointer");
     OPB_CHECK_ARG(B > 0 && N2 > 0 && N3 > 0 && B <= 65535, "op_sim_dual_softmax: bad shape B=%d N2=%d N3=%d", B, N2, N3);
@@ -268,15 +274,55 @@ extern "C" int op_sim_dual_softmax(const float *m2, const float *m3, int B, int 
     p.rowsum_part = w.rowsum_part; p.colsum_part = w.colsum_part; p.invR = w.invR; p.invC = w.invC;
     p.rowmax_part = w.rowmax_part; p.colmax_part = w.colmax_part; p.conf = conf;
     OPB_CHECK_ARG(p.tiles_m <= 65535, "op_sim_dual_softmax: N2 too large");
-    dim3 grid(p.tiles_n, p.tiles_m, B);
-    k_sim_pass<1><<<grid, 256, 0, st>>>(p);
-    OPB_CHECK_LAUNCH();
-    k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n, N2, w.invR);
-    k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC);
-    OPB_CHECK_LAUNCH();
-    k_sim_pass<2><<<grid, 256, 0, st>>>(p);
-    OPB_CHECK_LAUNCH();
-    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, p.tiles_n, N2, w.idx0, w.val0);
+    int row_parts = p.tiles_n;                       // partials per query row (column tiles or column splits)
+    if (!tensor_cores) {
+        dim3 grid(p.tiles_n, p.tiles_m, B);
+        k_sim_pass<1><<<grid, 256, 0, st>>>(p);
+        OPB_CHECK_LAUNCH();
+        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, row_parts, N2, w.invR);
+        k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC);
+        OPB_CHECK_LAUNCH();
+        k_sim_pass<2><<<grid, 256, 0, st>>>(p);
+        OPB_CHECK_LAUNCH();
+    } else {
+        // split fp32 unit rows into scaled fp16 hi/lo planes, describe them to TMA, run the two tcgen05 passes
+        const long long n2e = (long long)B * N2 * kD, n3e = (long long)B * N3 * kD;
+        simtc::k_split_planes<<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, n2e, simtc::kOperandScale);
+        simtc::k_split_planes<<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, n3e, simtc::kOperandScale);
+        OPB_CHECK_LAUNCH();
+        CUtensorMap t2h, t2l, t3h, t3l;
+        int rc;
+        if ((rc = make_tmap_f16_3d(&t2h, w.m2h, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) ||
+            (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, simtc::BN)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, simtc::BN)))
+            return rc;
+        // enough CTAs for ~2 waves over 148 SMs: split the column tiles when frames x row tiles is small
+        int splits = ceil_div(2 * 148, (long long)B * p.tiles_m);
+        splits = splits < 1 ? 1 : (splits > p.tiles_n ? p.tiles_n : splits);
+        simtc::Params q{};
+        q.N2 = N2; q.N3 = N3; q.tiles_n = p.tiles_n; q.tiles_per_split = ceil_div(p.tiles_n, splits);
+        splits = ceil_div(p.tiles_n, q.tiles_per_split);
+        row_parts = splits;
+        const double log2e = 1.4426950408889634;
+        q.c1 = (float)(log2e / ((double)scale_factor * simtc::kOperandScale * simtc::kOperandScale));
+        q.c0 = (float)(log2e / (double)scale_factor);
+        q.rowsum_part = w.rowsum_part; q.colsum_part = w.colsum_part; q.invR = w.invR; q.invC = w.invC;
+        q.rowmax_part = w.rowmax_part; q.colmax_part = w.colmax_part; q.conf = conf;
+        static bool configured = false;
+        if (!configured) {
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            configured = true;
+        }
+        dim3 grid(splits, p.tiles_m, B);
+        simtc::k_sim_tc<1><<<grid, 192, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
+        OPB_CHECK_LAUNCH();
+        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n, N2, w.invR);
+        k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC);
+        OPB_CHECK_LAUNCH();
+        simtc::k_sim_tc<2><<<grid, 192, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
+        OPB_CHECK_LAUNCH();
+    }
+    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, w.idx0, w.val0);
     k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, w.idx1, w.val1);
     OPB_CHECK_LAUNCH();
     const int nmax = N2 > N3 ? N2 : N3;
@@ -284,4 +330,18 @@ extern "C" int op_sim_dual_softmax(const float *m2, const float *m3, int B, int 
                                                                   matches0, matches1, scores0, scores1);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
+}
+
+extern "C" int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+                                   float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                                   float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
+    return sim_impl(true, m2, m3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
+                    workspace, workspace_bytes, stream);
+}
+
+extern "C" int op_sim_dual_softmax_simt(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+                                        float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                                        float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
+    return sim_impl(false, m2, m3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
+                    workspace, workspace_bytes, stream);
 }

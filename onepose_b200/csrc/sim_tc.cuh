@@ -1,0 +1,258 @@
+// tcgen05 / TMA version of the similarity + dual-softmax passes (included by sim_dual_softmax.cu).
+//
+// One CTA owns 128 query rows of one frame and walks a range of 128-column tiles of the 3D points.
+//   warp 4   : TMA producer.  The CTA's A operand (128 rows x K=256, fp16 hi and lo planes, 128 KB) is loaded once
+//              and stays resident; B (3D descriptors) streams through a ring of five 16 KB units, one unit =
+//              one 64-wide k-block of one plane (hi or lo) of a 128-column tile.
+//   warp 5   : TMEM allocation + single-thread tcgen05.mma issue.  Per k-block: Ah*Bh, Al*Bh on the hi unit,
+//              Ah*Bl on the lo unit (split precision, see tc_common.cuh); fp32 accumulators are double-buffered
+//              in TMEM (2 x 128 columns) so the epilogue of tile j overlaps the MMAs of tile j+1.
+//   warps 0-3: epilogue.  Thread = one query row (TMEM lane).  e = exp2(acc*c1 - c0) with the fixed shift
+//              1/scale (|cos| <= 1).  PASS 1 keeps the row sum in a register and reduces column sums across the
+//              128 rows with a shuffle transpose-reduce; PASS 2 writes conf = (e/R)(e/C) once, 512 contiguous
+//              bytes per thread, and tracks row / column maxima as packed (value, inverted index) keys.
+#pragma once
+#include "tc_common.cuh"
+
+namespace opb {
+namespace simtc {
+
+constexpr int BM = 128, BN = 128, NKB = 4, UNITS = 5;
+constexpr int TILE_BYTES = 128 * 128;                 // 128 rows x 64 fp16
+constexpr int A_BYTES = 2 * NKB * TILE_BYTES;         // 131072
+constexpr int RING_BYTES = UNITS * TILE_BYTES;        // 81920
+constexpr int SCRATCH_BYTES = 2 * 4 * BN * 8;         // double-buffered [4 warps][128] u64
+constexpr int SMEM_BYTES = A_BYTES + RING_BYTES + SCRATCH_BYTES + 256 + 1024;   // + barriers + alignment slack
+constexpr float kOperandScale = 64.f;                 // unit-vector components are scaled into fp16's normal range
+
+struct Params {
+    int N2, N3, tiles_n, tiles_per_split;
+    float c1, c0;                                     // e = exp2(acc * c1 - c0)
+    float *rowsum_part, *colsum_part;                 // [B][tiles_n][N2] (per column tile), [B][tiles_m][N3]
+    const float *invR, *invC;
+    unsigned long long *rowmax_part, *colmax_part;
+    float *conf;
+};
+
+struct Barriers {
+    uint64_t a_full, b_full[UNITS], b_empty[UNITS], acc_full[2], acc_empty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// sum over the 32 lanes of v[i]; lane L ends up with the total of element L in v[0]
+__device__ __forceinline__ float transpose_reduce_sum(float *v, int lane) {
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        const bool upper = (lane & step) != 0;
+#pragma unroll
+        for (int i = 0; i < step; ++i) {
+            const float send = upper ? v[i] : v[i + step];
+            const float keep = upper ? v[i + step] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, step);
+        }
+    }
+    return v[0];
+}
+__device__ __forceinline__ unsigned long long transpose_reduce_max(unsigned long long *v, int lane) {
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        const bool upper = (lane & step) != 0;
+#pragma unroll
+        for (int i = 0; i < step; ++i) {
+            const unsigned long long send = upper ? v[i] : v[i + step];
+            const unsigned long long keep = upper ? v[i + step] : v[i];
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, send, step);
+            v[i] = keep > other ? keep : other;
+        }
+    }
+    return v[0];
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(192, 1)
+k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l,
+         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l, const Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *sA = smem, *sB = smem + A_BYTES;
+    unsigned long long *scratch = reinterpret_cast<unsigned long long *>(smem + A_BYTES + RING_BYTES);
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + SCRATCH_BYTES);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int split = blockIdx.x, row_tile = blockIdx.y, b = blockIdx.z;
+    const int m0 = row_tile * BM;
+    const int t0 = split * p.tiles_per_split;
+    const int t1 = min(p.tiles_n, t0 + p.tiles_per_split);
+    if (t0 >= t1) return;                                   // uniform for the whole CTA
+
+    if (threadIdx.x == 0) {
+        tc::mbar_init(&bar->a_full, 1);
+        for (int i = 0; i < UNITS; ++i) { tc::mbar_init(&bar->b_full[i], 1); tc::mbar_init(&bar->b_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], 128); }
+        tc::fence_barrier_init();
+    }
+    if (warp == 5) tc::tmem_alloc<256>(&bar->tmem_base);
+    if (warp == 4 && lane == 0) {
+        tc::tma_prefetch_desc(&tm_m2h); tc::tma_prefetch_desc(&tm_m2l); tc::tma_prefetch_desc(&tm_m3h); tc::tma_prefetch_desc(&tm_m3l);
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = bar->tmem_base;
+
+    if (warp == 4) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            tc::mbar_arrive_expect_tx(&bar->a_full, A_BYTES);
+            for (int plane = 0; plane < 2; ++plane)
+                for (int kb = 0; kb < NKB; ++kb)
+                    tc::tma_load_3d(sA + (plane * NKB + kb) * TILE_BYTES, plane ? &tm_m2l : &tm_m2h, &bar->a_full, kb * 64, m0, b);
+            uint32_t u = 0;
+            for (int t = t0; t < t1; ++t)
+                for (int kb = 0; kb < NKB; ++kb)
+                    for (int plane = 0; plane < 2; ++plane, ++u) {
+                        const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
+                        tc::mbar_wait(&bar->b_empty[stage], ph ^ 1);
+                        tc::mbar_arrive_expect_tx(&bar->b_full[stage], TILE_BYTES);
+                        tc::tma_load_3d(sB + stage * TILE_BYTES, plane ? &tm_m3l : &tm_m3h, &bar->b_full[stage], kb * 64, t * BN, b);
+                    }
+        }
+        __syncwarp();
+    } else if (warp == 5) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN);
+            tc::mbar_wait(&bar->a_full, 0);
+            tc::tcgen05_fence_after();
+            const uint32_t a_base = tc::smem_u32(sA), b_base = tc::smem_u32(sB);
+            uint32_t u = 0;
+            int j = 0;
+            for (int t = t0; t < t1; ++t, ++j) {
+                const uint32_t as = j & 1, aph = (j >> 1) & 1;
+                tc::mbar_wait(&bar->acc_empty[as], aph ^ 1);
+                tc::tcgen05_fence_after();
+                const uint32_t d = tmem_base + as * BN;
+                for (int kb = 0; kb < NKB; ++kb)
+                    for (int plane = 0; plane < 2; ++plane, ++u) {
+                        const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
+                        tc::mbar_wait(&bar->b_full[stage], ph);
+                        tc::tcgen05_fence_after();
+                        const uint64_t bd = tc::umma_desc_k128(b_base + stage * TILE_BYTES);
+                        const uint64_t ah = tc::umma_desc_k128(a_base + kb * TILE_BYTES);
+                        const uint64_t al = tc::umma_desc_k128(a_base + (NKB + kb) * TILE_BYTES);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {            // UMMA_K = 16 fp16 = 32 bytes -> +2 in the address field
+                            if (plane == 0) {
+                                tc::umma_f16(d, ah + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                                tc::umma_f16(d, al + 2 * k, bd + 2 * k, idesc, 1);
+                            } else {
+                                tc::umma_f16(d, ah + 2 * k, bd + 2 * k, idesc, 1);
+                            }
+                        }
+                        tc::umma_commit(&bar->b_empty[stage]);    // frees the ring unit when these MMAs retire
+                    }
+                tc::umma_commit(&bar->acc_full[as]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ================= epilogue (warps 0-3, one query row per thread) =================
+        const int row = m0 + warp * 32 + lane;
+        const bool row_ok = row < p.N2;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(warp * 32) << 16);
+        float row_sum = 0.f;
+        unsigned long long row_key = 0ull;
+        float ir = 0.f;
+        if (PASS == 2 && row_ok) ir = p.invR[(long long)b * p.N2 + row];
+        float *crow = PASS == 2 ? p.conf + ((long long)b * p.N2 + (row_ok ? row : 0)) * p.N3 : nullptr;
+        const bool vec_ok = (p.N3 & 3) == 0;
+        int j = 0;
+        for (int t = t0; t < t1; ++t, ++j) {
+            const uint32_t as = j & 1, aph = (j >> 1) & 1;
+            unsigned long long *scr = scratch + (j & 1) * 4 * BN;
+            tc::mbar_wait(&bar->acc_full[as], aph);
+            tc::tcgen05_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                float v[32];
+                tc::tmem_ld_32x32(lane_base + as * BN + c * 32, v);
+                tc::tmem_ld_wait();
+                if (c == 3) { tc::tcgen05_fence_before(); tc::mbar_arrive(&bar->acc_empty[as]); }   // TMEM buffer is free again
+                const int col0 = t * BN + c * 32;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float e = exp2f(fmaf(v[i], p.c1, -p.c0));
+                    v[i] = (row_ok && col0 + i < p.N3) ? e : 0.f;
+                }
+                if (PASS == 1) {
+                    if (c == 0) row_sum = 0.f;               // per-tile partial: the fold over tiles is split-invariant
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) row_sum += v[i];
+                    if (c == 3 && row_ok) p.rowsum_part[((long long)b * p.tiles_n + t) * p.N2 + row] = row_sum;
+                    const float cs = transpose_reduce_sum(v, lane);
+                    reinterpret_cast<float *>(scr)[warp * BN + c * 32 + lane] = cs;
+                } else {
+                    unsigned long long keys[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int col = col0 + i;
+                        const float ic = col < p.N3 ? __ldg(p.invC + (long long)b * p.N3 + col) : 0.f;
+                        const float cf = (v[i] * ic) * (v[i] * ir);
+                        v[i] = cf;
+                        const bool ok = row_ok && col < p.N3;
+                        const unsigned long long kr = ok ? (((unsigned long long)__float_as_uint(cf) << 32) | (0xffffffffu - (unsigned)col)) : 0ull;
+                        row_key = kr > row_key ? kr : row_key;
+                        keys[i] = ok ? (((unsigned long long)__float_as_uint(cf) << 32) | (0xffffffffu - (unsigned)row)) : 0ull;
+                    }
+                    if (row_ok) {
+                        if (vec_ok && col0 + 31 < p.N3) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q)
+                                *reinterpret_cast<float4 *>(crow + col0 + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                        } else {
+                            for (int i = 0; i < 32; ++i) if (col0 + i < p.N3) crow[col0 + i] = v[i];
+                        }
+                    }
+                    const unsigned long long ck = transpose_reduce_max(keys, lane);
+                    scr[warp * BN + c * 32 + lane] = ck;
+                }
+            }
+            epi_bar_sync();
+            {   // fold the four warps' column partials in a fixed order: thread = column
+                const int tid = threadIdx.x, col = t * BN + tid;
+                if (col < p.N3) {
+                    if (PASS == 1) {
+                        const float *s = reinterpret_cast<const float *>(scr);
+                        p.colsum_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] = ((s[tid] + s[BN + tid]) + s[2 * BN + tid]) + s[3 * BN + tid];
+                    } else {
+                        unsigned long long k = scr[tid];
+#pragma unroll
+                        for (int w = 1; w < 4; ++w) k = scr[w * BN + tid] > k ? scr[w * BN + tid] : k;
+                        p.colmax_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] = k;
+                    }
+                }
+            }
+        }
+        if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * gridDim.x + split) * p.N2 + row] = row_key;
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 5) tc::tmem_dealloc<256>(tmem_base);
+}
+
+// fp32 rows -> scaled fp16 hi / lo planes
+__global__ void k_split_planes(const float *__restrict__ x, __half *__restrict__ hi, __half *__restrict__ lo, long long n, float scale) {
+    const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= n) return;
+    const float4 v = *reinterpret_cast<const float4 *>(x + i);
+    __half h[4], l[4];
+    tc::split_f16(v.x * scale, h[0], l[0]); tc::split_f16(v.y * scale, h[1], l[1]);
+    tc::split_f16(v.z * scale, h[2], l[2]); tc::split_f16(v.w * scale, h[3], l[3]);
+    *reinterpret_cast<uint2 *>(hi + i) = *reinterpret_cast<uint2 *>(h);
+    *reinterpret_cast<uint2 *>(lo + i) = *reinterpret_cast<uint2 *>(l);
+}
+
+}  // namespace simtc
+}  // namespace opb

@@ -1,0 +1,24 @@
+// Host-side TMA tensor-map construction (driver API cuTensorMapEncodeTiled).
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace opb {
+
+int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows) {
+    cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)batch};
+    cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)rows * cols * 2};     // bytes, dims 1 and 2
+    cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = cuTensorMapEncodeTiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(base), dims, strides, box, estr,
+                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        const char *msg = nullptr;
+        cuGetErrorString(r, &msg);
+        set_error("cuTensorMapEncodeTiled failed: %s (rows=%d cols=%d batch=%d)", msg ? msg : "?", rows, cols, batch);
+        return OPB_ERR_CUDA;
+    }
+    return OPB_OK;
+}
+
+}  // namespace opb

@@ -127,3 +127,44 @@ def test_lit_wrapper_contract():
     pred, conf = lit(data)
     assert set(["matches0", "matches1", "matching_scores0", "matching_scores1"]) <= set(pred)
     assert conf.shape == (1, 48, 64)
+
+
+def _run_sim(fn_name, m2, m3, scale=0.07, thr=0.2):
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    B, N2, _ = m2.shape
+    N3 = m3.shape[1]
+    conf = torch.empty(B, N2, N3, device="cuda")
+    i0 = torch.empty(B, N2, dtype=torch.int64, device="cuda"); i1 = torch.empty(B, N3, dtype=torch.int64, device="cuda")
+    s0 = torch.empty(B, N2, device="cuda"); s1 = torch.empty(B, N3, device="cuda")
+    nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    call(fn_name, ptr(m2), ptr(m3), B, N2, N3, scale, thr, ptr(conf), ptr(i0), ptr(i1), ptr(s0), ptr(s1), ptr(ws), nbytes,
+         stream_ptr())
+    torch.cuda.synchronize()
+    return conf, i0, i1, s0, s1
+
+
+@pytest.mark.parametrize("shape", [(2, 300, 500), (1, 129, 257), (3, 128, 128), (1, 2048, 8192), (1, 45, 1000)])
+def test_sim_tcgen05_vs_cuda_core_and_float64(shape):
+    """The tcgen05 split-precision kernel against the exact-fp32 CUDA-core kernel and a float64 restatement."""
+    B, N2, N3 = shape
+    g = torch.Generator().manual_seed(N2 * 7 + N3)
+    m2 = torch.nn.functional.normalize(torch.randn(B, N2, 256, generator=g), dim=2)
+    m3 = torch.nn.functional.normalize(torch.randn(B, N3, 256, generator=g), dim=2)
+    # plant strong correspondences so the softmax is peaked and matches exist
+    k = min(N2, N3) // 2
+    m3[:, :k] = torch.nn.functional.normalize(m2[:, :k] + 0.05 * torch.randn(B, k, 256, generator=g), dim=2)
+    m2c, m3c = m2.cuda().contiguous(), m3.cuda().contiguous()
+    tc = _run_sim("op_sim_dual_softmax", m2c, m3c)
+    cc = _run_sim("op_sim_dual_softmax_simt", m2c, m3c)
+    s = torch.matmul(m2.double(), m3.double().transpose(1, 2)) / 0.07
+    ref = torch.softmax(s, 1) * torch.softmax(s, 2)
+    assert helpers.conf_rel_err(tc[0].cpu(), ref) < helpers.CONF_RTOL
+    assert helpers.conf_rel_err(cc[0].cpu(), ref) < helpers.CONF_RTOL
+    for b in range(B):
+        helpers.assert_matches_equal_off_ties(tc[1][b].cpu(), cc[1][b].cpu(), ref[b], axis=2)
+        helpers.assert_matches_equal_off_ties(tc[2][b].cpu(), cc[2][b].cpu(), ref[b], axis=1)
+    assert int((tc[1] > -1).sum()) >= k // 2
+    # deterministic
+    tc2 = _run_sim("op_sim_dual_softmax", m2c, m3c)
+    assert torch.equal(tc[0], tc2[0]) and torch.equal(tc[1], tc2[1])
