@@ -58,7 +58,7 @@ def build(force=False, verbose=False):
     with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
         list(ex.map(run, jobs))
     if jobs or force or _stale(LIB, objs):
-        run([NVCC] + ARCH + ["-shared", "-cudart", "shared", "-o", LIB] + objs + ["-lcuda"])
+        run([NVCC] + ARCH + ["-shared", "-cudart", "shared", "-o", LIB] + objs)
     return LIB
 
 

@@ -9,13 +9,27 @@ int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, in
     cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)rows * cols * 2};     // bytes, dims 1 and 2
     cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = cuTensorMapEncodeTiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(base), dims, strides, box, estr,
+    // the driver entry point is resolved at run time so that the library loads (and exports its ABI) on
+    // hosts without libcuda.so.1 -- nothing here links against the driver library.
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+            set_error("cuTensorMapEncodeTiled is not available from the CUDA driver (%s)", cudaGetErrorString(e));
+            return OPB_ERR_CUDA;
+        }
+        encode = (encode_fn)fn;
+    }
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(base), dims, strides, box, estr,
                                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
-        const char *msg = nullptr;
-        cuGetErrorString(r, &msg);
-        set_error("cuTensorMapEncodeTiled failed: %s (rows=%d cols=%d batch=%d)", msg ? msg : "?", rows, cols, batch);
+        set_error("cuTensorMapEncodeTiled failed: CUresult %d (rows=%d cols=%d batch=%d)", (int)r, rows, cols, batch);
         return OPB_ERR_CUDA;
     }
     return OPB_OK;
