@@ -86,6 +86,29 @@ int op_kv_reduce(const float *kv, float *KV, float *Ksum, int B, int M, void *wo
 int op_attn_apply(const float *Qp, const float *KV, const float *Ksum, float *out, int B, int N, int M,
                   void *stream);
 
+/* ---- (2b) the same projections on the 5th-gen tensor cores (tcgen05 + TMA) -------------------------
+ * Operands are "split-precision planes": a tensor x is held as two fp16 arrays hi = fp16(64 x),
+ * lo = fp16(64 x - hi) (22 significant bits; |x| < 1023).  A product is three kind::f16 MMAs
+ * (hi*hi + lo*hi + hi*lo) accumulated in fp32 TMEM, which keeps conf_matrix within the 1e-3 bound
+ * where a single fp16/bf16/tf32 pass does not (precision).  Plane pointers are void*
+ * (fp16 storage), 16-byte aligned; K1, K2 multiples of 64; Cout 256 or 512.
+ * op_linear_tc: C = epi([A1|A2] . W^T); outputs fp32 C and/or planes (Ch, Cl) for the next GEMM.
+ * flags: OPB_LIN_ELU1, OPB_LIN_RESIDUAL (C += result, needs C), OPB_LIN_STATS (stats_partial
+ * [B][op_linear_tc_stat_parts(rows)][Cout][2] fp32 partial sum / sum of squares of the result
+ * WITHOUT the bias; op_instnorm_finalize_tc folds them in float64 and adds the bias to the mean). */
+int op_split_planes(const float *x, void *hi, void *lo, long long n, void *stream);
+int op_norm_relu_split(const float *h, const float *mean, const float *rstd, void *hi, void *lo, int B, int rows,
+                       int C, void *stream);
+int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
+                 const void *Wl, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
+                 int flags, int elu_cols, float *stats_partial, void *stream);
+int op_linear_tc_stat_parts(int rows_per_batch);
+int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B, int parts, int C, int rows_per_batch,
+                            float eps, float *mean, float *rstd, void *stream);
+/* op_attn_apply writing split-precision planes instead of fp32 */
+int op_attn_apply_planes(const float *Qp, const float *KV, const float *Ksum, void *out_hi, void *out_lo, int B, int N,
+                         int M, void *stream);
+
 /* row-wise L2 normalisation x / max(||x||, 1e-12)  (F.normalize, :245-246); in place allowed */
 int op_l2_normalize_rows(const float *x, float *out, long long rows, int C, void *stream);
 

@@ -6,6 +6,7 @@
 // block reduces a chunk of points and a second kernel folds the chunk partials in a fixed order, so
 // results are bit-reproducible run to run.
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace opb {
 
@@ -75,7 +76,7 @@ __global__ void k_kv_finalize(const float *__restrict__ partial, float *__restri
 // out[n, h*64+q] = (Q'[n,h,:] . KV[h,:,q]) * M / (Q'[n,h,:] . Ksum[h,:] + 1e-6)
 __global__ void __launch_bounds__(256)
 k_attn_apply(const float *__restrict__ Qp, const float *__restrict__ KV, const float *__restrict__ Ksum,
-             float *__restrict__ out, int N, int M) {
+             float *__restrict__ out, __half *__restrict__ out_hi, __half *__restrict__ out_lo, int N, int M) {
     __shared__ __align__(16) float KVs[kDh][kDh];
     __shared__ __align__(16) float Qs[64][kDh + 4];
     __shared__ float Kss[kDh];
@@ -115,7 +116,15 @@ k_attn_apply(const float *__restrict__ Qp, const float *__restrict__ KV, const f
         if (n >= N) continue;
         const float z = 1.f / (den[i] + 1e-6f);
         float4 o = make_float4(acc[i][0] * z * fM, acc[i][1] * z * fM, acc[i][2] * z * fM, acc[i][3] * z * fM);
-        *reinterpret_cast<float4 *>(out + ((long long)b * N + n) * kD + h * kDh + qx * 4) = o;
+        const long long off = ((long long)b * N + n) * kD + h * kDh + qx * 4;
+        if (out) *reinterpret_cast<float4 *>(out + off) = o;
+        if (out_hi) {            // split-precision planes of 64*x for the tcgen05 merge projection (linear_tc.cuh)
+            __half hh[4], ll[4];
+            tc::split_f16(o.x * 64.f, hh[0], ll[0]); tc::split_f16(o.y * 64.f, hh[1], ll[1]);
+            tc::split_f16(o.z * 64.f, hh[2], ll[2]); tc::split_f16(o.w * 64.f, hh[3], ll[3]);
+            *reinterpret_cast<uint2 *>(out_hi + off) = *reinterpret_cast<uint2 *>(hh);
+            *reinterpret_cast<uint2 *>(out_lo + off) = *reinterpret_cast<uint2 *>(ll);
+        }
     }
 }
 
@@ -149,7 +158,17 @@ extern "C" int op_attn_apply(const float *Qp, const float *KV, const float *Ksum
     OPB_CHECK_ARG(Qp && KV && Ksum && out, "op_attn_apply: null pointer");
     OPB_CHECK_ARG(B > 0 && N > 0 && M > 0 && B <= 65535, "op_attn_apply: bad shape B=%d N=%d M=%d", B, N, M);
     dim3 grid(opb::ceil_div(N, 64), opb::kHeads, B);
-    opb::k_attn_apply<<<grid, 256, 0, (cudaStream_t)stream>>>(Qp, KV, Ksum, out, N, M);
+    opb::k_attn_apply<<<grid, 256, 0, (cudaStream_t)stream>>>(Qp, KV, Ksum, out, nullptr, nullptr, N, M);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
+
+extern "C" int op_attn_apply_planes(const float *Qp, const float *KV, const float *Ksum, void *out_hi, void *out_lo, int B, int N,
+                                    int M, void *stream) {
+    OPB_CHECK_ARG(Qp && KV && Ksum && out_hi && out_lo, "op_attn_apply_planes: null pointer");
+    OPB_CHECK_ARG(B > 0 && N > 0 && M > 0 && B <= 65535, "op_attn_apply_planes: bad shape B=%d N=%d M=%d", B, N, M);
+    dim3 grid(opb::ceil_div(N, 64), opb::kHeads, B);
+    opb::k_attn_apply<<<grid, 256, 0, (cudaStream_t)stream>>>(Qp, KV, Ksum, nullptr, (__half *)out_hi, (__half *)out_lo, N, M);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

@@ -1,0 +1,240 @@
+// tcgen05 / TMA fused linear layer on split-precision fp16 planes (included by linear_tc.cu).
+//
+// C[b,n,:] = epi( [A1 | A2][b,n,:] . W^T ),  fp32-class accuracy from kind::f16 MMAs: every operand is kept as
+// two fp16 planes (hi, lo) of the value scaled by 64 (tc_common.cuh), and a product is issued as three MMAs
+// Ah*Wh + Al*Wh + Ah*Wl accumulated in fp32 TMEM.
+//
+// Persistent CTA (one per SM), 128-row x 256-column output tiles, tiles never straddle frames:
+//   warp 8    : TMA producer.  Per 64-wide k-block one stage = {A hi 16 KB, W hi 32 KB | A lo 16 KB, W lo 32 KB};
+//               the hi and lo halves complete on separate mbarriers so the Ah*Wh MMAs start as soon as they land.
+//   warp 9    : TMEM allocation (512 columns = two 128x256 fp32 accumulators) + single-thread tcgen05.mma issue.
+//   warps 0-7 : epilogue; warp w reads TMEM lane quadrant w%4 (32 rows, thread = row) and column half w/4.
+//               acc/4096 -> [InstanceNorm partial statistics] -> +bias -> [elu+1] -> [+= residual] -> fp32 store
+//               and/or re-split into the hi/lo planes the next GEMM consumes.  The epilogue of tile j overlaps
+//               the MMAs of tile j+1 (double-buffered accumulator).
+#pragma once
+#include "tc_common.cuh"
+
+namespace opb {
+namespace lintc {
+
+constexpr int BM = 128, BN = 256, BK = 64, STAGES = 2;
+constexpr int A_PLANE = BM * BK * 2;                  // 16384
+constexpr int W_PLANE = BN * BK * 2;                  // 32768
+constexpr int HALF_BYTES = A_PLANE + W_PLANE;         // one precision half of a stage (49152)
+constexpr int STAGE_BYTES = 2 * HALF_BYTES;           // 98304
+constexpr int BIAS_FLOATS = 512;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BIAS_FLOATS * 4 + 256 + 1024;
+constexpr int EPI_WARPS = 8, THREADS = (EPI_WARPS + 2) * 32;
+constexpr float kScale = 64.f;                        // activations and weights are stored as 64*x
+constexpr float kInvScale2 = 1.f / (kScale * kScale);
+
+struct Params {
+    int B, rows, Cout, K1, K2, flags, elu_cols;
+    int row_tiles, col_tiles, total_tiles;
+    const float *bias;
+    float *C;                      // fp32 [B, rows, Cout] or null
+    __half *Ch, *Cl;               // planes [B, rows, Cout] (x64) or null
+    float2 *stats;                 // [B][row_tiles*4][Cout] (sum, sum of squares) of the PRE-BIAS result
+};
+
+struct Barriers {
+    uint64_t full_hi[STAGES], full_lo[STAGES], empty[STAGES], acc_full[2], acc_empty[2];
+    uint32_t tmem_base;
+};
+
+// sum over the 32 lanes of v[i]; lane L ends up with the total of element L in v[0]
+__device__ __forceinline__ float transpose_reduce_sum(float *v, int lane) {
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+        const bool upper = (lane & step) != 0;
+#pragma unroll
+        for (int i = 0; i < step; ++i) {
+            const float send = upper ? v[i] : v[i + step];
+            const float keep = upper ? v[i + step] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, step);
+        }
+    }
+    return v[0];
+}
+
+__device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
+    return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
+}
+
+// 32 fp32 values -> 32 (hi, lo) fp16 pairs of 64*x, stored as 64 contiguous bytes per plane
+__device__ __forceinline__ void store_planes32(const float *v, __half *hi_dst, __half *lo_dst) {
+    uint32_t h[16], l[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        __half h0, l0, h1, l1;
+        tc::split_f16(v[2 * i] * kScale, h0, l0);
+        tc::split_f16(v[2 * i + 1] * kScale, h1, l1);
+        h[i] = pack_h2(h0, h1);
+        l[i] = pack_h2(l0, l1);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        reinterpret_cast<uint4 *>(hi_dst)[q] = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+        reinterpret_cast<uint4 *>(lo_dst)[q] = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
+    }
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ CUtensorMap tm_a1l,
+            const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
+            const __grid_constant__ CUtensorMap tm_wh, const __grid_constant__ CUtensorMap tm_wl, const Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float *s_bias = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES);
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + STAGES * STAGE_BYTES + BIAS_FLOATS * 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nkb1 = p.K1 / BK, nkb = (p.K1 + p.K2) / BK;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; ++i) { tc::mbar_init(&bar->full_hi[i], 1); tc::mbar_init(&bar->full_lo[i], 1); tc::mbar_init(&bar->empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], EPI_WARPS); }
+        tc::fence_barrier_init();
+    }
+    for (int i = threadIdx.x; i < BIAS_FLOATS; i += THREADS) s_bias[i] = (p.bias && i < p.Cout) ? p.bias[i] : 0.f;
+    if (warp == 9) tc::tmem_alloc<512>(&bar->tmem_base);
+    if (warp == 8 && lane == 0) {
+        tc::tma_prefetch_desc(&tm_a1h); tc::tma_prefetch_desc(&tm_a1l); tc::tma_prefetch_desc(&tm_wh); tc::tma_prefetch_desc(&tm_wl);
+        if (p.K2) { tc::tma_prefetch_desc(&tm_a2h); tc::tma_prefetch_desc(&tm_a2l); }
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = bar->tmem_base;
+
+    // tile t -> (frame b, row tile, column tile); the column tile is the fastest index so neighbouring CTAs share A rows
+    auto decode = [&](int t, int &b, int &rt, int &ct) { ct = t % p.col_tiles; const int r = t / p.col_tiles; rt = r % p.row_tiles; b = r / p.row_tiles; };
+
+    if (warp == 8) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+                int b, rt, ct; decode(t, b, rt, ct);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
+                    uint8_t *st = smem + stage * STAGE_BYTES;
+                    const bool second = kb >= nkb1;
+                    const int ka = (second ? kb - nkb1 : kb) * BK;
+                    tc::mbar_wait(&bar->empty[stage], ph ^ 1);
+                    tc::mbar_arrive_expect_tx(&bar->full_hi[stage], HALF_BYTES);
+                    tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, b);
+                    tc::tma_load_3d(st + A_PLANE, &tm_wh, &bar->full_hi[stage], kb * BK, ct * BN, 0);
+                    tc::mbar_arrive_expect_tx(&bar->full_lo[stage], HALF_BYTES);
+                    tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, b);
+                    tc::tma_load_3d(st + HALF_BYTES + A_PLANE, &tm_wl, &bar->full_lo[stage], kb * BK, ct * BN, 0);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN);
+            const uint32_t base = tc::smem_u32(smem);
+            uint32_t it = 0;
+            int j = 0;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
+                const uint32_t as = j & 1, aph = (j >> 1) & 1;
+                tc::mbar_wait(&bar->acc_empty[as], aph ^ 1);
+                tc::tcgen05_fence_after();
+                const uint32_t d = tmem_base + as * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
+                    const uint32_t sb = base + stage * STAGE_BYTES;
+                    const uint64_t ah = tc::umma_desc_k128(sb), wh = tc::umma_desc_k128(sb + A_PLANE);
+                    const uint64_t al = tc::umma_desc_k128(sb + HALF_BYTES), wl = tc::umma_desc_k128(sb + HALF_BYTES + A_PLANE);
+                    tc::mbar_wait(&bar->full_hi[stage], ph);
+                    tc::tcgen05_fence_after();
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) tc::umma_f16(d, ah + 2 * k, wh + 2 * k, idesc, (kb | k) != 0);   // UMMA_K = 16 fp16 = 32 B
+                    tc::mbar_wait(&bar->full_lo[stage], ph);
+                    tc::tcgen05_fence_after();
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        tc::umma_f16(d, al + 2 * k, wh + 2 * k, idesc, 1);
+                        tc::umma_f16(d, ah + 2 * k, wl + 2 * k, idesc, 1);
+                    }
+                    tc::umma_commit(&bar->empty[stage]);          // frees the stage when these MMAs retire
+                }
+                tc::umma_commit(&bar->acc_full[as]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ================= epilogue (warps 0-7) =================
+        const int quad = warp & 3, half = warp >> 2;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+        int j = 0;
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
+            int b, rt, ct; decode(t, b, rt, ct);
+            const uint32_t as = j & 1, aph = (j >> 1) & 1;
+            const int row = rt * BM + quad * 32 + lane;
+            const bool row_ok = row < p.rows;
+            const long long grow = (long long)b * p.rows + (row_ok ? row : 0);
+            tc::mbar_wait(&bar->acc_full[as], aph);
+            tc::tcgen05_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                const int ccol = half * 128 + c * 32;             // column inside the tile
+                const int col0 = ct * BN + ccol;                  // output column
+                float v[32];
+                tc::tmem_ld_32x32(lane_base + as * BN + ccol, v);
+                tc::tmem_ld_wait();
+                if (c == 3) {                                     // this warp has drained its part of the accumulator
+                    tc::tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] *= kInvScale2;
+                if (p.flags & OPB_LIN_STATS) {
+                    float s[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) s[i] = v[i];     // rows past the end are exact zeros (TMA zero fill, no bias yet)
+                    const float cs = transpose_reduce_sum(s, lane);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) s[i] = v[i] * v[i];
+                    const float cq = transpose_reduce_sum(s, lane);
+                    p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + col0 + lane] = make_float2(cs, cq);
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float4 bq = *reinterpret_cast<const float4 *>(s_bias + col0 + 4 * q);
+                    v[4 * q] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
+                }
+                if ((p.flags & OPB_LIN_ELU1) && col0 < p.elu_cols) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] + 1.f : __expf(v[i]);   // elu(x)+1
+                }
+                if (row_ok) {
+                    if (p.C) {
+                        float4 *dst = reinterpret_cast<float4 *>(p.C + grow * p.Cout + col0);
+                        if (p.flags & OPB_LIN_RESIDUAL) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const float4 o = dst[q];
+                                v[4 * q] += o.x; v[4 * q + 1] += o.y; v[4 * q + 2] += o.z; v[4 * q + 3] += o.w;
+                            }
+                        }
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                    }
+                    if (p.Ch) store_planes32(v, p.Ch + grow * p.Cout + col0, p.Cl + grow * p.Cout + col0);
+                }
+            }
+        }
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 9) tc::tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace lintc
+}  // namespace opb

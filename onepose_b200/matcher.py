@@ -119,6 +119,9 @@ class GATsSuperGlue(nn.Module):
         self._ws = _Workspace()
         self._db_cache = {}          # static object DB in point-major layout
         self._trace = None           # debugging aid: list that receives (layer, x2, x3) clones
+        # projections on the tcgen05 tensor cores (split-precision planes); False = exact-fp32 CUDA-core kernels,
+        # kept as the on-device cross-check of the tensor-core path (tests), not as a fallback
+        self.use_tensor_cores = True
 
     # ------------------------------------------------------------------ weights in kernel layout
     def _weights_key(self):
@@ -152,6 +155,13 @@ class GATsSuperGlue(nn.Module):
                     W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias),
                     W1=f(mlp[3].weight[:, :, 0]), b1=f(mlp[3].bias)))
         self._packed = dict(layers=packed, Wf=f(self.final_proj.weight[:, :, 0]), bf=f(self.final_proj.bias))
+        # split-precision fp16 planes of every projection weight for the tcgen05 path (linear_tc.cuh)
+        with torch.cuda.device(device):
+            for lw in packed:
+                for k in ("Wq", "Wkv", "Wm", "W0", "W1"):
+                    if k in lw:
+                        lw[k + "_p"] = self._split_new(lw[k])
+            self._packed["Wf_p"] = self._split_new(self._packed["Wf"])
         self._packed_key = key
         self._db_cache.clear()       # cached W-transformed leaves depend on the weights
         return self._packed
@@ -166,6 +176,21 @@ class GATsSuperGlue(nn.Module):
         bstride = x.stride(0) if x.shape[0] > 1 else 0
         call("op_channel_major_to_point_major", ptr(x), ptr(out), out.shape[0], C, N, bstride, stream_ptr())
         return out
+
+    @staticmethod
+    def _split(x, hi, lo):
+        """fp32 tensor -> (hi, lo) fp16 planes of 64*x (op_split_planes)."""
+        call("op_split_planes", ptr(x), ptr(hi), ptr(lo), x.numel(), stream_ptr())
+        return hi, lo
+
+    @classmethod
+    def _split_new(cls, x):
+        x = x.contiguous()
+        return cls._split(x, torch.empty(x.shape, dtype=torch.float16, device=x.device),
+                          torch.empty(x.shape, dtype=torch.float16, device=x.device))
+
+    def _planes(self, name, shape, dev):
+        return (self._ws.get(name + ".hi", shape, torch.float16, dev), self._ws.get(name + ".lo", shape, torch.float16, dev))
 
     def _static_db(self, d3, lv, L):
         """Point-major copy of the object DB, cached while the caller keeps handing the same tensors."""
@@ -222,6 +247,49 @@ class GATsSuperGlue(nn.Module):
         rstd = self._ws.get("rstd", (B, 2 * _D), torch.float32, dev)
         call("op_instnorm_finalize", ptr(stats), B, tiles, 2 * _D, N, 1e-5, ptr(mean), ptr(rstd), stream_ptr())
         self._linear(h, lw["W1"], lw["b1"], x, B, N, flags=2 | 8, mean=mean, rstd=rstd, tag="mlp1")   # NORM_RELU in, RESIDUAL out
+
+    # ------------------------------------------------------------------ tcgen05 launchers (linear_tc.cuh)
+    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, tag=""):
+        """A1/A2/W/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp."""
+        K1 = A1[0].shape[-1]
+        K2 = 0 if A2 is None else A2[0].shape[-1]
+        Cout = W[0].shape[0]
+        timeline.work = 2.0 * B * rows * (K1 + K2) * Cout
+        call("op_linear_tc", ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
+             ptr(W[0]), ptr(W[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
+             B, rows, Cout, flags, elu_cols, ptr(stats), stream_ptr(), tag=tag)
+
+    def _kv_tc(self, src_p, B, M, lw, tag):
+        dev = src_p[0].device
+        kv = self._ws.get(f"kv{M}", (B, M, 2 * _D), torch.float32, dev)
+        self._linear_tc(src_p, lw["Wkv_p"], lw["bkv"], B, M, C=kv, flags=1, elu_cols=_D, tag="kv")
+        KV = self._ws.get("KV" + tag, (B, _HEADS, 64, 64), torch.float32, dev)
+        Ks = self._ws.get("Ks" + tag, (B, _HEADS, 64), torch.float32, dev)
+        nbytes = lib.op_kv_reduce_workspace_bytes(B, M)
+        w = self._ws.get(f"kvws{M}", (nbytes,), torch.uint8, dev)
+        call("op_kv_reduce", ptr(kv), ptr(KV), ptr(Ks), B, M, ptr(w), nbytes, stream_ptr())
+        return KV, Ks
+
+    def _propagate_tc(self, x, x_p, B, N, M, KV, Ks, lw):
+        """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place."""
+        dev = x.device
+        q = self._ws.get(f"q{N}", (B, N, _D), torch.float32, dev)
+        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, C=q, flags=1, elu_cols=_D, tag="q")
+        att_p = self._planes(f"att{N}", (B, N, _D), dev)
+        call("op_attn_apply_planes", ptr(q), ptr(KV), ptr(Ks), ptr(att_p[0]), ptr(att_p[1]), B, N, M, stream_ptr())
+        msg_p = self._planes(f"msg{N}", (B, N, _D), dev)
+        self._linear_tc(att_p, lw["Wm_p"], lw["bm"], B, N, Cp=msg_p, tag="merge")
+        h = self._ws.get(f"h{N}", (B, N, 2 * _D), torch.float32, dev)
+        parts = lib.op_linear_tc_stat_parts(N)
+        stats = self._ws.get(f"tcstats{N}", (B, parts, 2 * _D, 2), torch.float32, dev)
+        self._linear_tc(x_p, lw["W0_p"], lw["b0"], B, N, A2=msg_p, C=h, flags=4, stats=stats, tag="mlp0")
+        mean = self._ws.get("mean", (B, 2 * _D), torch.float32, dev)
+        rstd = self._ws.get("rstd", (B, 2 * _D), torch.float32, dev)
+        call("op_instnorm_finalize_tc", ptr(stats), ptr(lw["b0"]), B, parts, 2 * _D, N, 1e-5, ptr(mean), ptr(rstd), stream_ptr())
+        hn_p = self._planes(f"hn{N}", (B, N, 2 * _D), dev)
+        timeline.work = 8.0 * B * N * 2 * _D                                    # bytes: fp32 in, two fp16 planes out
+        call("op_norm_relu_split", ptr(h), ptr(mean), ptr(rstd), ptr(hn_p[0]), ptr(hn_p[1]), B, N, 2 * _D, stream_ptr())
+        self._linear_tc(hn_p, lw["W1_p"], lw["b1"], B, N, C=x, Cp=x_p, flags=2, tag="mlp1")     # RESIDUAL, in place
 
     def _gats(self, x3, db, B, N3, L, lw, li):
         hp = self.hparams
@@ -289,32 +357,48 @@ class GATsSuperGlue(nn.Module):
         x3 = self._ws.get("x3", (B, N3, _D), torch.float32, dev)
         x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
 
+        tcp = self.use_tensor_cores
+        if tcp:
+            x2_p = self._split(x2, *self._planes("x2", (B, N2, _D), dev))
+            x3_p = self._planes("x3", (B, N3, _D), dev)          # filled after the first GATs layer
         for li, lw in enumerate(pk["layers"]):
             kind = lw["kind"]
             if kind == "GATs":
                 self._gats(x3, db, B, N3, L, lw, li)
+                if tcp:
+                    self._split(x3, *x3_p)
                 if self._trace is not None:
                     self._trace.append((li, x2.clone(), x3.clone()))
                 continue
             # both deltas of a layer are computed from the layer's input (:77-78,82-83): reduce the source
             # side of both calls first, then update the two streams in place.
+            s2, s3 = (x2_p, x3_p) if tcp else (x2, x3)
+            kvf = self._kv_tc if tcp else self._kv
             if kind == "cross":
-                KVa, Ksa = self._kv(x3, B, N3, lw, "a")       # desc2d attends to desc3d
-                KVb, Ksb = self._kv(x2, B, N2, lw, "b")       # desc3d attends to desc2d
+                KVa, Ksa = kvf(s3, B, N3, lw, "a")       # desc2d attends to desc3d
+                KVb, Ksb = kvf(s2, B, N2, lw, "b")       # desc3d attends to desc2d
                 Ma, Mb = N3, N2
             else:
-                KVa, Ksa = self._kv(x2, B, N2, lw, "a")
-                KVb, Ksb = self._kv(x3, B, N3, lw, "b")
+                KVa, Ksa = kvf(s2, B, N2, lw, "a")
+                KVb, Ksb = kvf(s3, B, N3, lw, "b")
                 Ma, Mb = N2, N3
-            self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
-            self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
+            if tcp:
+                self._propagate_tc(x2, x2_p, B, N2, Ma, KVa, Ksa, lw)
+                self._propagate_tc(x3, x3_p, B, N3, Mb, KVb, Ksb, lw)
+            else:
+                self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
+                self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
             if self._trace is not None:
                 self._trace.append((li, x2.clone(), x3.clone()))
 
         m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
         m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
-        self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")               # final_proj, :241
-        self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
+        if tcp:
+            self._linear_tc(x2_p, pk["Wf_p"], pk["bf"], B, N2, C=m2, tag="final")          # final_proj, :241
+            self._linear_tc(x3_p, pk["Wf_p"], pk["bf"], B, N3, C=m3, tag="final")
+        else:
+            self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")
+            self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
         call("op_l2_normalize_rows", ptr(m2), ptr(m2), B * N2, _D, stream_ptr())
         call("op_l2_normalize_rows", ptr(m3), ptr(m3), B * N3, _D, stream_ptr())
 

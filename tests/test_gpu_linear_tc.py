@@ -1,0 +1,120 @@
+"""GPU parity tests of the tcgen05 split-precision projections (op_linear_tc and its plane producers) against
+float64 restatements of the reference ops (Conv1d k=1, elu+1, InstanceNorm1d+ReLU, residual;
+GATs_SuperGlue.py:88-147), and of the whole matcher against the exact-fp32 CUDA-core path."""
+import numpy as np
+import pytest
+import torch
+
+from onepose_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _planes(x):
+    from onepose_b200._lib import call, ptr, stream_ptr
+    x = x.contiguous()
+    hi = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+    lo = torch.empty_like(hi)
+    call("op_split_planes", ptr(x), ptr(hi), ptr(lo), x.numel(), stream_ptr())
+    return hi, lo
+
+
+def _unsplit(p):
+    return (p[0].double() + p[1].double()) / 64.0
+
+
+def _linear_tc(A1, W, bias, *, A2=None, want_c=True, want_planes=False, flags=0, elu_cols=0, C_init=None):
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    B, rows, K1 = A1.shape
+    Cout = W.shape[0]
+    a1 = _planes(A1); w = _planes(W)
+    a2 = _planes(A2) if A2 is not None else None
+    C = (C_init.clone() if C_init is not None else torch.full((B, rows, Cout), float("nan"), device="cuda")) if want_c else None
+    Cp = (torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda"), torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda")) if want_planes else None
+    parts = lib.op_linear_tc_stat_parts(rows)
+    stats = torch.full((B, parts, Cout, 2), float("nan"), device="cuda") if flags & 4 else None
+    call("op_linear_tc", ptr(a1[0]), ptr(a1[1]), K1, ptr(a2[0]) if a2 else None, ptr(a2[1]) if a2 else None,
+         0 if A2 is None else A2.shape[2], ptr(w[0]), ptr(w[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None,
+         ptr(Cp[1]) if Cp else None, B, rows, Cout, flags, elu_cols, ptr(stats), stream_ptr())
+    torch.cuda.synchronize()
+    return C, Cp, stats
+
+
+def _rel(x, ref):
+    return ((x.double() - ref).abs().max() / ref.abs().max()).item()
+
+
+def test_split_planes_roundtrip():
+    g = torch.Generator().manual_seed(1)
+    x = (torch.randn(4096, generator=g) * torch.logspace(-4, 2, 4096)).cuda()
+    back = _unsplit(_planes(x))
+    err = (back - x.double()).abs()
+    assert float((err / x.double().abs().clamp_min(1e-3)).max()) < 2e-6        # 22 significant bits above fp16's subnormal floor
+
+
+@pytest.mark.parametrize("shape", [(1, 128, 256, 256), (2, 300, 256, 512), (3, 77, 512, 256), (1, 2048, 256, 256), (2, 1000, 512, 512)])
+def test_linear_tc_plain(shape):
+    B, rows, K, Cout = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    A = torch.randn(B, rows, K, generator=g).cuda() * 0.3
+    W = (torch.randn(Cout, K, generator=g) / K ** 0.5).cuda()
+    bias = torch.randn(Cout, generator=g).cuda() * 0.1
+    ref = A.double() @ W.double().t() + bias.double()
+    C, Cp, _ = _linear_tc(A, W, bias, want_planes=True)
+    assert _rel(C, ref) < 5e-6
+    assert _rel(_unsplit(Cp), ref) < 5e-6
+    C2, _, _ = _linear_tc(A, W, bias)
+    assert torch.equal(C, C2)                                                   # deterministic
+
+
+def test_linear_tc_two_sources_elu_stats_residual():
+    B, rows = 2, 333
+    g = torch.Generator().manual_seed(5)
+    A1 = torch.randn(B, rows, 256, generator=g).cuda() * 0.2
+    A2 = torch.randn(B, rows, 256, generator=g).cuda() * 0.5
+    W = (torch.randn(512, 512, generator=g) / 512 ** 0.5).cuda()
+    bias = torch.randn(512, generator=g).cuda()
+    lin = torch.cat([A1, A2], 2).double() @ W.double().t()
+    # concatenated K + InstanceNorm statistics (MLP layer 0, :135-147)
+    C, _, stats = _linear_tc(A1, W, bias, A2=A2, flags=4)
+    assert _rel(C, lin + bias.double()) < 5e-6
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    mean = torch.empty(B, 512, device="cuda"); rstd = torch.empty(B, 512, device="cuda")
+    call("op_instnorm_finalize_tc", ptr(stats), ptr(bias), B, lib.op_linear_tc_stat_parts(rows), 512, rows, 1e-5, ptr(mean), ptr(rstd), stream_ptr())
+    h = lin + bias.double()
+    np.testing.assert_allclose(mean.cpu().numpy(), h.mean(1).cpu().numpy(), rtol=0, atol=2e-6)
+    np.testing.assert_allclose(rstd.cpu().numpy(), (1.0 / torch.sqrt(h.var(1, unbiased=False) + 1e-5)).cpu().numpy(), rtol=3e-6)
+    # InstanceNorm + ReLU producer of the next GEMM's planes
+    hn = (torch.zeros(B, rows, 512, dtype=torch.float16, device="cuda"), torch.zeros(B, rows, 512, dtype=torch.float16, device="cuda"))
+    call("op_norm_relu_split", ptr(C), ptr(mean), ptr(rstd), ptr(hn[0]), ptr(hn[1]), B, rows, 512, stream_ptr())
+    ref_n = torch.relu((h - h.mean(1, keepdim=True)) / torch.sqrt(h.var(1, unbiased=False, keepdim=True) + 1e-5))
+    assert float((_unsplit(hn) - ref_n).abs().max()) < 2e-5
+    # elu+1 on the first 256 output columns only (K | V projection, :90-91)
+    Ce, _, _ = _linear_tc(A1, W[:, :256].contiguous(), bias, flags=1, elu_cols=256)
+    l2 = A1.double() @ W[:, :256].double().t() + bias.double()
+    ref_e = torch.cat([torch.nn.functional.elu(l2[..., :256]) + 1, l2[..., 256:]], 2)
+    assert _rel(Ce, ref_e) < 5e-6
+    # residual add in place (:78,83)
+    x0 = torch.randn(B, rows, 512, generator=g).cuda()
+    Cr, Crp, _ = _linear_tc(A1, W[:, :256].contiguous(), bias, flags=2, C_init=x0, want_planes=True)
+    assert _rel(Cr, x0.double() + l2) < 5e-6
+    assert _rel(_unsplit(Crp), x0.double() + l2) < 5e-6
+
+
+@pytest.mark.parametrize("damped", [False, True])
+def test_matcher_tensor_core_path_vs_cuda_core_path(damped):
+    from onepose_b200.matcher import GATsSuperGlue
+    from tests import helpers
+    hp = dict(synth.DEFAULT_HPARAMS); hp["match_threshold"] = 0.0 if not damped else 0.2
+    obj = synth.make_object(1, 700, 8)
+    frames = [synth.make_frame(obj, f, 450) for f in range(2)]
+    data = {k: v.cuda() for k, v in synth.pack_batch(obj, frames).items()}
+    m = GATsSuperGlue(hp).cuda().eval()
+    m.load_state_dict(synth.make_weights(0, damped=damped), strict=True)
+    pred_tc, conf_tc = m(data)
+    conf_tc = conf_tc.clone(); m0_tc = pred_tc["matches0_batched"].clone()
+    m.use_tensor_cores = False
+    pred_cc, conf_cc = m(data)
+    assert helpers.conf_rel_err(conf_tc.cpu(), conf_cc.cpu()) < helpers.CONF_RTOL
+    for b in range(2):
+        helpers.assert_matches_equal_off_ties(m0_tc[b].cpu(), pred_cc["matches0_batched"][b].cpu(), conf_cc[b].cpu(), axis=2)
