@@ -85,7 +85,8 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
             const __grid_constant__ CUtensorMap tm_wh, const __grid_constant__ CUtensorMap tm_wl, const Params p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment (SWIZZLE_128B) by an offset on the shared array, so accesses stay in the shared address space (LDS/STS)
+    uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     float *s_bias = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES);
     Barriers *bar = reinterpret_cast<Barriers *>(smem + STAGES * STAGE_BYTES + BIAS_FLOATS * 4);
 

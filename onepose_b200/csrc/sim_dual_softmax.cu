@@ -176,36 +176,39 @@ k_sim_pass(const SimParams p) {
     }
 }
 
-// inv[b][i] = 1 / sum_t part[b][t][i]
-__global__ void k_sim_finalize_sums(const float *__restrict__ part, int tiles, int n, float *__restrict__ inv) {
+// inv[b][i] = 1 / sum_t part[b][t][i]   (as_log2: log2 of it, for the exponent-folded tcgen05 pass 2)
+__global__ void k_sim_finalize_sums(const float *__restrict__ part, int tiles, int n, float *__restrict__ inv, int as_log2) {
     const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float s = 0.f;
     for (int t = 0; t < tiles; ++t) s += part[((long long)b * tiles + t) * n + i];
-    inv[(long long)b * n + i] = 1.f / s;
+    inv[(long long)b * n + i] = as_log2 ? -log2f(s) : 1.f / s;
 }
 
-__global__ void k_sim_finalize_max(const unsigned long long *__restrict__ part, int tiles, int n,
+__global__ void k_sim_finalize_max(const unsigned long long *__restrict__ part, int tiles, int n, int n_other,
                                    int *__restrict__ idx, float *__restrict__ val) {
     const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     unsigned long long k = 0ull;
     for (int t = 0; t < tiles; ++t) { const unsigned long long v = part[((long long)b * tiles + t) * n + i]; k = v > k ? v : k; }
-    idx[(long long)b * n + i] = (int)(0xffffffffu - (unsigned)(k & 0xffffffffull));
+    // an all-zero row / column of conf can select a padding slot of the last tile: every index is then a maximum, clamp it
+    const int id = (int)(0xffffffffu - (unsigned)(k & 0xffffffffull));
+    idx[(long long)b * n + i] = id < n_other ? id : n_other - 1;
     val[(long long)b * n + i] = __uint_as_float((unsigned)(k >> 32));
 }
 
 // mutual nearest neighbour + threshold, GATs_SuperGlue.py:256-267
-__global__ void k_mutual_select(const int *__restrict__ idx0, const float *__restrict__ val0, const int *__restrict__ idx1,
+// The score of a pair is read back from conf itself (exact), the packed keys only select.
+__global__ void k_mutual_select(const int *__restrict__ idx0, const float *__restrict__ conf, const int *__restrict__ idx1,
                                 int N2, int N3, float thr, int64_t *__restrict__ matches0, int64_t *__restrict__ matches1,
                                 float *__restrict__ scores0, float *__restrict__ scores1) {
     const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
     const int *i0 = idx0 + (long long)b * N2, *i1 = idx1 + (long long)b * N3;
-    const float *v0 = val0 + (long long)b * N2;
+    const float *cb = conf + (long long)b * N2 * N3;
     if (i < N2) {
         const int j = i0[i];
         const bool mutual = i1[j] == i;
-        const float ms = mutual ? v0[i] : 0.f;
+        const float ms = mutual ? cb[(long long)i * N3 + j] : 0.f;
         scores0[(long long)b * N2 + i] = ms;
         matches0[(long long)b * N2 + i] = (mutual && ms > thr) ? (int64_t)j : (int64_t)-1;
     }
@@ -213,7 +216,7 @@ __global__ void k_mutual_select(const int *__restrict__ idx0, const float *__res
         const int n = i1[i];                       // best query for this 3D point
         const bool mutual1 = i0[n] == i;
         const bool mutual0_n = i1[i0[n]] == n;
-        const float ms0_n = mutual0_n ? v0[n] : 0.f;
+        const float ms0_n = mutual0_n ? cb[(long long)n * N3 + i0[n]] : 0.f;
         scores1[(long long)b * N3 + i] = mutual1 ? ms0_n : 0.f;
         const bool valid0_n = mutual0_n && ms0_n > thr;
         matches1[(long long)b * N3 + i] = (mutual1 && valid0_n) ? (int64_t)n : (int64_t)-1;
@@ -233,9 +236,9 @@ static SimWorkspace carve(void *base, int B, int N2, int N3) {
     SimWorkspace w;
     size_t off = 0;
     auto take = [&](size_t bytes) { void *p = base ? (char *)base + off : nullptr; off += align_up(bytes, 256); return p; };
-    w.rowmax_part = (unsigned long long *)take((size_t)B * tn * N2 * 8);
+    w.rowmax_part = (unsigned long long *)take((size_t)B * tn * 2 * N2 * 8);   // x2: the tcgen05 epilogue splits a tile's columns over two warps
     w.colmax_part = (unsigned long long *)take((size_t)B * tm * N3 * 8);
-    w.rowsum_part = (float *)take((size_t)B * tn * N2 * 4);
+    w.rowsum_part = (float *)take((size_t)B * tn * 2 * N2 * 4);
     w.colsum_part = (float *)take((size_t)B * tm * N3 * 4);
     w.invR = (float *)take((size_t)B * N2 * 4);
     w.invC = (float *)take((size_t)B * N3 * 4);
@@ -279,8 +282,8 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         dim3 grid(p.tiles_n, p.tiles_m, B);
         k_sim_pass<1><<<grid, 256, 0, st>>>(p);
         OPB_CHECK_LAUNCH();
-        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, row_parts, N2, w.invR);
-        k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC);
+        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, row_parts, N2, w.invR, 0);
+        k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC, 0);
         OPB_CHECK_LAUNCH();
         k_sim_pass<2><<<grid, 256, 0, st>>>(p);
         OPB_CHECK_LAUNCH();
@@ -301,11 +304,12 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         simtc::Params q{};
         q.N2 = N2; q.N3 = N3; q.tiles_n = p.tiles_n; q.tiles_per_split = ceil_div(p.tiles_n, splits);
         splits = ceil_div(p.tiles_n, q.tiles_per_split);
-        row_parts = splits;
+        row_parts = splits * 2;
         const double log2e = 1.4426950408889634;
         q.c1 = (float)(log2e / ((double)scale_factor * simtc::kOperandScale * simtc::kOperandScale));
         q.c0 = (float)(log2e / (double)scale_factor);
-        q.rowsum_part = w.rowsum_part; q.colsum_part = w.colsum_part; q.invR = w.invR; q.invC = w.invC;
+        q.c2 = 2.f * q.c1;
+        q.rowsum_part = w.rowsum_part; q.colsum_part = w.colsum_part; q.lgR = w.invR; q.lgC = w.invC;
         q.rowmax_part = w.rowmax_part; q.colmax_part = w.colmax_part; q.conf = conf;
         static bool configured = false;
         if (!configured) {
@@ -314,19 +318,19 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
             configured = true;
         }
         dim3 grid(splits, p.tiles_m, B);
-        simtc::k_sim_tc<1><<<grid, 192, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
+        simtc::k_sim_tc<1><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
         OPB_CHECK_LAUNCH();
-        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n, N2, w.invR);
-        k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC);
+        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n * 2, N2, w.invR, 1);
+        k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC, 1);
         OPB_CHECK_LAUNCH();
-        simtc::k_sim_tc<2><<<grid, 192, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
+        simtc::k_sim_tc<2><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
         OPB_CHECK_LAUNCH();
     }
-    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, w.idx0, w.val0);
-    k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, w.idx1, w.val1);
+    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, N3, w.idx0, w.val0);
+    k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, N2, w.idx1, w.val1);
     OPB_CHECK_LAUNCH();
     const int nmax = N2 > N3 ? N2 : N3;
-    k_mutual_select<<<dim3(ceil_div(nmax, 256), B), 256, 0, st>>>(w.idx0, w.val0, w.idx1, N2, N3, match_threshold,
+    k_mutual_select<<<dim3(ceil_div(nmax, 256), B), 256, 0, st>>>(w.idx0, conf, w.idx1, N2, N3, match_threshold,
                                                                   matches0, matches1, scores0, scores1);
     OPB_CHECK_LAUNCH();
     return OPB_OK;

@@ -22,14 +22,16 @@ constexpr int TILE_BYTES = 128 * 128;                 // 128 rows x 64 fp16
 constexpr int A_BYTES = 2 * NKB * TILE_BYTES;         // 131072
 constexpr int RING_BYTES = UNITS * TILE_BYTES;        // 81920
 constexpr int SCRATCH_BYTES = 2 * 4 * BN * 8;         // double-buffered [4 warps][128] u64
-constexpr int SMEM_BYTES = A_BYTES + RING_BYTES + SCRATCH_BYTES + 256 + 1024;   // + barriers + alignment slack
+constexpr int LGC_BYTES = 2 * BN * 4;                 // double-buffered column terms of the current tile
+constexpr int SMEM_BYTES = A_BYTES + RING_BYTES + SCRATCH_BYTES + LGC_BYTES + 256 + 1024;   // + barriers + alignment slack
 constexpr float kOperandScale = 64.f;                 // unit-vector components are scaled into fp16's normal range
 
 struct Params {
     int N2, N3, tiles_n, tiles_per_split;
     float c1, c0;                                     // e = exp2(acc * c1 - c0)
     float *rowsum_part, *colsum_part;                 // [B][tiles_n][N2] (per column tile), [B][tiles_m][N3]
-    const float *invR, *invC;
+    float c2;                                         // 2*c1
+    const float *lgR, *lgC;                           // log2(1/R_n), log2(1/C_m)
     unsigned long long *rowmax_part, *colmax_part;
     float *conf;
 };
@@ -39,7 +41,7 @@ struct Barriers {
     uint32_t tmem_base;
 };
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // sum over the 32 lanes of v[i]; lane L ends up with the total of element L in v[0]
 __device__ __forceinline__ float transpose_reduce_sum(float *v, int lane) {
@@ -71,14 +73,16 @@ __device__ __forceinline__ unsigned long long transpose_reduce_max(unsigned long
 }
 
 template <int PASS>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l,
          const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l, const Params p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment (SWIZZLE_128B) by an offset on the shared array, so accesses stay in the shared address space (LDS/STS)
+    uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t *sA = smem, *sB = smem + A_BYTES;
     unsigned long long *scratch = reinterpret_cast<unsigned long long *>(smem + A_BYTES + RING_BYTES);
-    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + SCRATCH_BYTES);
+    float *s_lgc = reinterpret_cast<float *>(smem + A_BYTES + RING_BYTES + SCRATCH_BYTES);
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + SCRATCH_BYTES + LGC_BYTES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int split = blockIdx.x, row_tile = blockIdx.y, b = blockIdx.z;
@@ -90,11 +94,11 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     if (threadIdx.x == 0) {
         tc::mbar_init(&bar->a_full, 1);
         for (int i = 0; i < UNITS; ++i) { tc::mbar_init(&bar->b_full[i], 1); tc::mbar_init(&bar->b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], 128); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], 8); }
         tc::fence_barrier_init();
     }
-    if (warp == 5) tc::tmem_alloc<256>(&bar->tmem_base);
-    if (warp == 4 && lane == 0) {
+    if (warp == 9) tc::tmem_alloc<256>(&bar->tmem_base);
+    if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_m2h); tc::tma_prefetch_desc(&tm_m2l); tc::tma_prefetch_desc(&tm_m3h); tc::tma_prefetch_desc(&tm_m3l);
     }
     tc::tcgen05_fence_before();
@@ -102,7 +106,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = bar->tmem_base;
 
-    if (warp == 4) {
+    if (warp == 8) {
         // ================= TMA producer =================
         if (lane == 0) {
             tc::mbar_arrive_expect_tx(&bar->a_full, A_BYTES);
@@ -120,7 +124,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                     }
         }
         __syncwarp();
-    } else if (warp == 5) {
+    } else if (warp == 9) {
         // ================= MMA issuer =================
         if (lane == 0) {
             constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN);
@@ -158,88 +162,125 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         }
         __syncwarp();
     } else {
-        // ================= epilogue (warps 0-3, one query row per thread) =================
-        const int row = m0 + warp * 32 + lane;
+        // ================= epilogue (warps 0-7): TMEM lane quadrant = warp % 4 (thread = query row), column half = warp / 4 ===
+        const int quad = warp & 3, half = warp >> 2;
+        const int row = m0 + quad * 32 + lane;
         const bool row_ok = row < p.N2;
-        const uint32_t lane_base = tmem_base + ((uint32_t)(warp * 32) << 16);
-        float row_sum = 0.f;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
         unsigned long long row_key = 0ull;
-        float ir = 0.f;
-        if (PASS == 2 && row_ok) ir = p.invR[(long long)b * p.N2 + row];
+        // PASS 2: conf = exp2(2*c1*acc - 2*c0 + log2(1/R_n) + log2(1/C_m)); rows / columns past the end carry -inf => conf = +0
+        float rowc = 0.f;
+        if (PASS == 2) rowc = row_ok ? p.lgR[(long long)b * p.N2 + row] - 2.f * p.c0 : -INFINITY;
         float *crow = PASS == 2 ? p.conf + ((long long)b * p.N2 + (row_ok ? row : 0)) * p.N3 : nullptr;
         const bool vec_ok = (p.N3 & 3) == 0;
+        const uint32_t rinv = 127u - (uint32_t)(quad * 32 + lane);          // inverted row index inside the tile
+        // fold of the four quadrants' column partials of tile (tt, buffer jj), thread = column, fixed order
+        auto fold_columns = [&](int tt, int jj) {
+            const unsigned long long *scr = scratch + (jj & 1) * 4 * BN;
+            const int tid = threadIdx.x, col = tt * BN + tid;
+            if (tid < BN && col < p.N3) {
+                if (PASS == 1) {
+                    const float *sf = reinterpret_cast<const float *>(scr);
+                    p.colsum_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] = ((sf[tid] + sf[BN + tid]) + sf[2 * BN + tid]) + sf[3 * BN + tid];
+                } else {
+                    const uint32_t *su = reinterpret_cast<const uint32_t *>(scr);
+                    uint32_t k = su[tid];
+#pragma unroll
+                    for (int w = 1; w < 4; ++w) k = su[w * BN + tid] > k ? su[w * BN + tid] : k;
+                    p.colmax_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] =
+                        ((unsigned long long)(k & 0xFFFFFF80u) << 32) | (unsigned long long)(0xffffffffu - (unsigned)(m0 + 127 - (int)(k & 127u)));
+                }
+            }
+        };
+        auto load_lgc = [&](int tt) -> float {           // column term of tile tt for this thread (threads 0..127)
+            const int col = tt * BN + (int)threadIdx.x;
+            return (PASS == 2 && threadIdx.x < BN && tt < t1 && col < p.N3) ? p.lgC[(long long)b * p.N3 + col] : -INFINITY;
+        };
+        float lg_next = load_lgc(t0);
         int j = 0;
         for (int t = t0; t < t1; ++t, ++j) {
             const uint32_t as = j & 1, aph = (j >> 1) & 1;
             unsigned long long *scr = scratch + (j & 1) * 4 * BN;
+            float *lgc = s_lgc + (j & 1) * BN;
+            if (PASS == 2 && threadIdx.x < BN) lgc[threadIdx.x] = lg_next;
+            epi_bar_sync();                       // one barrier per tile: lgc(j) is visible and the partials of tile j-1 are complete
+            if (j > 0) fold_columns(t - 1, j - 1);
+            lg_next = load_lgc(t + 1);            // in flight during this tile
             tc::mbar_wait(&bar->acc_full[as], aph);
             tc::tcgen05_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                float v[32];
-                tc::tmem_ld_32x32(lane_base + as * BN + c * 32, v);
-                tc::tmem_ld_wait();
-                if (c == 3) { tc::tcgen05_fence_before(); tc::mbar_arrive(&bar->acc_empty[as]); }   // TMEM buffer is free again
-                const int col0 = t * BN + c * 32;
+            // both 32-column chunks of this warp are fetched up front, then the accumulator is handed back to the MMA warp
+            float v[2][32];
+            tc::tmem_ld_32x32(lane_base + as * BN + half * 64, v[0]);
+            tc::tmem_ld_32x32(lane_base + as * BN + half * 64 + 32, v[1]);
+            tc::tmem_ld_wait();
+            tc::tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
+            uint32_t tile_rk = 0u;
+            float row_sum = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float e = exp2f(fmaf(v[i], p.c1, -p.c0));
-                    v[i] = (row_ok && col0 + i < p.N3) ? e : 0.f;
-                }
+            for (int cc = 0; cc < 2; ++cc) {
+                const int ccol = half * 64 + cc * 32;          // column inside the tile
+                const int col0 = t * BN + ccol;
+                float *vv = v[cc];
                 if (PASS == 1) {
-                    if (c == 0) row_sum = 0.f;               // per-tile partial: the fold over tiles is split-invariant
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) row_sum += v[i];
-                    if (c == 3 && row_ok) p.rowsum_part[((long long)b * p.tiles_n + t) * p.N2 + row] = row_sum;
-                    const float cs = transpose_reduce_sum(v, lane);
-                    reinterpret_cast<float *>(scr)[warp * BN + c * 32 + lane] = cs;
-                } else {
-                    unsigned long long keys[32];
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        const int col = col0 + i;
-                        const float ic = col < p.N3 ? __ldg(p.invC + (long long)b * p.N3 + col) : 0.f;
-                        const float cf = (v[i] * ic) * (v[i] * ir);
-                        v[i] = cf;
-                        const bool ok = row_ok && col < p.N3;
-                        const unsigned long long kr = ok ? (((unsigned long long)__float_as_uint(cf) << 32) | (0xffffffffu - (unsigned)col)) : 0ull;
-                        row_key = kr > row_key ? kr : row_key;
-                        keys[i] = ok ? (((unsigned long long)__float_as_uint(cf) << 32) | (0xffffffffu - (unsigned)row)) : 0ull;
+                        const float e = tc::ex2(fmaf(vv[i], p.c1, -p.c0));
+                        vv[i] = (row_ok && col0 + i < p.N3) ? e : 0.f;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) row_sum += vv[i];
+                    const float cs = transpose_reduce_sum(vv, lane);
+                    reinterpret_cast<float *>(scr)[quad * BN + ccol + lane] = cs;
+                } else {
+                    // 32-bit selection keys: conf bits with the low 7 mantissa bits replaced by the inverted in-tile index
+                    // (ties within 2^-16 relative resolve to the smaller index; the exact score is read back from conf).
+                    uint32_t ck = 0u;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const float4 l4 = *reinterpret_cast<const float4 *>(lgc + ccol + 4 * q);
+                        const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int i = 4 * q + e;
+                            const float cf = tc::ex2(fmaf(vv[i], p.c2, rowc + l[e]));
+                            vv[i] = cf;
+                            const uint32_t bits = __float_as_uint(cf) & 0xFFFFFF80u;
+                            const uint32_t kr = bits | (uint32_t)(127 - (ccol + i));
+                            tile_rk = kr > tile_rk ? kr : tile_rk;
+                            const uint32_t r = __reduce_max_sync(0xffffffffu, bits | rinv);
+                            ck = lane == i ? r : ck;
+                        }
                     }
                     if (row_ok) {
                         if (vec_ok && col0 + 31 < p.N3) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q)
-                                *reinterpret_cast<float4 *>(crow + col0 + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                                *reinterpret_cast<float4 *>(crow + col0 + 4 * q) = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
                         } else {
-                            for (int i = 0; i < 32; ++i) if (col0 + i < p.N3) crow[col0 + i] = v[i];
+                            for (int i = 0; i < 32; ++i) if (col0 + i < p.N3) crow[col0 + i] = vv[i];
                         }
                     }
-                    const unsigned long long ck = transpose_reduce_max(keys, lane);
-                    scr[warp * BN + c * 32 + lane] = ck;
+                    reinterpret_cast<uint32_t *>(scr)[quad * BN + ccol + lane] = ck;
                 }
             }
-            epi_bar_sync();
-            {   // fold the four warps' column partials in a fixed order: thread = column
-                const int tid = threadIdx.x, col = t * BN + tid;
-                if (col < p.N3) {
-                    if (PASS == 1) {
-                        const float *s = reinterpret_cast<const float *>(scr);
-                        p.colsum_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] = ((s[tid] + s[BN + tid]) + s[2 * BN + tid]) + s[3 * BN + tid];
-                    } else {
-                        unsigned long long k = scr[tid];
-#pragma unroll
-                        for (int w = 1; w < 4; ++w) k = scr[w * BN + tid] > k ? scr[w * BN + tid] : k;
-                        p.colmax_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] = k;
-                    }
-                }
+            if (PASS == 1) {
+                // per-(tile, column half) partial: the fold over partials is split-invariant
+                if (row_ok) p.rowsum_part[((long long)b * (p.tiles_n * 2) + t * 2 + half) * p.N2 + row] = row_sum;
+            } else {   // tile key -> global 64-bit key (value bits high, inverted global column low)
+                const unsigned long long k64 = ((unsigned long long)(tile_rk & 0xFFFFFF80u) << 32) |
+                                               (unsigned long long)(0xffffffffu - (unsigned)(t * BN + 127 - (int)(tile_rk & 127u)));
+                row_key = k64 > row_key ? k64 : row_key;
             }
         }
-        if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * gridDim.x + split) * p.N2 + row] = row_key;
+        epi_bar_sync();
+        fold_columns(t1 - 1, j - 1);
+        if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * (gridDim.x * 2) + split * 2 + half) * p.N2 + row] = row_key;
     }
     tc::tcgen05_fence_before();
     __syncthreads();
-    if (warp == 5) tc::tmem_dealloc<256>(tmem_base);
+    if (warp == 9) tc::tmem_dealloc<256>(tmem_base);
 }
 
 // fp32 rows -> scaled fp16 hi / lo planes

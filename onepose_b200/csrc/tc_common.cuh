@@ -127,6 +127,12 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+__device__ __forceinline__ float ex2(float x) {      // MUFU.EX2: 2 ulp, ex2(-inf) = +0, results below 2^-126 flush to 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // ---------------------------------------------------------------- split precision
 __device__ __forceinline__ void split_f16(float x, __half &hi, __half &lo) {
     hi = __float2half_rn(x);
