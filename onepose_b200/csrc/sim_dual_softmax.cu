@@ -7,6 +7,7 @@
 // conf = (e/R_n)*(e/C_m) to HBM exactly once and keeps per-row / per-column (max, argmax) as packed
 // 64-bit keys (value bits high, inverted index low => ties resolve to the smallest index).  All
 // cross-tile reductions go through per-tile partials folded in a fixed order (deterministic).
+#include <stdlib.h>
 #include "common.cuh"
 #include "sim_tc.cuh"
 
@@ -293,7 +294,7 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         simtc::k_split_planes<<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, n2e, simtc::kOperandScale);
         simtc::k_split_planes<<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, n3e, simtc::kOperandScale);
         OPB_CHECK_LAUNCH();
-        CUtensorMap t2h, t2l, t3h, t3l;
+        CUtensorMap t2h, t2l, t3h, t3l, tconf;
         int rc;
         if ((rc = make_tmap_f16_3d(&t2h, w.m2h, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) ||
             (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, simtc::BN)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, simtc::BN)))
@@ -309,6 +310,9 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         q.c1 = (float)(log2e / ((double)scale_factor * simtc::kOperandScale * simtc::kOperandScale));
         q.c0 = (float)(log2e / (double)scale_factor);
         q.c2 = 2.f * q.c1;
+        q.tma_store = (N3 % 4 == 0) && ((uintptr_t)conf % 16 == 0);
+        if (q.tma_store) { if ((rc = make_tmap_f32_3d_store(&tconf, conf, B, N2, N3, 32))) return rc; } else tconf = t2h;
+        { const char *e = getenv("OPB_SIM_DBG"); q.dbg = e ? atoi(e) : 0; }
         q.rowsum_part = w.rowsum_part; q.colsum_part = w.colsum_part; q.lgR = w.invR; q.lgC = w.invC;
         q.rowmax_part = w.rowmax_part; q.colmax_part = w.colmax_part; q.conf = conf;
         static bool configured = false;
@@ -318,12 +322,12 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
             configured = true;
         }
         dim3 grid(splits, p.tiles_m, B);
-        simtc::k_sim_tc<1><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
+        simtc::k_sim_tc<1><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, tconf, q);
         OPB_CHECK_LAUNCH();
         k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n * 2, N2, w.invR, 1);
         k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC, 1);
         OPB_CHECK_LAUNCH();
-        simtc::k_sim_tc<2><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, q);
+        simtc::k_sim_tc<2><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, tconf, q);
         OPB_CHECK_LAUNCH();
     }
     k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, N3, w.idx0, w.val0);

@@ -17,13 +17,15 @@
 namespace opb {
 namespace simtc {
 
-constexpr int BM = 128, BN = 128, NKB = 4, UNITS = 5;
+constexpr int BM = 128, BN = 128, NKB = 4, UNITS = 4;
 constexpr int TILE_BYTES = 128 * 128;                 // 128 rows x 64 fp16
 constexpr int A_BYTES = 2 * NKB * TILE_BYTES;         // 131072
 constexpr int RING_BYTES = UNITS * TILE_BYTES;        // 81920
+constexpr int STG_WARP_BYTES = 32 * 16 * 4;            // per epilogue warp: 32 rows x 16 fp32 columns, TMA-store staging
+constexpr int STG_BYTES = 8 * STG_WARP_BYTES;         // 16384
 constexpr int SCRATCH_BYTES = 2 * 4 * BN * 8;         // double-buffered [4 warps][128] u64
 constexpr int LGC_BYTES = 2 * BN * 4;                 // double-buffered column terms of the current tile
-constexpr int SMEM_BYTES = A_BYTES + RING_BYTES + SCRATCH_BYTES + LGC_BYTES + 256 + 1024;   // + barriers + alignment slack
+constexpr int SMEM_BYTES = A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES + LGC_BYTES + 256 + 1024;   // + barriers + alignment slack
 constexpr float kOperandScale = 64.f;                 // unit-vector components are scaled into fp16's normal range
 
 struct Params {
@@ -34,6 +36,8 @@ struct Params {
     const float *lgR, *lgC;                           // log2(1/R_n), log2(1/C_m)
     unsigned long long *rowmax_part, *colmax_part;
     float *conf;
+    int tma_store;                                    // conf rows are 16-byte aligned: write conf through TMA stores
+    int dbg;                                          // experiment switches (OPB_SIM_DBG), 0 in production
 };
 
 struct Barriers {
@@ -75,14 +79,16 @@ __device__ __forceinline__ unsigned long long transpose_reduce_max(unsigned long
 template <int PASS>
 __global__ void __launch_bounds__(320, 1)
 k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l,
-         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l, const Params p) {
+         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l,
+         const __grid_constant__ CUtensorMap tm_conf, const Params p) {
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment (SWIZZLE_128B) by an offset on the shared array, so accesses stay in the shared address space (LDS/STS)
     uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t *sA = smem, *sB = smem + A_BYTES;
-    unsigned long long *scratch = reinterpret_cast<unsigned long long *>(smem + A_BYTES + RING_BYTES);
-    float *s_lgc = reinterpret_cast<float *>(smem + A_BYTES + RING_BYTES + SCRATCH_BYTES);
-    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + SCRATCH_BYTES + LGC_BYTES);
+    uint8_t *s_stg = smem + A_BYTES + RING_BYTES;
+    unsigned long long *scratch = reinterpret_cast<unsigned long long *>(smem + A_BYTES + RING_BYTES + STG_BYTES);
+    float *s_lgc = reinterpret_cast<float *>(smem + A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES);
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES + LGC_BYTES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int split = blockIdx.x, row_tile = blockIdx.y, b = blockIdx.z;
@@ -100,6 +106,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     if (warp == 9) tc::tmem_alloc<256>(&bar->tmem_base);
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_m2h); tc::tma_prefetch_desc(&tm_m2l); tc::tma_prefetch_desc(&tm_m3h); tc::tma_prefetch_desc(&tm_m3l);
+        if (PASS == 2 && p.tma_store) tc::tma_prefetch_desc(&tm_conf);
     }
     tc::tcgen05_fence_before();
     __syncthreads();
@@ -249,11 +256,32 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                             const uint32_t bits = __float_as_uint(cf) & 0xFFFFFF80u;
                             const uint32_t kr = bits | (uint32_t)(127 - (ccol + i));
                             tile_rk = kr > tile_rk ? kr : tile_rk;
-                            const uint32_t r = __reduce_max_sync(0xffffffffu, bits | rinv);
-                            ck = lane == i ? r : ck;
+                            if (!(p.dbg & 2)) {
+                                const uint32_t r = __reduce_max_sync(0xffffffffu, bits | rinv);
+                                ck = lane == i ? r : ck;
+                            } else ck |= bits;
                         }
                     }
-                    if (row_ok) {
+                    if (p.tma_store) {
+                        // coalesced write: stage 32 rows x 16 columns in (64-byte swizzled) shared memory, one TMA store per half
+                        // chunk; rows / columns past the end of conf are clipped by the TMA unit
+                        uint8_t *stg = s_stg + warp * STG_WARP_BYTES;
+#pragma unroll
+                        for (int hc = 0; hc < 2; ++hc) {
+                            if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
+                            __syncwarp();
+#pragma unroll
+                            for (int q = 0; q < 4; ++q)
+                                *reinterpret_cast<float4 *>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) =
+                                    make_float4(vv[hc * 16 + 4 * q], vv[hc * 16 + 4 * q + 1], vv[hc * 16 + 4 * q + 2], vv[hc * 16 + 4 * q + 3]);
+                            tc::fence_proxy_async();
+                            __syncwarp();
+                            if (lane == 0 && !(p.dbg & 1)) {
+                                tc::tma_store_3d(&tm_conf, stg, col0 + hc * 16, m0 + quad * 32, b);
+                                tc::tma_store_commit();
+                            }
+                        }
+                    } else if (row_ok) {
                         if (vec_ok && col0 + 31 < p.N3) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q)
@@ -276,6 +304,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         }
         epi_bar_sync();
         fold_columns(t1 - 1, j - 1);
+        if (PASS == 2 && lane == 0) tc::tma_store_wait_all();
         if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * (gridDim.x * 2) + split * 2 + half) * p.N2 + row] = row_key;
     }
     tc::tcgen05_fence_before();

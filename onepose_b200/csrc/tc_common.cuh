@@ -63,6 +63,16 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
         : "memory");
 }
 
+// TMA store (shared -> global), bulk-group completion
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *m, const void *smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---------------------------------------------------------------- TMEM
 template <int COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t *smem_result) {   // one full warp
@@ -144,5 +154,8 @@ __device__ __forceinline__ void split_f16(float x, __half &hi, __half &lo) {
 // host: tensor map of an fp16 [batch, rows, cols] row-major array, box = {64 cols, box_rows, 1}, 128-byte swizzle.
 // Out-of-range rows are zero-filled, so ragged row counts need no special casing in the kernels.
 int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// host: tensor map of an fp32 [batch, rows, cols] row-major array for TMA stores, box = {16 cols, box_rows, 1}, 64-byte swizzle
+// (cols must be a multiple of 4: global strides are multiples of 16 bytes).
+int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 
 }  // namespace opb
