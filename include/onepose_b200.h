@@ -140,9 +140,13 @@ int op_gather_matches(const int64_t *matches0, const float *scores0, const float
  * Correspondences of frame f are rows [f*stride, f*stride + count[f]) of pts2d/pts3d (float64,
  * converted to float32 inside as cv2 does).  samples: [n_samples_sets, H, 5] int32 minimal-sample
  * indices (host-generated cv::RNG stream); frame f uses sample set sample_set[f].
+ * samples == sample_set == NULL: cv2's own stream is generated on the device, lazily per round.
  * Stage 1 solves one 5-point EPnP per hypothesis and counts inliers (float32 squared reprojection
  * error <= thr^2); stage 2 replays cv2's sequential accept / adaptive-niters rule, recomputes the
  * winner's inlier mask, refits EPnP on all inliers and converts to [R|t/scale].
+ * Hypotheses are evaluated in rounds [0,32), [32,256), [256,1024), [1024,4096), ...; a frame stops taking part once
+ * cv2's adaptive iteration bound, replayed over the rounds done, is reached (hyp_counts stay -1 beyond: same result as
+ * evaluating all H, cv2 never looks at them).
  * Outputs: pose [F,3,4] float64, inlier_mask [F,stride] uint8, n_inliers [F] int32,
  * iters_run [F] int32, hyp_counts [F,H] int32 (diagnostic), hyp_pose [F,H,6] float64 (rvec,tvec). */
 size_t op_pnp_workspace_bytes(int F, int stride, int H);

@@ -81,7 +81,7 @@ LAUNCHES = {
     "op_split_planes": 1, "op_norm_relu_split": 1, "op_linear_tc": 1, "op_instnorm_finalize_tc": 1, "op_attn_apply_planes": 1,
     "op_channel_major_to_point_major": 1, "op_gats_leaf_aggregate": 1, "op_linear": 1, "op_instnorm_finalize": 1,
     "op_kv_reduce": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 9, "op_sim_dual_softmax_simt": 7,
-    "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 3,
+    "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 5,
 }
 
 

@@ -66,12 +66,17 @@ __device__ inline void solve_minimal(const float *X32, const float *uv32, const 
 __global__ void __launch_bounds__(kHypBlock)
 k_pnp_hypotheses(const float *__restrict__ X32, const float *__restrict__ uv32, const int32_t *__restrict__ count, int stride,
                  const double *__restrict__ Kmat, const int32_t *__restrict__ samples, const int32_t *__restrict__ sample_set,
-                 int H, float thr2, int32_t *__restrict__ hyp_counts, double *__restrict__ hyp_pose) {
+                 int H_total, int h_begin, int h_end, const int32_t *__restrict__ bound, float thr2, int32_t *__restrict__ hyp_counts,
+                 double *__restrict__ hyp_pose) {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
-    const int h = blockIdx.x * kHypBlock + threadIdx.x;
+    const int h = h_begin + blockIdx.x * kHypBlock + threadIdx.x;
+    // adaptive rounds: cv2's sequential loop never looks at iteration >= niters, and niters only shrinks, so a warp whose
+    // first hypothesis is already past the bound replayed over the earlier rounds has nothing to contribute
+    if (h - lane >= h_end || (bound && h - lane >= bound[f])) return;
+    const int H = h_end < H_total ? h_end : H_total;
     const int n = count[f];
     if (n <= 5) {                       // no RANSAC for n <= 5 (handled in k_pnp_select_refit)
-        if (h < H) hyp_counts[(long long)f * H + h] = -1;
+        if (h < H) hyp_counts[(long long)f * H_total + h] = -1;
         return;
     }
     const Cam cam = load_cam(Kmat + (long long)f * 9);
@@ -79,13 +84,13 @@ k_pnp_hypotheses(const float *__restrict__ X32, const float *__restrict__ uv32, 
     double rvec[3] = {0, 0, 0}, tvec[3] = {0, 0, 0}, R[9];
     bool ok = false;
     if (h < H) {
-        const int32_t *s = samples + ((long long)sample_set[f] * H + h) * 5;
+        const int32_t *s = samples + ((long long)sample_set[f] * H_total + h) * 5;
         int idx[5];
         ok = true;
         for (int i = 0; i < 5; ++i) { idx[i] = s[i]; ok = ok && idx[i] >= 0 && idx[i] < n; }
         if (ok) {
             solve_minimal(X, uv, idx, cam, rvec, tvec);
-            double *dst = hyp_pose + ((long long)f * H + h) * 6;
+            double *dst = hyp_pose + ((long long)f * H_total + h) * 6;
             dst[0] = rvec[0]; dst[1] = rvec[1]; dst[2] = rvec[2]; dst[3] = tvec[0]; dst[4] = tvec[1]; dst[5] = tvec[2];
         }
     }
@@ -105,20 +110,23 @@ k_pnp_hypotheses(const float *__restrict__ X32, const float *__restrict__ uv32, 
         for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
         if (lane == hh) my_count = c;
     }
-    if (h < H) hyp_counts[(long long)f * H + h] = my_count;
+    if (h < H) hyp_counts[(long long)f * H_total + h] = my_count;
 }
 
-// cv::RNG((uint64)-1) multiply-with-carry stream, one sequential generator per frame
-__global__ void k_pnp_cv_samples(const int32_t *__restrict__ count, int F, int H, int32_t *__restrict__ samples,
-                                 int32_t *__restrict__ sample_set) {
+// cv::RNG((uint64)-1) multiply-with-carry stream, one sequential generator per frame.  Samples [h_begin, h_end) are
+// drawn; the generator state is carried in rng_state between rounds (rng_state == nullptr: one shot from the seed).
+__global__ void k_pnp_cv_samples(const int32_t *__restrict__ count, int F, int H, int h_begin, int h_end,
+                                 const int32_t *__restrict__ bound, unsigned long long *__restrict__ rng_state,
+                                 int32_t *__restrict__ samples, int32_t *__restrict__ sample_set) {
     const int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= F) return;
-    sample_set[f] = f;
+    if (h_begin == 0) sample_set[f] = f;
+    if (bound && h_begin >= bound[f]) return;
     const unsigned n = (unsigned)count[f];
     int32_t *out = samples + (long long)f * H * 5;
-    if (n < 5) { for (int i = 0; i < H * 5; ++i) out[i] = 0; return; }
-    unsigned long long state = 0xffffffffffffffffull;
-    for (int it = 0; it < H; ++it) {
+    if (n < 5) { for (int i = h_begin * 5; i < h_end * 5; ++i) out[i] = 0; return; }
+    unsigned long long state = (h_begin == 0 || !rng_state) ? 0xffffffffffffffffull : rng_state[f];
+    for (int it = h_begin; it < h_end; ++it) {
         int idx[5];
         for (int i = 0; i < 5; ++i) {
             int v;
@@ -133,6 +141,7 @@ __global__ void k_pnp_cv_samples(const int32_t *__restrict__ count, int F, int H
             out[it * 5 + i] = v;
         }
     }
+    if (rng_state) rng_state[f] = state;
 }
 
 __device__ inline int update_num_iters(double p, double ep, int model_points, int max_iters) {
@@ -143,6 +152,29 @@ __device__ inline int update_num_iters(double p, double ep, int model_points, in
     if (denom < DBL_MIN) return 0;
     num = log(num); denom = log(denom);
     return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)llrint(num / denom);
+}
+
+// Replays cv2's accept rule over the counts of round [h_begin, h_end) and tightens the per-frame iteration bound
+// (state = {niters, best_count}).  One thread per frame: the rule is a dependent scan.
+__global__ void k_pnp_bound_update(const int32_t *__restrict__ count, int F, int H, int h_begin, int h_end,
+                                   const int32_t *__restrict__ hyp_counts, double confidence, int max_iters,
+                                   int32_t *__restrict__ bound, int32_t *__restrict__ state) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    int niters = h_begin == 0 ? max_iters : state[2 * f], best = h_begin == 0 ? 0 : state[2 * f + 1];
+    const int n = count[f];
+    if (n > 5) {
+        const int32_t *cnt = hyp_counts + (long long)f * H;
+        for (int it = h_begin; it < h_end && it < niters; ++it) {
+            const int good = cnt[it];
+            const int floor_ = best > 4 ? best : 4;
+            if (good > floor_) { best = good; niters = update_num_iters(confidence, (double)(n - good) / n, 5, niters); }
+        }
+    } else {
+        niters = 0;
+    }
+    state[2 * f] = niters; state[2 * f + 1] = best;
+    bound[f] = niters;
 }
 
 // ordered block reduction of K doubles per thread; result broadcast to all threads through `out`

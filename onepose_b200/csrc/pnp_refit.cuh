@@ -224,14 +224,19 @@ k_pnp_select_refit(const float *__restrict__ X32, const float *__restrict__ uv32
     }
 }
 
-struct PnpWorkspace { float *X32, *uv32; double *alphas; int32_t *inl; size_t bytes; };
-static PnpWorkspace carve_pnp(void *base, int F, int stride) {
+struct PnpWorkspace { float *X32, *uv32; double *alphas; int32_t *inl, *bound, *state, *samples, *sample_set; unsigned long long *rng; size_t bytes; };
+static PnpWorkspace carve_pnp(void *base, int F, int stride, int H) {
     PnpWorkspace w; size_t off = 0;
     auto take = [&](size_t bytes) { void *p = base ? (char *)base + off : nullptr; off += align_up(bytes, 256); return p; };
     w.alphas = (double *)take((size_t)F * stride * 4 * sizeof(double));
     w.X32 = (float *)take((size_t)F * stride * 3 * sizeof(float));
     w.uv32 = (float *)take((size_t)F * stride * 2 * sizeof(float));
     w.inl = (int32_t *)take((size_t)F * stride * sizeof(int32_t));
+    w.bound = (int32_t *)take((size_t)F * sizeof(int32_t));
+    w.state = (int32_t *)take((size_t)F * 2 * sizeof(int32_t));
+    w.rng = (unsigned long long *)take((size_t)F * sizeof(unsigned long long));
+    w.sample_set = (int32_t *)take((size_t)F * sizeof(int32_t));
+    w.samples = (int32_t *)take((size_t)F * H * 5 * sizeof(int32_t));     // cv2's stream when the caller supplies no samples
     w.bytes = off;
     return w;
 }
@@ -240,13 +245,12 @@ static PnpWorkspace carve_pnp(void *base, int F, int stride) {
 }  // namespace opb
 
 extern "C" size_t op_pnp_workspace_bytes(int F, int stride, int H) {
-    (void)H;
-    return opb::pnp::carve_pnp(nullptr, F > 0 ? F : 1, stride > 0 ? stride : 1).bytes;
+    return opb::pnp::carve_pnp(nullptr, F > 0 ? F : 1, stride > 0 ? stride : 1, H > 0 ? H : 1).bytes;
 }
 
 extern "C" int op_pnp_cv_samples(const int32_t *count, int F, int H, int32_t *samples, int32_t *sample_set, void *stream) {
     OPB_CHECK_ARG(count && samples && sample_set && F > 0 && H > 0, "op_pnp_cv_samples: bad argument");
-    opb::pnp::k_pnp_cv_samples<<<opb::ceil_div(F, 32), 32, 0, (cudaStream_t)stream>>>(count, F, H, samples, sample_set);
+    opb::pnp::k_pnp_cv_samples<<<opb::ceil_div(F, 32), 32, 0, (cudaStream_t)stream>>>(count, F, H, 0, H, nullptr, nullptr, samples, sample_set);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }
@@ -258,19 +262,41 @@ extern "C" int op_pnp_ransac(const double *pts2d, const double *pts3d, const int
                              int32_t *hyp_counts, double *hyp_pose, void *workspace, size_t workspace_bytes, void *stream) {
     using namespace opb;
     using namespace opb::pnp;
-    OPB_CHECK_ARG(pts2d && pts3d && count && K && samples && sample_set && pose && inlier_mask && n_inliers && iters_run &&
+    OPB_CHECK_ARG(pts2d && pts3d && count && K && pose && inlier_mask && n_inliers && iters_run &&
                   hyp_counts && hyp_pose && workspace, "op_pnp_ransac: null pointer");
+    OPB_CHECK_ARG((samples == nullptr) == (sample_set == nullptr), "op_pnp_ransac: samples and sample_set come together (both NULL = cv2's own stream)");
     OPB_CHECK_ARG(F > 0 && stride > 0 && H > 0 && F <= 65535, "op_pnp_ransac: bad shape F=%d stride=%d H=%d", F, stride, H);
     OPB_CHECK_ARG(scale != 0.0 && reproj_thr > 0, "op_pnp_ransac: bad scale / threshold");
-    PnpWorkspace w = carve_pnp(workspace, F, stride);
+    PnpWorkspace w = carve_pnp(workspace, F, stride, H);
     if (workspace_bytes < w.bytes) { set_error("op_pnp_ransac: workspace %zu < %zu bytes", workspace_bytes, w.bytes); return OPB_ERR_WORKSPACE; }
     cudaStream_t st = (cudaStream_t)stream;
     const float thr2 = (float)(reproj_thr * reproj_thr);
     k_pnp_prepare<<<dim3(ceil_div(stride, 256), F), 256, 0, st>>>(pts2d, pts3d, count, stride, w.X32, w.uv32);
     OPB_CHECK_LAUNCH();
-    k_pnp_hypotheses<<<dim3(ceil_div(H, kHypBlock), F), kHypBlock, 0, st>>>(w.X32, w.uv32, count, stride, K, samples, sample_set, H,
-                                                                            thr2, hyp_counts, hyp_pose);
-    OPB_CHECK_LAUNCH();
+    // Adaptive rounds (exactly cv2's result): round r evaluates hypotheses [h0, h1) only for frames whose iteration bound --
+    // cv2's niters replayed over the rounds before -- still reaches h0.  Unevaluated hyp_counts stay -1.
+    OPB_CHECK_CUDA(cudaMemsetAsync(hyp_counts, 0xFF, (size_t)F * H * sizeof(int32_t), st));
+    const bool own_stream = samples == nullptr;
+    if (own_stream) { samples = w.samples; sample_set = w.sample_set; }
+    static const int kRoundEnd[] = {32, 256, 1024, 4096};
+    int h0 = 0;
+    for (int r = 0; h0 < H; ++r) {
+        int h1 = r < 4 ? kRoundEnd[r] : h0 + 4096;
+        if (h1 > H) h1 = H;
+        const int32_t *bnd = r == 0 ? nullptr : w.bound;
+        if (own_stream) {
+            k_pnp_cv_samples<<<ceil_div(F, 32), 32, 0, st>>>(count, F, H, h0, h1, bnd, w.rng, w.samples, w.sample_set);
+            OPB_CHECK_LAUNCH();
+        }
+        k_pnp_hypotheses<<<dim3(ceil_div(h1 - h0, kHypBlock), F), kHypBlock, 0, st>>>(w.X32, w.uv32, count, stride, K, samples, sample_set, H,
+                                                                                    h0, h1, bnd, thr2, hyp_counts, hyp_pose);
+        OPB_CHECK_LAUNCH();
+        if (h1 < H) {
+            k_pnp_bound_update<<<ceil_div(F, 64), 64, 0, st>>>(count, F, H, h0, h1, hyp_counts, confidence, max_iters, w.bound, w.state);
+            OPB_CHECK_LAUNCH();
+        }
+        h0 = h1;
+    }
     k_pnp_select_refit<<<F, kRefitThreads, 0, st>>>(w.X32, w.uv32, count, stride, K, hyp_counts, hyp_pose, H, thr2, confidence,
                                                     max_iters, scale, w.alphas, w.inl, pose, inlier_mask, n_inliers, iters_run);
     OPB_CHECK_LAUNCH();

@@ -66,15 +66,12 @@ def ransac_pnp_batched(K, pts2d, pts3d, counts, samples=None, sample_set=None, s
     pts3d = pts3d.to(torch.float64).contiguous()
     K = K.to(device=dev, dtype=torch.float64).contiguous()
     counts = counts.to(device=dev, dtype=torch.int32).contiguous()
-    if samples is None:          # cv2's own stream, generated on the device (no host round trip)
+    if samples is None:          # cv2's own stream, generated lazily on the device inside op_pnp_ransac
         H = int(hypotheses)
-        samples = torch.empty(F, H, 5, dtype=torch.int32, device=dev)
-        sample_set = torch.empty(F, dtype=torch.int32, device=dev)
-        with torch.cuda.device(dev):
-            call("op_pnp_cv_samples", ptr(counts), F, H, ptr(samples), ptr(sample_set), stream_ptr())
-    samples = samples.to(device=dev, dtype=torch.int32).contiguous()
-    sample_set = sample_set.to(device=dev, dtype=torch.int32).contiguous()
-    H = samples.shape[1]
+    else:
+        samples = samples.to(device=dev, dtype=torch.int32).contiguous()
+        sample_set = sample_set.to(device=dev, dtype=torch.int32).contiguous()
+        H = samples.shape[1]
     pose = torch.empty(F, 3, 4, dtype=torch.float64, device=dev)
     mask = torch.empty(F, S, dtype=torch.uint8, device=dev)
     n_inl = torch.empty(F, dtype=torch.int32, device=dev)
@@ -89,7 +86,7 @@ def ransac_pnp_batched(K, pts2d, pts3d, counts, samples=None, sample_set=None, s
                                 ptr(iters), ptr(hyp_counts), ptr(hyp_pose), ptr(ws), nbytes, stream_ptr())
     out = dict(pose=pose, inlier_mask=mask.bool(), n_inliers=n_inl, iters_run=iters)
     if return_debug:
-        out.update(hyp_counts=hyp_counts, hyp_pose=hyp_pose, samples=samples, sample_set=sample_set)
+        out.update(hyp_counts=hyp_counts, hyp_pose=hyp_pose)
     return out
 
 

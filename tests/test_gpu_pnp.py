@@ -34,13 +34,23 @@ def test_hypothesis_stage_vs_restatement():
     pr = synth.make_pnp_problem(31, 1200, 0.6, scale=1000.0)
     X, uv, K = pr["pts3d"], pr["pts2d"], pr["K"]
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
-    r = ransac_pnp_batched(t(K)[None], t(uv)[None], t(X)[None], torch.tensor([len(X)], dtype=torch.int32).cuda(),
-                           scale=1000.0, hypotheses=256, return_debug=True)
-    samples = r["samples"][0].cpu().numpy()
+    from onepose_b200._lib import call, ptr, stream_ptr
+    cnt_t = torch.tensor([len(X)], dtype=torch.int32).cuda()
+    smp = torch.empty(1, 256, 5, dtype=torch.int32, device="cuda"); sset = torch.empty(1, dtype=torch.int32, device="cuda")
+    call("op_pnp_cv_samples", ptr(cnt_t), 1, 256, ptr(smp), ptr(sset), stream_ptr())
+    samples = smp[0].cpu().numpy()
     assert np.array_equal(samples, po.cv_sample_stream(len(X), 256))        # device RNG == cv::RNG
+    r = ransac_pnp_batched(t(K)[None], t(uv)[None], t(X)[None], cnt_t, samples=smp, sample_set=sset,
+                           scale=1000.0, return_debug=True)
+    r_own = ransac_pnp_batched(t(K)[None], t(uv)[None], t(X)[None], cnt_t, scale=1000.0, hypotheses=256, return_debug=True)
+    assert torch.equal(r["hyp_counts"], r_own["hyp_counts"]) and torch.equal(r["pose"], r_own["pose"])   # lazy stream == supplied stream
     X32, uv32 = X.astype(np.float32), uv.astype(np.float32)
     hp = r["hyp_pose"][0].cpu().numpy(); hc = r["hyp_counts"][0].cpu().numpy()
     same_count = 0; close = 0; clean = 0; clean_close = 0
+    # adaptive rounds: hypotheses past cv2's iteration bound are not evaluated (count -1) -- compare the evaluated ones
+    evaluated = np.nonzero(hc >= 0)[0]
+    assert len(evaluated) >= 32 and int(r["iters_run"][0]) <= len(evaluated)
+    samples = samples[evaluated]; hp = hp[evaluated]; hc = hc[evaluated]
     for h, s in enumerate(samples):
         rv, tv = po.hypothesis(X32, uv32, K, s)
         cnt = int((po.reproj_err(X32, uv32, K, rv, tv) <= np.float32(25)).sum())
