@@ -240,7 +240,7 @@ def run_ours(args):
         for name, (kms, n, work) in sorted(summary.items(), key=lambda kv: -kv[1][0]):
             ent = {"ms_per_step": kms / args.steps, "calls_per_step": n / args.steps, "share": kms / tot}
             if work > 0:
-                if name.startswith("op_linear"):
+                if name.startswith(("op_linear", "op_atb")):
                     ent.update(bound="tensor", achieved=work / (kms * 1e-3) / 1e12, peak=peaks["tensor"], unit="TFLOP/s")
                 else:
                     ent.update(bound="hbm", achieved=work / (kms * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")

@@ -67,6 +67,9 @@ int op_gats_leaf_aggregate(const float *leaf, long long leaf_bstride, const floa
 #define OPB_LIN_RESIDUAL 2
 #define OPB_LIN_STATS 4
 #define OPB_LIN_NORM_RELU 8
+#define OPB_LIN_COLSUM 16    /* op_linear_tc: stats_partial = (sum, 0) of the value after bias / elu+1 over the valid rows */
+#define OPB_LIN_ZSCALE 32    /* op_linear_tc: each 64-column head of a row is multiplied by zscale_num / (row_head . ksum[b, head] + 1e-6) */
+#define OPB_LIN_WBATCHED 64  /* op_linear_tc: W planes are [B, Cout, K], one matrix per frame */
 int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
               float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,
               const float *mean, const float *rstd, double *stats_partial, void *stream);
@@ -101,10 +104,21 @@ int op_norm_relu_split(const float *h, const float *mean, const float *rstd, voi
                        int C, void *stream);
 int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
                  const void *Wl, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
-                 int flags, int elu_cols, float *stats_partial, void *stream);
+                 int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream);
 int op_linear_tc_stat_parts(int rows_per_batch);
 int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B, int parts, int C, int rows_per_batch,
                             float eps, float *mean, float *rstd, void *stream);
+/* Source side of linear attention on the tensor cores (:88-99), re-associated so that the V projection is never
+ * materialised: op_atb_tc computes per-chunk partials of G = K'^T X over the M source points (A = K' planes, B = X
+ * planes, both [B, M, 256]; partial [B][op_atb_chunks(M)][256][256] fp32); op_kv_post folds them and the OPB_LIN_COLSUM
+ * partials of K' (ksum_partial [B][nparts][256][2]) and emits ksum [B,256], optionally KV [B,4,64,64] (:96, scaled by inv_m = 1/M),
+ * and the per-frame matrix P_b[o,(h,d)] = sum_q KV_h[d,q] Wm[o,(h,q)] as planes [B,256,256], so that
+ * message = (Q' M / (Q'_h.Ksum_h + 1e-6)) P_b^T + bm is one op_linear_tc call (OPB_LIN_ZSCALE on the Q projection,
+ * OPB_LIN_WBATCHED on the merge).  Wv [256,256] / bv head-major rows, Wm [256,256] head-major columns. */
+int op_atb_chunks(int M);
+int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const void *Bl, int B, int M, float *partial, void *stream);
+int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *Wv, const float *bv,
+               const float *Wm, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream);
 /* op_attn_apply writing split-precision planes instead of fp32 */
 int op_attn_apply_planes(const float *Qp, const float *KV, const float *Ksum, void *out_hi, void *out_lo, int B, int N,
                          int M, void *stream);

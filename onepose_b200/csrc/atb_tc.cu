@@ -1,0 +1,245 @@
+// (2) Source side of linear attention on the tensor cores -- reference linear_attention, GATs_SuperGlue.py:88-99.
+//
+// KV_h = sum_m K'_h[m]^T V_h[m] / M with V = X Wv^T + bv is re-associated as
+//     KV_h = ( (K'_h^T X) Wv_h^T + Ksum_h bv_h^T ) / M ,
+// so the only reduction over the M source points is G = K'^T X, a plain [256 x M] x [M x 256] GEMM (the V projection
+// is never materialised), and the attention read-out + merge convolution (:98, :119) collapse into one per-frame matrix
+//     P_b[o, (h,d)] = sum_q KV_h[d,q] Wm[o, (h,q)]
+// applied to Q'' = Q' M / (Q'_h . Ksum_h + 1e-6) by the ordinary projection kernel (linear_tc.cuh, ZSCALE + WBATCHED).
+//
+//  k_atb_tc   : G partial of one chunk of points.  Both operands are row-major [points, 256] split-precision planes,
+//               i.e. MN-major UMMA operands (K = point): TMA boxes of 32 points x 64 channels (SWIZZLE_128B), three
+//               stages of 64 KB, tcgen05.mma M128 N256 K16 x 3 passes into two 256-column TMEM accumulators.
+//  k_kv_post  : per (frame, head): fold the chunk partials and the Ksum partials in a fixed order, KV', P_b -> planes.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace opb {
+namespace atb {
+
+constexpr int KB = 32;                         // points per k-block
+constexpr int BLK = KB * 128;                  // one 64-channel block of one plane: 32 rows x 128 B = 4096
+constexpr int PLANE = 4 * BLK;                 // 256 channels
+constexpr int STAGE_BYTES = 4 * PLANE;         // A hi, A lo, B hi, B lo = 65536
+constexpr int STAGES = 3;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;
+constexpr int THREADS = 320;
+constexpr int kChunk = 512;                    // points per CTA
+
+struct Barriers { uint64_t full[STAGES], empty[STAGES], acc_full; uint32_t tmem_base; };
+
+// MN-major SWIZZLE_128B operand: 64-element (128 B) atoms along M/N spaced LBO apart, 8-row groups along K spaced SBO apart
+__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) |
+           ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+k_atb_tc(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUtensorMap tm_al,
+         const __grid_constant__ CUtensorMap tm_bh, const __grid_constant__ CUtensorMap tm_bl, int M, int nchunks,
+         float *__restrict__ partial /* [B][nchunks][256][256] */) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + STAGES * STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int chunk = blockIdx.x, b = blockIdx.y;
+    const int p0 = chunk * kChunk, p1 = min(M, p0 + kChunk);
+    const int nkb = (p1 - p0 + KB - 1) / KB;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; ++i) { tc::mbar_init(&bar->full[i], 1); tc::mbar_init(&bar->empty[i], 1); }
+        tc::mbar_init(&bar->acc_full, 1);
+        tc::fence_barrier_init();
+    }
+    if (warp == 9) tc::tmem_alloc<512>(&bar->tmem_base);
+    if (warp == 8 && lane == 0) { tc::tma_prefetch_desc(&tm_ah); tc::tma_prefetch_desc(&tm_al); tc::tma_prefetch_desc(&tm_bh); tc::tma_prefetch_desc(&tm_bl); }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = bar->tmem_base;
+
+    if (warp == 8) {
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; ++kb) {
+                const uint32_t stage = kb % STAGES, ph = (kb / STAGES) & 1;
+                uint8_t *st = smem + stage * STAGE_BYTES;
+                tc::mbar_wait(&bar->empty[stage], ph ^ 1);
+                tc::mbar_arrive_expect_tx(&bar->full[stage], STAGE_BYTES);
+                const int row = p0 + kb * KB;                 // rows past M are zero-filled by TMA
+#pragma unroll
+                for (int blk = 0; blk < 4; ++blk) {
+                    tc::tma_load_3d(st + 0 * PLANE + blk * BLK, &tm_ah, &bar->full[stage], blk * 64, row, b);
+                    tc::tma_load_3d(st + 1 * PLANE + blk * BLK, &tm_al, &bar->full[stage], blk * 64, row, b);
+                    tc::tma_load_3d(st + 2 * PLANE + blk * BLK, &tm_bh, &bar->full[stage], blk * 64, row, b);
+                    tc::tma_load_3d(st + 3 * PLANE + blk * BLK, &tm_bl, &bar->full[stage], blk * 64, row, b);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        if (lane == 0) {
+            // D = f32, A = B = f16, both MN-major (bits 15, 16), M = 128, N = 256
+            constexpr uint32_t idesc = tc::umma_idesc_f16(128, 256) | (1u << 15) | (1u << 16);
+            const uint32_t base = tc::smem_u32(smem);
+            for (int kb = 0; kb < nkb; ++kb) {
+                const uint32_t stage = kb % STAGES, ph = (kb / STAGES) & 1;
+                const uint32_t sb = base + stage * STAGE_BYTES;
+                tc::mbar_wait(&bar->full[stage], ph);
+                tc::tcgen05_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < KB / 16; ++ks) {         // 16 points = two 8-row groups = 2048 B
+                    const uint64_t bh = umma_desc_mn128(sb + 2 * PLANE + ks * 2048, BLK, 1024);
+                    const uint64_t bl = umma_desc_mn128(sb + 3 * PLANE + ks * 2048, BLK, 1024);
+#pragma unroll
+                    for (int mh = 0; mh < 2; ++mh) {           // output rows (K' channels) mh*128 .. +127 = channel blocks 2mh, 2mh+1
+                        const uint64_t ah = umma_desc_mn128(sb + 0 * PLANE + mh * 2 * BLK + ks * 2048, BLK, 1024);
+                        const uint64_t al = umma_desc_mn128(sb + 1 * PLANE + mh * 2 * BLK + ks * 2048, BLK, 1024);
+                        const uint32_t d = tmem_base + mh * 256;
+                        tc::umma_f16(d, ah, bh, idesc, (kb | ks) != 0);
+                        tc::umma_f16(d, al, bh, idesc, 1);
+                        tc::umma_f16(d, ah, bl, idesc, 1);
+                    }
+                }
+                tc::umma_commit(&bar->empty[stage]);
+            }
+            tc::umma_commit(&bar->acc_full);
+        }
+        __syncwarp();
+    } else {
+        const int quad = warp & 3, half = warp >> 2;
+        tc::mbar_wait(&bar->acc_full, 0);
+        tc::tcgen05_fence_after();
+        float *dst0 = partial + ((long long)b * nchunks + chunk) * 256 * 256;
+#pragma unroll 1
+        for (int mh = 0; mh < 2; ++mh) {
+            const int d = mh * 128 + quad * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                const int col = half * 128 + c * 32;
+                float v[32];
+                tc::tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + mh * 256 + col, v);
+                tc::tmem_ld_wait();
+                float4 *dst = reinterpret_cast<float4 *>(dst0 + (long long)d * 256 + col);
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    dst[q] = make_float4(v[4 * q] * (1.f / 4096.f), v[4 * q + 1] * (1.f / 4096.f), v[4 * q + 2] * (1.f / 4096.f), v[4 * q + 3] * (1.f / 4096.f));
+            }
+        }
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 9) tc::tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace atb
+}  // namespace opb
+
+namespace opb {
+namespace atb {
+
+// per (head h, frame b): G_h = sum of chunk partials; Ksum_h = sum of column-sum partials; KV'_h = G_h Wv_h^T + Ksum_h bv_h^T;
+// P_b[o, h*64+d] = sum_q KV'_h[d,q] Wm[o, h*64+q] written as split-precision planes (x64).  All folds in a fixed order.
+__global__ void __launch_bounds__(256)
+k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
+          const float *__restrict__ Wv /* [256][256] head-major rows */, const float *__restrict__ bv,
+          const float *__restrict__ Wm /* [256][256] head-major columns */, float inv_m, float *__restrict__ ksum /* [B][256] */,
+          float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
+    extern __shared__ float sm[];
+    float *G = sm;                     // [64][256]
+    float *KV = sm + 64 * 256;         // [64][65]
+    float *Ks = KV + 64 * 65;          // [64]
+    const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    for (int e = tid; e < 64 * 256; e += 256) {
+        const int d = e >> 8, c = e & 255;
+        float s = 0.f;
+        for (int k = 0; k < nchunks; ++k) s += partial[(((long long)b * nchunks + k) * 256 + h * 64 + d) * 256 + c];
+        G[e] = s;
+    }
+    if (tid < 64) {
+        double s = 0;
+        for (int k = 0; k < nparts; ++k) s += (double)ksum_part[((long long)b * nparts + k) * 256 + h * 64 + tid].x;
+        Ks[tid] = (float)s;
+        ksum[(long long)b * 256 + h * 64 + tid] = (float)s;
+    }
+    __syncthreads();
+    {   // KV'[d][q]: thread = (q, group of 16 d)
+        const int q = tid & 63, d0 = (tid >> 6) * 16;
+        float acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+        const float *w = Wv + (long long)(h * 64 + q) * 256;
+        for (int c = 0; c < 256; ++c) {
+            const float wc = __ldg(w + c);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) acc[i] = fmaf(G[(d0 + i) * 256 + c], wc, acc[i]);
+        }
+        const float bq = bv[h * 64 + q];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float v = fmaf(Ks[d0 + i], bq, acc[i]) * inv_m;        // value / v_length, :93-94
+            KV[(d0 + i) * 65 + q] = v;
+            if (kv_out) kv_out[(((long long)b * 4 + h) * 64 + d0 + i) * 64 + q] = v;
+        }
+    }
+    __syncthreads();
+    {   // P[o][h*64 + d], thread = o
+        const int o = tid;
+        float wm[64];
+#pragma unroll
+        for (int q = 0; q < 64; ++q) wm[q] = __ldg(Wm + (long long)o * 256 + h * 64 + q);
+        __half *ph = Ph + ((long long)b * 256 + o) * 256 + h * 64, *pl = Pl + ((long long)b * 256 + o) * 256 + h * 64;
+        for (int d = 0; d < 64; d += 2) {
+            float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+            for (int q = 0; q < 64; ++q) { a0 = fmaf(KV[d * 65 + q], wm[q], a0); a1 = fmaf(KV[(d + 1) * 65 + q], wm[q], a1); }
+            __half h0, l0, h1, l1;
+            tc::split_f16(a0 * 64.f, h0, l0); tc::split_f16(a1 * 64.f, h1, l1);
+            *reinterpret_cast<__half2 *>(ph + d) = __halves2half2(h0, h1);
+            *reinterpret_cast<__half2 *>(pl + d) = __halves2half2(l0, l1);
+        }
+    }
+}
+
+constexpr int kPostSmem = (64 * 256 + 64 * 65 + 64) * 4;
+
+}  // namespace atb
+}  // namespace opb
+
+extern "C" int op_atb_chunks(int M) { return opb::ceil_div(M > 0 ? M : 1, opb::atb::kChunk); }
+
+extern "C" int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const void *Bl, int B, int M, float *partial, void *stream) {
+    using namespace opb;
+    OPB_CHECK_ARG(Ah && Al && Bh && Bl && partial, "op_atb_tc: null pointer");
+    OPB_CHECK_ARG(B > 0 && M > 0 && B <= 65535, "op_atb_tc: bad shape B=%d M=%d", B, M);
+    CUtensorMap tah, tal, tbh, tbl;
+    int rc;
+    if ((rc = make_tmap_f16_3d(&tah, Ah, B, M, kD, atb::KB)) || (rc = make_tmap_f16_3d(&tal, Al, B, M, kD, atb::KB)) ||
+        (rc = make_tmap_f16_3d(&tbh, Bh, B, M, kD, atb::KB)) || (rc = make_tmap_f16_3d(&tbl, Bl, B, M, kD, atb::KB)))
+        return rc;
+    static bool configured = false;
+    if (!configured) {
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_atb_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::SMEM_BYTES));
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_kv_post, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::kPostSmem));
+        configured = true;
+    }
+    const int nchunks = ceil_div(M, atb::kChunk);
+    atb::k_atb_tc<<<dim3(nchunks, B), atb::THREADS, atb::SMEM_BYTES, (cudaStream_t)stream>>>(tah, tal, tbh, tbl, M, nchunks, partial);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
+
+extern "C" int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *Wv, const float *bv,
+                          const float *Wm, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream) {
+    using namespace opb;
+    OPB_CHECK_ARG(partial && ksum_partial && Wv && bv && Wm && ksum && Ph && Pl, "op_kv_post: null pointer");
+    OPB_CHECK_ARG(B > 0 && nchunks > 0 && nparts > 0 && B <= 65535, "op_kv_post: bad shape");
+    static bool configured = false;
+    if (!configured) {
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_kv_post, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::kPostSmem));
+        configured = true;
+    }
+    atb::k_kv_post<<<dim3(4, B), 256, atb::kPostSmem, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, Wv, bv, Wm,
+                                                                            inv_m, ksum, kv_out, (__half *)Ph, (__half *)Pl);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}

@@ -99,7 +99,7 @@ extern "C" int op_instnorm_finalize_tc(const float *stats_partial, const float *
 
 extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
                             const void *Wl, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
-                            int flags, int elu_cols, float *stats_partial, void *stream) {
+                            int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream) {
     using namespace opb;
     OPB_CHECK_ARG(A1h && A1l && Wh && Wl, "op_linear_tc: null operand plane");
     OPB_CHECK_ARG(K1 > 0 && K1 % lintc::BK == 0 && K2 >= 0 && K2 % lintc::BK == 0, "op_linear_tc: K1=%d K2=%d must be multiples of 64", K1, K2);
@@ -108,7 +108,9 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(C || Ch, "op_linear_tc: no output requested");
     OPB_CHECK_ARG((Ch == nullptr) == (Cl == nullptr), "op_linear_tc: Ch/Cl must come together");
     OPB_CHECK_ARG(!(flags & OPB_LIN_RESIDUAL) || C, "op_linear_tc: RESIDUAL needs the fp32 output");
-    OPB_CHECK_ARG(!(flags & OPB_LIN_STATS) || stats_partial, "op_linear_tc: STATS needs stats_partial");
+    OPB_CHECK_ARG(!(flags & (OPB_LIN_STATS | OPB_LIN_COLSUM)) || stats_partial, "op_linear_tc: STATS / COLSUM need stats_partial");
+    OPB_CHECK_ARG(!((flags & OPB_LIN_STATS) && (flags & OPB_LIN_COLSUM)), "op_linear_tc: STATS and COLSUM are exclusive");
+    OPB_CHECK_ARG(!(flags & OPB_LIN_ZSCALE) || (ksum && Cout == 256), "op_linear_tc: ZSCALE needs ksum and Cout == 256");
     OPB_CHECK_ARG(!(flags & OPB_LIN_NORM_RELU), "op_linear_tc: NORM_RELU is applied by op_norm_relu_split");
     OPB_CHECK_ARG(!(flags & OPB_LIN_ELU1) || elu_cols % 32 == 0, "op_linear_tc: elu_cols must be a multiple of 32");
     OPB_CHECK_ARG(B >= 0 && rows_per_batch >= 0, "op_linear_tc: bad B=%d rows=%d", B, rows_per_batch);
@@ -117,7 +119,8 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl;
     int rc;
     if ((rc = make_tmap_f16_3d(&ta1h, A1h, B, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, B, rows_per_batch, K1, lintc::BM)) ||
-        (rc = make_tmap_f16_3d(&twh, Wh, 1, Cout, K, lintc::BN)) || (rc = make_tmap_f16_3d(&twl, Wl, 1, Cout, K, lintc::BN)))
+        (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, lintc::BN)) ||
+        (rc = make_tmap_f16_3d(&twl, Wl, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, lintc::BN)))
         return rc;
     if (K2) {
         if ((rc = make_tmap_f16_3d(&ta2h, A2h, B, rows_per_batch, K2, lintc::BM)) || (rc = make_tmap_f16_3d(&ta2l, A2l, B, rows_per_batch, K2, lintc::BM)))
@@ -132,6 +135,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(total < (1ll << 31), "op_linear_tc: too many tiles");
     p.total_tiles = (int)total;
     p.bias = bias; p.C = C; p.Ch = (__half *)Ch; p.Cl = (__half *)Cl; p.stats = (float2 *)stats_partial;
+    p.ksum = ksum; p.zscale_num = zscale_num; p.w_batched = (flags & OPB_LIN_WBATCHED) ? 1 : 0;
     static bool configured = false;
     if (!configured) {
         OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::SMEM_BYTES));

@@ -35,7 +35,11 @@ struct Params {
     const float *bias;
     float *C;                      // fp32 [B, rows, Cout] or null
     __half *Ch, *Cl;               // planes [B, rows, Cout] (x64) or null
-    float2 *stats;                 // [B][row_tiles*4][Cout] (sum, sum of squares) of the PRE-BIAS result
+    float2 *stats;                 // [B][row_tiles*4][Cout] (sum, sum of squares) of the PRE-BIAS result (STATS) or
+                                   // (sum, 0) of the final value over the valid rows (COLSUM)
+    const float *ksum;             // ZSCALE: [B][Cout] per-frame Ksum; every 64-column head of a row is divided by (row_head . ksum_head + 1e-6)
+    float zscale_num;              // ZSCALE numerator: the source length M of :94,98 (z = M / (q.ksum + 1e-6))
+    int w_batched;                 // W planes are [B][Cout][K] (one matrix per frame)
 };
 
 struct Barriers {
@@ -126,10 +130,10 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     tc::mbar_wait(&bar->empty[stage], ph ^ 1);
                     tc::mbar_arrive_expect_tx(&bar->full_hi[stage], HALF_BYTES);
                     tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, b);
-                    tc::tma_load_3d(st + A_PLANE, &tm_wh, &bar->full_hi[stage], kb * BK, ct * BN, 0);
+                    tc::tma_load_3d(st + A_PLANE, &tm_wh, &bar->full_hi[stage], kb * BK, ct * BN, p.w_batched ? b : 0);
                     tc::mbar_arrive_expect_tx(&bar->full_lo[stage], HALF_BYTES);
                     tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, b);
-                    tc::tma_load_3d(st + HALF_BYTES + A_PLANE, &tm_wl, &bar->full_lo[stage], kb * BK, ct * BN, 0);
+                    tc::tma_load_3d(st + HALF_BYTES + A_PLANE, &tm_wl, &bar->full_lo[stage], kb * BK, ct * BN, p.w_batched ? b : 0);
                 }
             }
         }
@@ -182,52 +186,85 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             tc::mbar_wait(&bar->acc_full[as], aph);
             tc::tcgen05_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                const int ccol = half * 128 + c * 32;             // column inside the tile
+            for (int hh = 0; hh < 2; ++hh) {                      // 64 output columns (one attention head) per iteration
+                const int ccol = half * 128 + hh * 64;            // column inside the tile
                 const int col0 = ct * BN + ccol;                  // output column
-                float v[32];
-                tc::tmem_ld_32x32(lane_base + as * BN + ccol, v);
+                float v[2][32];
+                tc::tmem_ld_32x32(lane_base + as * BN + ccol, v[0]);
+                tc::tmem_ld_32x32(lane_base + as * BN + ccol + 32, v[1]);
                 tc::tmem_ld_wait();
-                if (c == 3) {                                     // this warp has drained its part of the accumulator
+                if (hh == 1) {                                    // this warp has drained its part of the accumulator
                     tc::tcgen05_fence_before();
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
                 }
+                float den = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] *= kInvScale2;
-                if (p.flags & OPB_LIN_STATS) {
-                    float s[32];
+                for (int cc = 0; cc < 2; ++cc) {
+                    float *vv = v[cc];
+                    const int c0 = col0 + cc * 32;
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) s[i] = v[i];     // rows past the end are exact zeros (TMA zero fill, no bias yet)
-                    const float cs = transpose_reduce_sum(s, lane);
+                    for (int i = 0; i < 32; ++i) vv[i] *= kInvScale2;
+                    if (p.flags & OPB_LIN_STATS) {
+                        float s[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) s[i] = v[i] * v[i];
-                    const float cq = transpose_reduce_sum(s, lane);
-                    p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + col0 + lane] = make_float2(cs, cq);
+                        for (int i = 0; i < 32; ++i) s[i] = vv[i];     // rows past the end are exact zeros (TMA zero fill, no bias yet)
+                        const float cs = transpose_reduce_sum(s, lane);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) s[i] = vv[i] * vv[i];
+                        const float cq = transpose_reduce_sum(s, lane);
+                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, cq);
+                    }
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const float4 bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
+                        vv[4 * q] += bq.x; vv[4 * q + 1] += bq.y; vv[4 * q + 2] += bq.z; vv[4 * q + 3] += bq.w;
+                    }
+                    if ((p.flags & OPB_LIN_ELU1) && c0 < p.elu_cols) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) vv[i] = vv[i] > 0.f ? vv[i] + 1.f : __expf(vv[i]);   // elu(x)+1
+                    }
+                    if (p.flags & OPB_LIN_COLSUM) {                // column sums of the final value over the valid rows (Ksum, :97)
+                        float s[32];
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
+                        const float cs = transpose_reduce_sum(s, lane);
+                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
+                    }
+                    if (p.flags & OPB_LIN_ZSCALE) {                // Q'_h . Ksum_h of this row (linear attention normaliser, :97)
+                        const float4 *ks = reinterpret_cast<const float4 *>(p.ksum + (long long)b * p.Cout + c0);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 k4 = __ldg(ks + q);
+                            den = fmaf(vv[4 * q], k4.x, den); den = fmaf(vv[4 * q + 1], k4.y, den);
+                            den = fmaf(vv[4 * q + 2], k4.z, den); den = fmaf(vv[4 * q + 3], k4.w, den);
+                        }
+                    }
                 }
+                if (p.flags & OPB_LIN_ZSCALE) {
+                    const float z = p.zscale_num / (den + 1e-6f);
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const float4 bq = *reinterpret_cast<const float4 *>(s_bias + col0 + 4 * q);
-                    v[4 * q] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
-                }
-                if ((p.flags & OPB_LIN_ELU1) && col0 < p.elu_cols) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] + 1.f : __expf(v[i]);   // elu(x)+1
+                    for (int i = 0; i < 32; ++i) { v[0][i] *= z; v[1][i] *= z; }
                 }
                 if (row_ok) {
-                    if (p.C) {
-                        float4 *dst = reinterpret_cast<float4 *>(p.C + grow * p.Cout + col0);
-                        if (p.flags & OPB_LIN_RESIDUAL) {
 #pragma unroll
-                            for (int q = 0; q < 8; ++q) {
-                                const float4 o = dst[q];
-                                v[4 * q] += o.x; v[4 * q + 1] += o.y; v[4 * q + 2] += o.z; v[4 * q + 3] += o.w;
+                    for (int cc = 0; cc < 2; ++cc) {
+                        float *vv = v[cc];
+                        const int c0 = col0 + cc * 32;
+                        if (p.C) {
+                            float4 *dst = reinterpret_cast<float4 *>(p.C + grow * p.Cout + c0);
+                            if (p.flags & OPB_LIN_RESIDUAL) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) {
+                                    const float4 o = dst[q];
+                                    vv[4 * q] += o.x; vv[4 * q + 1] += o.y; vv[4 * q + 2] += o.z; vv[4 * q + 3] += o.w;
+                                }
                             }
-                        }
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                            for (int q = 0; q < 8; ++q) dst[q] = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
+                        }
+                        if (p.Ch) store_planes32(vv, p.Ch + grow * p.Cout + c0, p.Cl + grow * p.Cout + c0);
                     }
-                    if (p.Ch) store_planes32(v, p.Ch + grow * p.Cout + col0, p.Cl + grow * p.Cout + col0);
                 }
             }
         }

@@ -149,7 +149,8 @@ class GATsSuperGlue(nn.Module):
                 wq, wk, wv = (f(at.proj[j].weight[:, :, 0])[perm] for j in range(3))
                 bq, bk, bv = (f(at.proj[j].bias)[perm] for j in range(3))
                 packed.append(dict(
-                    kind=kind, Wq=wq.contiguous(), bq=bq.contiguous(),
+                    kind=kind, Wq=wq.contiguous(), bq=bq.contiguous(), Wk=wk.contiguous(), bk=bk.contiguous(),
+                    Wv=wv.contiguous(), bv=bv.contiguous(),
                     Wkv=torch.cat([wk, wv], 0).contiguous(), bkv=torch.cat([bk, bv], 0).contiguous(),
                     Wm=f(at.merge.weight[:, :, 0])[:, perm].contiguous(), bm=f(at.merge.bias),
                     W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias),
@@ -158,7 +159,7 @@ class GATsSuperGlue(nn.Module):
         # split-precision fp16 planes of every projection weight for the tcgen05 path (linear_tc.cuh)
         with torch.cuda.device(device):
             for lw in packed:
-                for k in ("Wq", "Wkv", "Wm", "W0", "W1"):
+                for k in ("Wq", "Wk", "Wkv", "Wm", "W0", "W1"):
                     if k in lw:
                         lw[k + "_p"] = self._split_new(lw[k])
             self._packed["Wf_p"] = self._split_new(self._packed["Wf"])
@@ -249,36 +250,47 @@ class GATsSuperGlue(nn.Module):
         self._linear(h, lw["W1"], lw["b1"], x, B, N, flags=2 | 8, mean=mean, rstd=rstd, tag="mlp1")   # NORM_RELU in, RESIDUAL out
 
     # ------------------------------------------------------------------ tcgen05 launchers (linear_tc.cuh)
-    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, tag=""):
+    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, ksum=None, zscale_num=1.0, tag=""):
         """A1/A2/W/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp."""
         K1 = A1[0].shape[-1]
         K2 = 0 if A2 is None else A2[0].shape[-1]
-        Cout = W[0].shape[0]
+        Cout = W[0].shape[-2]
         timeline.work = 2.0 * B * rows * (K1 + K2) * Cout
         call("op_linear_tc", ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
              ptr(W[0]), ptr(W[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
-             B, rows, Cout, flags, elu_cols, ptr(stats), stream_ptr(), tag=tag)
+             B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr(), tag=tag)
 
     def _kv_tc(self, src_p, B, M, lw, tag):
+        """Source side of linear attention (:90-97) re-associated for the tensor cores (atb_tc.cu): K' projection with
+        column sums, G = K'^T X, then per frame Ksum and P_b = blockdiag(KV') Wm^T.  Returns (ksum, P_b planes)."""
         dev = src_p[0].device
-        kv = self._ws.get(f"kv{M}", (B, M, 2 * _D), torch.float32, dev)
-        self._linear_tc(src_p, lw["Wkv_p"], lw["bkv"], B, M, C=kv, flags=1, elu_cols=_D, tag="kv")
-        KV = self._ws.get("KV" + tag, (B, _HEADS, 64, 64), torch.float32, dev)
-        Ks = self._ws.get("Ks" + tag, (B, _HEADS, 64), torch.float32, dev)
-        nbytes = lib.op_kv_reduce_workspace_bytes(B, M)
-        w = self._ws.get(f"kvws{M}", (nbytes,), torch.uint8, dev)
-        call("op_kv_reduce", ptr(kv), ptr(KV), ptr(Ks), B, M, ptr(w), nbytes, stream_ptr())
-        return KV, Ks
+        kp = self._planes(f"kp{M}", (B, M, _D), dev)
+        parts = lib.op_linear_tc_stat_parts(M)
+        ks_part = self._ws.get(f"kspart{M}", (B, parts, _D, 2), torch.float32, dev)
+        self._linear_tc(src_p, lw["Wk_p"], lw["bk"], B, M, Cp=kp, flags=1 | 16, elu_cols=_D, stats=ks_part, tag="k")   # ELU1 | COLSUM
+        nch = lib.op_atb_chunks(M)
+        part = self._ws.get(f"gpart{M}", (B, nch, _D, _D), torch.float32, dev)
+        timeline.work = 2.0 * B * M * _D * _D
+        call("op_atb_tc", ptr(kp[0]), ptr(kp[1]), ptr(src_p[0]), ptr(src_p[1]), B, M, ptr(part), stream_ptr())
+        ksum = self._ws.get("ksum" + tag, (B, _D), torch.float32, dev)
+        P = self._planes("P" + tag, (B, _D, _D), dev)
+        call("op_kv_post", ptr(part), nch, ptr(ks_part), parts, ptr(lw["Wv"]), ptr(lw["bv"]), ptr(lw["Wm"]), B, 1.0 / M, ptr(ksum), None,
+             ptr(P[0]), ptr(P[1]), stream_ptr())
+        return ksum, P
 
-    def _propagate_tc(self, x, x_p, B, N, M, KV, Ks, lw):
-        """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place."""
+    def _propagate_tc(self, x, x_p, B, N, M, ksum, P, lw):
+        """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place.
+        message = (Q' / (Q'_h . Ksum_h + 1e-6)) P_b^T + bm  ==  merge(linear_attention(q, k, v))  (:98, :119)."""
         dev = x.device
-        q = self._ws.get(f"q{N}", (B, N, _D), torch.float32, dev)
-        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, C=q, flags=1, elu_cols=_D, tag="q")
-        att_p = self._planes(f"att{N}", (B, N, _D), dev)
-        call("op_attn_apply_planes", ptr(q), ptr(KV), ptr(Ks), ptr(att_p[0]), ptr(att_p[1]), B, N, M, stream_ptr())
+        q_p = self._planes(f"q{N}", (B, N, _D), dev)
+        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 32, elu_cols=_D, ksum=ksum, zscale_num=M, tag="q")     # ELU1 | ZSCALE
         msg_p = self._planes(f"msg{N}", (B, N, _D), dev)
-        self._linear_tc(att_p, lw["Wm_p"], lw["bm"], B, N, Cp=msg_p, tag="merge")
+        self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=64, tag="merge")                                    # WBATCHED
+        self._mlp_tc(x, x_p, msg_p, B, N, lw)
+
+    def _mlp_tc(self, x, x_p, msg_p, B, N, lw):
+        """MLP([x | message]) with InstanceNorm + ReLU and the residual add (:135-147, :78,83)."""
+        dev = x.device
         h = self._ws.get(f"h{N}", (B, N, 2 * _D), torch.float32, dev)
         parts = lib.op_linear_tc_stat_parts(N)
         stats = self._ws.get(f"tcstats{N}", (B, parts, 2 * _D, 2), torch.float32, dev)

@@ -23,19 +23,19 @@ def _unsplit(p):
     return (p[0].double() + p[1].double()) / 64.0
 
 
-def _linear_tc(A1, W, bias, *, A2=None, want_c=True, want_planes=False, flags=0, elu_cols=0, C_init=None):
+def _linear_tc(A1, W, bias, *, A2=None, want_c=True, want_planes=False, flags=0, elu_cols=0, C_init=None, ksum=None, zscale_num=1.0):
     from onepose_b200._lib import call, lib, ptr, stream_ptr
     B, rows, K1 = A1.shape
-    Cout = W.shape[0]
+    Cout = W.shape[-2]
     a1 = _planes(A1); w = _planes(W)
     a2 = _planes(A2) if A2 is not None else None
     C = (C_init.clone() if C_init is not None else torch.full((B, rows, Cout), float("nan"), device="cuda")) if want_c else None
     Cp = (torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda"), torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda")) if want_planes else None
     parts = lib.op_linear_tc_stat_parts(rows)
-    stats = torch.full((B, parts, Cout, 2), float("nan"), device="cuda") if flags & 4 else None
+    stats = torch.full((B, parts, Cout, 2), float("nan"), device="cuda") if flags & (4 | 16) else None
     call("op_linear_tc", ptr(a1[0]), ptr(a1[1]), K1, ptr(a2[0]) if a2 else None, ptr(a2[1]) if a2 else None,
          0 if A2 is None else A2.shape[2], ptr(w[0]), ptr(w[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None,
-         ptr(Cp[1]) if Cp else None, B, rows, Cout, flags, elu_cols, ptr(stats), stream_ptr())
+         ptr(Cp[1]) if Cp else None, B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr())
     torch.cuda.synchronize()
     return C, Cp, stats
 
@@ -118,3 +118,59 @@ def test_matcher_tensor_core_path_vs_cuda_core_path(damped):
     assert helpers.conf_rel_err(conf_tc.cpu(), conf_cc.cpu()) < helpers.CONF_RTOL
     for b in range(2):
         helpers.assert_matches_equal_off_ties(m0_tc[b].cpu(), pred_cc["matches0_batched"][b].cpu(), conf_cc[b].cpu(), axis=2)
+
+
+@pytest.mark.parametrize("shape", [(1, 512), (2, 700), (3, 33), (1, 2048)])
+def test_atb_tc_and_kv_post_vs_float64_linear_attention(shape):
+    """G = K'^T X on MN-major UMMA operands, then KV' / Ksum / P_b against a float64 restatement of :88-99,119."""
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    B, M = shape
+    g = torch.Generator().manual_seed(M)
+    X = (torch.randn(B, M, 256, generator=g) * 0.2).cuda()
+    Kp = (torch.rand(B, M, 256, generator=g) * 2).cuda()              # elu+1 > 0
+    nch = lib.op_atb_chunks(M)
+    part = torch.full((B, nch, 256, 256), float("nan"), device="cuda")
+    kp, xp = _planes(Kp), _planes(X)
+    call("op_atb_tc", ptr(kp[0]), ptr(kp[1]), ptr(xp[0]), ptr(xp[1]), B, M, ptr(part), stream_ptr())
+    torch.cuda.synchronize()
+    G = part.double().sum(1)
+    G_ref = Kp.double().transpose(1, 2) @ X.double()
+    assert _rel(G, G_ref) < 5e-6
+    # post: Ksum partials as OPB_LIN_COLSUM would write them (one part per 32 rows here), KV', P_b
+    Wv = (torch.randn(256, 256, generator=g) / 16).cuda(); bv = (torch.randn(256, generator=g) * 0.1).cuda()
+    Wm = (torch.randn(256, 256, generator=g) / 16).cuda()
+    nparts = (M + 31) // 32
+    pad = torch.zeros(B, nparts * 32, 256, device="cuda"); pad[:, :M] = Kp
+    ks_part = torch.stack([pad.view(B, nparts, 32, 256).sum(2), torch.zeros(B, nparts, 256, device="cuda")], -1).contiguous()
+    ksum = torch.empty(B, 256, device="cuda"); kv = torch.empty(B, 4, 64, 64, device="cuda")
+    Ph = torch.empty(B, 256, 256, dtype=torch.float16, device="cuda"); Pl = torch.empty_like(Ph)
+    call("op_kv_post", ptr(part), nch, ptr(ks_part), nparts, ptr(Wv), ptr(bv), ptr(Wm), B, 1.0 / M, ptr(ksum), ptr(kv), ptr(Ph), ptr(Pl), stream_ptr())
+    torch.cuda.synchronize()
+    V = X.double() @ Wv.double().t() + bv.double()
+    Kh = Kp.double().view(B, M, 4, 64); Vh = V.view(B, M, 4, 64)
+    KV_ref = torch.einsum("bmhd,bmhq->bhdq", Kh, Vh) / M
+    ks_ref = Kp.double().sum(1)
+    assert _rel(ksum, ks_ref) < 2e-6
+    assert _rel(kv, KV_ref) < 1e-5
+    P_ref = torch.einsum("bhdq,ohq->bohd", KV_ref, Wm.double().view(256, 4, 64)).reshape(B, 256, 256)
+    assert _rel(_unsplit((Ph, Pl)), P_ref) < 1e-5
+
+
+def test_q_projection_with_zscale_and_per_frame_merge_equals_attention_readout():
+    """OPB_LIN_ZSCALE + OPB_LIN_WBATCHED + OPB_LIN_COLSUM against the reference read-out (:97-98,119)."""
+    B, N = 2, 300
+    g = torch.Generator().manual_seed(9)
+    X = (torch.randn(B, N, 256, generator=g) * 0.2).cuda()
+    Wq = (torch.randn(256, 256, generator=g) / 16).cuda(); bq = (torch.randn(256, generator=g) * 0.1).cuda()
+    ksum = (torch.rand(B, 256, generator=g) * 50 + 1).cuda()
+    P = (torch.randn(B, 256, 256, generator=g) / 16).cuda(); bm = (torch.randn(256, generator=g) * 0.1).cuda()
+    _, Qp, st = _linear_tc(X, Wq, bq, want_c=False, want_planes=True, flags=1 | 16 | 32, elu_cols=256, ksum=ksum, zscale_num=777.0)
+    q1 = torch.nn.functional.elu(X.double() @ Wq.double().t() + bq.double()) + 1
+    den = (q1.view(B, N, 4, 64) * ksum.double().view(B, 1, 4, 64)).sum(-1, keepdim=True) + 1e-6
+    # COLSUM sums the activation (after bias / elu+1, before the ZSCALE division) over the valid rows
+    q2 = (q1.view(B, N, 4, 64) * 777.0 / den).reshape(B, N, 256)
+    assert _rel(_unsplit(Qp), q2) < 5e-6
+    np.testing.assert_allclose(st[..., 0].double().sum(1).cpu().numpy(), q1.sum(1).cpu().numpy(), rtol=1e-5)
+    msg, _, _ = _linear_tc(q2.float(), P, bm, flags=64)
+    ref = torch.einsum("bnk,bok->bno", q2, P.double()) + bm.double()
+    assert _rel(msg, ref) < 5e-6
