@@ -24,7 +24,7 @@ constexpr int STAGE_BYTES = 4 * PLANE;         // A hi, A lo, B hi, B lo = 65536
 constexpr int STAGES = 3;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;
 constexpr int THREADS = 320;
-constexpr int kChunk = 512;                    // points per CTA
+constexpr int kChunk = 1024;                   // points per CTA
 
 struct Barriers { uint64_t full[STAGES], empty[STAGES], acc_full; uint32_t tmem_base; };
 
@@ -137,70 +137,95 @@ k_atb_tc(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUte
 namespace opb {
 namespace atb {
 
-// per (head h, frame b): G_h = sum of chunk partials; Ksum_h = sum of column-sum partials; KV'_h = G_h Wv_h^T + Ksum_h bv_h^T;
-// P_b[o, h*64+d] = sum_q KV'_h[d,q] Wm[o, h*64+q] written as split-precision planes (x64).  All folds in a fixed order.
+// per (head h, frame b, group of 16 channels d): G = sum of chunk partials; Ksum = sum of column-sum partials;
+// KV_h[d,:] = (G_h[d,:] Wv_h^T + Ksum_h[d] bv_h^T) / M;  P_b[o, h*64+d] = sum_q KV_h[d,q] Wm[o, h*64+q] written as
+// split-precision planes (x64).  All folds in a fixed order.
+constexpr int kPostD = 16;
 __global__ void __launch_bounds__(256)
 k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
           const float *__restrict__ Wv /* [256][256] head-major rows */, const float *__restrict__ bv,
           const float *__restrict__ Wm /* [256][256] head-major columns */, float inv_m, float *__restrict__ ksum /* [B][256] */,
           float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
-    extern __shared__ float sm[];
-    float *G = sm;                     // [64][256]
-    float *KV = sm + 64 * 256;         // [64][65]
-    float *Ks = KV + 64 * 65;          // [64]
-    const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-    for (int e = tid; e < 64 * 256; e += 256) {
-        const int d = e >> 8, c = e & 255;
-        float s = 0.f;
-        for (int k = 0; k < nchunks; ++k) s += partial[(((long long)b * nchunks + k) * 256 + h * 64 + d) * 256 + c];
-        G[e] = s;
+    __shared__ float G[kPostD][256];
+    __shared__ float KV[kPostD][65];
+    __shared__ float Ks[kPostD];
+    __shared__ double Kslice[16][kPostD];
+    const int h = blockIdx.x, dg = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
+    const int ch0 = h * 64 + dg * kPostD;                       // first K' channel of this block
+    {   // G fold: thread = column c, 16 independent loads in flight per chunk; chunks summed in order
+        float acc[kPostD];
+#pragma unroll
+        for (int d = 0; d < kPostD; ++d) acc[d] = 0.f;
+        for (int k = 0; k < nchunks; ++k) {
+            const float *src = partial + (((long long)b * nchunks + k) * 256 + ch0) * 256 + tid;
+#pragma unroll
+            for (int d = 0; d < kPostD; ++d) acc[d] += __ldg(src + d * 256);
+        }
+#pragma unroll
+        for (int d = 0; d < kPostD; ++d) G[d][tid] = acc[d];
     }
-    if (tid < 64) {
+    {   // Ksum fold: 16 slices of the partial list per channel in float64, then the slices in order
+        const int d = tid & (kPostD - 1), slice = tid / kPostD;              // 16 slices
+        const int per = (nparts + 15) / 16, k0 = slice * per, k1 = min(nparts, k0 + per);
         double s = 0;
-        for (int k = 0; k < nparts; ++k) s += (double)ksum_part[((long long)b * nparts + k) * 256 + h * 64 + tid].x;
-        Ks[tid] = (float)s;
-        ksum[(long long)b * 256 + h * 64 + tid] = (float)s;
+        for (int k = k0; k < k1; ++k) s += (double)__ldg(&ksum_part[((long long)b * nparts + k) * 256 + ch0 + d].x);
+        Kslice[slice][d] = s;
     }
     __syncthreads();
-    {   // KV'[d][q]: thread = (q, group of 16 d)
-        const int q = tid & 63, d0 = (tid >> 6) * 16;
-        float acc[16];
+    if (tid < kPostD) {
+        double s = 0;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+        for (int k = 0; k < 16; ++k) s += Kslice[k][tid];
+        Ks[tid] = (float)s;
+        ksum[(long long)b * 256 + ch0 + tid] = (float)s;
+    }
+    __syncthreads();
+    {   // KV[d][q]: thread = (q, group of 4 d)
+        const int q = tid & 63, d0 = (tid >> 6) * 4;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
         const float *w = Wv + (long long)(h * 64 + q) * 256;
-        for (int c = 0; c < 256; ++c) {
-            const float wc = __ldg(w + c);
+        for (int c = 0; c < 256; c += 4) {
+            const float4 w4 = __ldg(reinterpret_cast<const float4 *>(w + c));
 #pragma unroll
-            for (int i = 0; i < 16; ++i) acc[i] = fmaf(G[(d0 + i) * 256 + c], wc, acc[i]);
+            for (int i = 0; i < 4; ++i) {
+                acc[i] = fmaf(G[d0 + i][c], w4.x, acc[i]); acc[i] = fmaf(G[d0 + i][c + 1], w4.y, acc[i]);
+                acc[i] = fmaf(G[d0 + i][c + 2], w4.z, acc[i]); acc[i] = fmaf(G[d0 + i][c + 3], w4.w, acc[i]);
+            }
         }
         const float bq = bv[h * 64 + q];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
+        for (int i = 0; i < 4; ++i) {
             const float v = fmaf(Ks[d0 + i], bq, acc[i]) * inv_m;        // value / v_length, :93-94
-            KV[(d0 + i) * 65 + q] = v;
-            if (kv_out) kv_out[(((long long)b * 4 + h) * 64 + d0 + i) * 64 + q] = v;
+            KV[d0 + i][q] = v;
+            if (kv_out) kv_out[(((long long)b * 4 + h) * 64 + dg * kPostD + d0 + i) * 64 + q] = v;
         }
     }
     __syncthreads();
-    {   // P[o][h*64 + d], thread = o
+    {   // P[o][ch0 + d], thread = o
         const int o = tid;
         float wm[64];
 #pragma unroll
-        for (int q = 0; q < 64; ++q) wm[q] = __ldg(Wm + (long long)o * 256 + h * 64 + q);
-        __half *ph = Ph + ((long long)b * 256 + o) * 256 + h * 64, *pl = Pl + ((long long)b * 256 + o) * 256 + h * 64;
-        for (int d = 0; d < 64; d += 2) {
+        for (int q = 0; q < 64; q += 4) {
+            const float4 w4 = __ldg(reinterpret_cast<const float4 *>(Wm + (long long)o * 256 + h * 64 + q));
+            wm[q] = w4.x; wm[q + 1] = w4.y; wm[q + 2] = w4.z; wm[q + 3] = w4.w;
+        }
+        uint32_t hh[kPostD / 2], ll[kPostD / 2];
+#pragma unroll
+        for (int d = 0; d < kPostD; d += 2) {
             float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-            for (int q = 0; q < 64; ++q) { a0 = fmaf(KV[d * 65 + q], wm[q], a0); a1 = fmaf(KV[(d + 1) * 65 + q], wm[q], a1); }
+            for (int q = 0; q < 64; ++q) { a0 = fmaf(KV[d][q], wm[q], a0); a1 = fmaf(KV[d + 1][q], wm[q], a1); }
             __half h0, l0, h1, l1;
             tc::split_f16(a0 * 64.f, h0, l0); tc::split_f16(a1 * 64.f, h1, l1);
-            *reinterpret_cast<__half2 *>(ph + d) = __halves2half2(h0, h1);
-            *reinterpret_cast<__half2 *>(pl + d) = __halves2half2(l0, l1);
+            hh[d / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+            ll[d / 2] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
         }
+        uint4 *ph = reinterpret_cast<uint4 *>(Ph + ((long long)b * 256 + o) * 256 + ch0);
+        uint4 *pl = reinterpret_cast<uint4 *>(Pl + ((long long)b * 256 + o) * 256 + ch0);
+        ph[0] = make_uint4(hh[0], hh[1], hh[2], hh[3]); ph[1] = make_uint4(hh[4], hh[5], hh[6], hh[7]);
+        pl[0] = make_uint4(ll[0], ll[1], ll[2], ll[3]); pl[1] = make_uint4(ll[4], ll[5], ll[6], ll[7]);
     }
 }
-
-constexpr int kPostSmem = (64 * 256 + 64 * 65 + 64) * 4;
 
 }  // namespace atb
 }  // namespace opb
@@ -219,7 +244,6 @@ extern "C" int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const v
     static bool configured = false;
     if (!configured) {
         OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_atb_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::SMEM_BYTES));
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_kv_post, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::kPostSmem));
         configured = true;
     }
     const int nchunks = ceil_div(M, atb::kChunk);
@@ -233,12 +257,7 @@ extern "C" int op_kv_post(const float *partial, int nchunks, const float *ksum_p
     using namespace opb;
     OPB_CHECK_ARG(partial && ksum_partial && Wv && bv && Wm && ksum && Ph && Pl, "op_kv_post: null pointer");
     OPB_CHECK_ARG(B > 0 && nchunks > 0 && nparts > 0 && B <= 65535, "op_kv_post: bad shape");
-    static bool configured = false;
-    if (!configured) {
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_kv_post, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::kPostSmem));
-        configured = true;
-    }
-    atb::k_kv_post<<<dim3(4, B), 256, atb::kPostSmem, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, Wv, bv, Wm,
+    atb::k_kv_post<<<dim3(4, 64 / atb::kPostD, B), 256, 0, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, Wv, bv, Wm,
                                                                             inv_m, ksum, kv_out, (__half *)Ph, (__half *)Pl);
     OPB_CHECK_LAUNCH();
     return OPB_OK;

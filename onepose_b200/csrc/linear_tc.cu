@@ -116,7 +116,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(B >= 0 && rows_per_batch >= 0, "op_linear_tc: bad B=%d rows=%d", B, rows_per_batch);
     if (B == 0 || rows_per_batch == 0) return OPB_OK;
     const int K = K1 + K2;
-    CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl;
+    CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl, tc_, tch, tcl;
     int rc;
     if ((rc = make_tmap_f16_3d(&ta1h, A1h, B, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, B, rows_per_batch, K1, lintc::BM)) ||
         (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, lintc::BN)) ||
@@ -128,6 +128,11 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     } else {
         ta2h = ta1h; ta2l = ta1l;
     }
+    OPB_CHECK_ARG(((uintptr_t)C | (uintptr_t)Ch | (uintptr_t)Cl) % 16 == 0, "op_linear_tc: outputs must be 16-byte aligned");
+    if (C) { if ((rc = make_tmap_f32_3d_store(&tc_, C, B, rows_per_batch, Cout, 32))) return rc; } else tc_ = ta1h;
+    if (Ch) {
+        if ((rc = make_tmap_f16_3d_store(&tch, Ch, B, rows_per_batch, Cout, 32)) || (rc = make_tmap_f16_3d_store(&tcl, Cl, B, rows_per_batch, Cout, 32))) return rc;
+    } else { tch = ta1h; tcl = ta1h; }
     lintc::Params p{};
     p.B = B; p.rows = rows_per_batch; p.Cout = Cout; p.K1 = K1; p.K2 = K2; p.flags = flags; p.elu_cols = elu_cols;
     p.row_tiles = ceil_div(rows_per_batch, lintc::BM); p.col_tiles = Cout / lintc::BN;
@@ -142,7 +147,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
         configured = true;
     }
     const int grid = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
-    lintc::k_linear_tc<<<grid, lintc::THREADS, lintc::SMEM_BYTES, (cudaStream_t)stream>>>(ta1h, ta1l, ta2h, ta2l, twh, twl, p);
+    lintc::k_linear_tc<<<grid, lintc::THREADS, lintc::SMEM_BYTES, (cudaStream_t)stream>>>(ta1h, ta1l, ta2h, ta2l, twh, twl, tc_, tch, tcl, p);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

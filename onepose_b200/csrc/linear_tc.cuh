@@ -24,8 +24,10 @@ constexpr int W_PLANE = BN * BK * 2;                  // 32768
 constexpr int HALF_BYTES = A_PLANE + W_PLANE;         // one precision half of a stage (49152)
 constexpr int STAGE_BYTES = 2 * HALF_BYTES;           // 98304
 constexpr int BIAS_FLOATS = 512;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BIAS_FLOATS * 4 + 256 + 1024;
 constexpr int EPI_WARPS = 8, THREADS = (EPI_WARPS + 2) * 32;
+constexpr int STG_BUF = 32 * 64;                      // TMA-store staging buffer: 32 rows x 64 bytes (16 fp32 or 32 fp16 columns)
+constexpr int STG_BYTES = EPI_WARPS * 2 * STG_BUF;    // two per epilogue warp = 32768
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STG_BYTES + BIAS_FLOATS * 4 + 256;   // 231680 of 232448; base must be 1024-aligned
 constexpr float kScale = 64.f;                        // activations and weights are stored as 64*x
 constexpr float kInvScale2 = 1.f / (kScale * kScale);
 
@@ -66,33 +68,31 @@ __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
     return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
 }
 
-// 32 fp32 values -> 32 (hi, lo) fp16 pairs of 64*x, stored as 64 contiguous bytes per plane
-__device__ __forceinline__ void store_planes32(const float *v, __half *hi_dst, __half *lo_dst) {
-    uint32_t h[16], l[16];
+// 32 fp32 values ALREADY scaled by 64 -> 32 (hi, lo) fp16 pairs, 64 bytes per plane (packed cvt.rn.f16x2.f32)
+__device__ __forceinline__ void split_planes32(const float *vs, uint32_t *h, uint32_t *l) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-        __half h0, l0, h1, l1;
-        tc::split_f16(v[2 * i] * kScale, h0, l0);
-        tc::split_f16(v[2 * i + 1] * kScale, h1, l1);
-        h[i] = pack_h2(h0, h1);
-        l[i] = pack_h2(l0, l1);
-    }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        reinterpret_cast<uint4 *>(hi_dst)[q] = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
-        reinterpret_cast<uint4 *>(lo_dst)[q] = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
+        const __half2 hi = __floats2half2_rn(vs[2 * i], vs[2 * i + 1]);
+        const float2 hf = __half22float2(hi);
+        const __half2 lo = __floats2half2_rn(vs[2 * i] - hf.x, vs[2 * i + 1] - hf.y);
+        h[i] = *reinterpret_cast<const uint32_t *>(&hi);
+        l[i] = *reinterpret_cast<const uint32_t *>(&lo);
     }
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
 k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ CUtensorMap tm_a1l,
             const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
-            const __grid_constant__ CUtensorMap tm_wh, const __grid_constant__ CUtensorMap tm_wl, const Params p) {
-    extern __shared__ uint8_t smem_raw[];
-    // 1024-byte alignment (SWIZZLE_128B) by an offset on the shared array, so accesses stay in the shared address space (LDS/STS)
-    uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
-    float *s_bias = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES);
-    Barriers *bar = reinterpret_cast<Barriers *>(smem + STAGES * STAGE_BYTES + BIAS_FLOATS * 4);
+            const __grid_constant__ CUtensorMap tm_wh, const __grid_constant__ CUtensorMap tm_wl,
+            const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_ch, const __grid_constant__ CUtensorMap tm_cl,
+            const Params p) {
+    // SWIZZLE_128B operands need a 1024-byte aligned base: the dynamic shared window of a kernel without static shared memory
+    // starts at offset 0; checked below (every byte of the 227 KB is in use, there is no slack to re-align).
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (tc::smem_u32(smem) & 1023u) __trap();
+    uint8_t *s_stg = smem + STAGES * STAGE_BYTES;
+    float *s_bias = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES + STG_BYTES);
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + STAGES * STAGE_BYTES + STG_BYTES + BIAS_FLOATS * 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nkb1 = p.K1 / BK, nkb = (p.K1 + p.K2) / BK;
@@ -102,11 +102,13 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], EPI_WARPS); }
         tc::fence_barrier_init();
     }
-    for (int i = threadIdx.x; i < BIAS_FLOATS; i += THREADS) s_bias[i] = (p.bias && i < p.Cout) ? p.bias[i] : 0.f;
+    for (int i = threadIdx.x; i < BIAS_FLOATS; i += THREADS) s_bias[i] = (p.bias && i < p.Cout) ? kScale * p.bias[i] : 0.f;     // bias in the x64 domain of the planes
     if (warp == 9) tc::tmem_alloc<512>(&bar->tmem_base);
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_a1h); tc::tma_prefetch_desc(&tm_a1l); tc::tma_prefetch_desc(&tm_wh); tc::tma_prefetch_desc(&tm_wl);
         if (p.K2) { tc::tma_prefetch_desc(&tm_a2h); tc::tma_prefetch_desc(&tm_a2l); }
+        if (p.C) tc::tma_prefetch_desc(&tm_c);
+        if (p.Ch) { tc::tma_prefetch_desc(&tm_ch); tc::tma_prefetch_desc(&tm_cl); }
     }
     tc::tcgen05_fence_before();
     __syncthreads();
@@ -176,6 +178,20 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         // ================= epilogue (warps 0-7) =================
         const int quad = warp & 3, half = warp >> 2;
         const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+        // Coalesced output: 32 rows x 64 bytes are staged in (64-byte swizzled) shared memory and leave through one TMA store;
+        // rows past the end are clipped by the TMA unit.  Two staging buffers per warp, at most one store still reading.
+        uint32_t nst = 0;
+        auto stage_store = [&](const CUtensorMap *tm, int col, const uint4 *data, int bb, int r0) {
+            uint8_t *buf = s_stg + (warp * 2 + (nst & 1)) * STG_BUF;
+            if (lane == 0) tc::tma_store_wait_read1();
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4 *>(buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) = data[q];
+            tc::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) { tc::tma_store_3d(tm, buf, col, r0, bb); tc::tma_store_commit(); }
+            ++nst;
+        };
         int j = 0;
         for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
             int b, rt, ct; decode(t, b, rt, ct);
@@ -183,6 +199,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             const int row = rt * BM + quad * 32 + lane;
             const bool row_ok = row < p.rows;
             const long long grow = (long long)b * p.rows + (row_ok ? row : 0);
+            const int row0 = rt * BM + quad * 32;
             tc::mbar_wait(&bar->acc_full[as], aph);
             tc::tcgen05_fence_after();
 #pragma unroll 1
@@ -198,37 +215,41 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
                 }
+                // The epilogue math runs on vs = 64 * value (the scale of the output planes): acc holds 4096 * value.
                 float den = 0.f;
 #pragma unroll
                 for (int cc = 0; cc < 2; ++cc) {
                     float *vv = v[cc];
                     const int c0 = col0 + cc * 32;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) vv[i] *= kInvScale2;
                     if (p.flags & OPB_LIN_STATS) {
                         float s[32];
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) s[i] = vv[i];     // rows past the end are exact zeros (TMA zero fill, no bias yet)
+                        for (int i = 0; i < 32; ++i) s[i] = vv[i] * kInvScale2;     // rows past the end are exact zeros (TMA zero fill, no bias yet)
                         const float cs = transpose_reduce_sum(s, lane);
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) s[i] = vv[i] * vv[i];
+                        for (int i = 0; i < 32; ++i) { const float t = vv[i] * kInvScale2; s[i] = t * t; }
                         const float cq = transpose_reduce_sum(s, lane);
                         p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, cq);
                     }
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
                         const float4 bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
-                        vv[4 * q] += bq.x; vv[4 * q + 1] += bq.y; vv[4 * q + 2] += bq.z; vv[4 * q + 3] += bq.w;
+                        vv[4 * q] = fmaf(vv[4 * q], 1.f / kScale, bq.x); vv[4 * q + 1] = fmaf(vv[4 * q + 1], 1.f / kScale, bq.y);
+                        vv[4 * q + 2] = fmaf(vv[4 * q + 2], 1.f / kScale, bq.z); vv[4 * q + 3] = fmaf(vv[4 * q + 3], 1.f / kScale, bq.w);
                     }
                     if ((p.flags & OPB_LIN_ELU1) && c0 < p.elu_cols) {
+                        // 64 * (elu(x) + 1) = x > 0 ? vs + 64 : 64 exp(vs / 64) = ex2(vs * log2(e) / 64 + 6)
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) vv[i] = vv[i] > 0.f ? vv[i] + 1.f : __expf(vv[i]);   // elu(x)+1
+                        for (int i = 0; i < 32; ++i) {
+                            const float e = tc::ex2(fmaf(vv[i], 1.4426950408889634f / kScale, 6.f));
+                            vv[i] = vv[i] > 0.f ? vv[i] + kScale : e;
+                        }
                     }
-                    if (p.flags & OPB_LIN_COLSUM) {                // column sums of the final value over the valid rows (Ksum, :97)
+                    if (p.flags & OPB_LIN_COLSUM) {                // column sums of the value over the valid rows (Ksum, :97)
                         float s[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
-                        const float cs = transpose_reduce_sum(s, lane);
+                        const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
                         p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
                     }
                     if (p.flags & OPB_LIN_ZSCALE) {                // Q'_h . Ksum_h of this row (linear attention normaliser, :97)
@@ -242,32 +263,43 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     }
                 }
                 if (p.flags & OPB_LIN_ZSCALE) {
-                    const float z = p.zscale_num / (den + 1e-6f);
+                    const float z = p.zscale_num / (den * (1.f / kScale) + 1e-6f);
 #pragma unroll
                     for (int i = 0; i < 32; ++i) { v[0][i] *= z; v[1][i] *= z; }
                 }
-                if (row_ok) {
 #pragma unroll
-                    for (int cc = 0; cc < 2; ++cc) {
-                        float *vv = v[cc];
-                        const int c0 = col0 + cc * 32;
-                        if (p.C) {
-                            float4 *dst = reinterpret_cast<float4 *>(p.C + grow * p.Cout + c0);
-                            if (p.flags & OPB_LIN_RESIDUAL) {
+                for (int cc = 0; cc < 2; ++cc) {
+                    float *vv = v[cc];
+                    const int c0 = col0 + cc * 32;
+                    if (p.C) {
+                        if (p.flags & OPB_LIN_RESIDUAL) {            // x64 domain: vs += 64 * old
+                            if (row_ok) {
+                                const float4 *src = reinterpret_cast<const float4 *>(p.C + grow * p.Cout + c0);
 #pragma unroll
                                 for (int q = 0; q < 8; ++q) {
-                                    const float4 o = dst[q];
-                                    vv[4 * q] += o.x; vv[4 * q + 1] += o.y; vv[4 * q + 2] += o.z; vv[4 * q + 3] += o.w;
+                                    const float4 o = src[q];
+                                    vv[4 * q] = fmaf(o.x, kScale, vv[4 * q]); vv[4 * q + 1] = fmaf(o.y, kScale, vv[4 * q + 1]);
+                                    vv[4 * q + 2] = fmaf(o.z, kScale, vv[4 * q + 2]); vv[4 * q + 3] = fmaf(o.w, kScale, vv[4 * q + 3]);
                                 }
                             }
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) dst[q] = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
                         }
-                        if (p.Ch) store_planes32(vv, p.Ch + grow * p.Cout + c0, p.Cl + grow * p.Cout + c0);
+                    }
+                    if (p.Ch) {
+                        uint32_t h[16], l[16];
+                        split_planes32(vv, h, l);
+                        stage_store(&tm_ch, c0, reinterpret_cast<const uint4 *>(h), b, row0);
+                        stage_store(&tm_cl, c0, reinterpret_cast<const uint4 *>(l), b, row0);
+                    }
+                    if (p.C) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) vv[i] *= 1.f / kScale;
+                        stage_store(&tm_c, c0, reinterpret_cast<const uint4 *>(vv), b, row0);
+                        stage_store(&tm_c, c0 + 16, reinterpret_cast<const uint4 *>(vv + 16), b, row0);
                     }
                 }
             }
         }
+        if (lane == 0) tc::tma_store_wait_all();
     }
     tc::tcgen05_fence_before();
     __syncthreads();

@@ -71,6 +71,7 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap *m, const void *s
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ---------------------------------------------------------------- TMEM
@@ -157,5 +158,7 @@ int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, in
 // host: tensor map of an fp32 [batch, rows, cols] row-major array for TMA stores, box = {16 cols, box_rows, 1}, 64-byte swizzle
 // (cols must be a multiple of 4: global strides are multiples of 16 bytes).
 int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// same for fp16: box = {32 cols, box_rows, 1} (64-byte rows), 64-byte swizzle
+int make_tmap_f16_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 
 }  // namespace opb
