@@ -91,8 +91,9 @@ class _Workspace:
         key = (name, tuple(shape), dtype, str(device))
         t = self._bufs.get(key)
         if t is None:
-            # drop buffers of the same name with another shape: shapes change rarely, memory is large
-            for k in [k for k in self._bufs if k[0] == name]:
+            # keep at most two shapes per name (the per-frame and the shared single-frame use of a buffer)
+            same = [k for k in self._bufs if k[0] == name]
+            for k in same[:-1]:
                 del self._bufs[k]
             t = torch.empty(shape, dtype=dtype, device=device)
             self._bufs[key] = t
@@ -278,14 +279,19 @@ class GATsSuperGlue(nn.Module):
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 
-    def _propagate_tc(self, x, x_p, B, N, M, ksum, P, lw):
+    def _propagate_tc(self, x, x_p, B, N, M, ksum, P, lw, shared_src=False):
         """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place.
         message = (Q' / (Q'_h . Ksum_h + 1e-6)) P_b^T + bm  ==  merge(linear_attention(q, k, v))  (:98, :119)."""
         dev = x.device
         q_p = self._planes(f"q{N}", (B, N, _D), dev)
+        if shared_src:          # one source (ksum [1,256], P_b [1,256,256]) for all B frames: P is an ordinary weight
+            ksum = self._ws.get("ksum_bc", (B, _D), torch.float32, dev).copy_(ksum.expand(B, _D))
+            P, wflag = (P[0][0], P[1][0]), 0
+        else:
+            wflag = 64                                                                                            # WBATCHED
         self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 32, elu_cols=_D, ksum=ksum, zscale_num=M, tag="q")     # ELU1 | ZSCALE
         msg_p = self._planes(f"msg{N}", (B, N, _D), dev)
-        self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=64, tag="merge")                                    # WBATCHED
+        self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=wflag, tag="merge")
         self._mlp_tc(x, x_p, msg_p, B, N, lw)
 
     def _mlp_tc(self, x, x_p, msg_p, B, N, lw):
@@ -367,41 +373,76 @@ class GATsSuperGlue(nn.Module):
         db = self._static_db(desc3d, leaves[:, :, :N3 * L], L)
         x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
         x3 = self._ws.get("x3", (B, N3, _D), torch.float32, dev)
-        x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
-
         tcp = self.use_tensor_cores
+        # With one object DB shared by the whole batch the 3D stream does not depend on the query frame until it first
+        # receives a message from the 2D stream (the x-side update of the first 'cross' layer): up to there it is
+        # computed once (batch of 1) and then broadcast -- the same bits per frame, 1/B of the work.
+        single3 = bool(tcp and db["shared"])
+        if single3:
+            x3s = self._ws.get("x3s", (1, N3, _D), torch.float32, dev)
+            x3s.copy_(db["d3"])
+            x3s_p = self._planes("x3s", (1, N3, _D), dev)
+        else:
+            x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
         if tcp:
             x2_p = self._split(x2, *self._planes("x2", (B, N2, _D), dev))
             x3_p = self._planes("x3", (B, N3, _D), dev)          # filled after the first GATs layer
+
+        def broadcast3():
+            x3.copy_(x3s.expand(B, N3, _D))
+            x3_p[0].copy_(x3s_p[0].expand(B, N3, _D)); x3_p[1].copy_(x3s_p[1].expand(B, N3, _D))
+
         for li, lw in enumerate(pk["layers"]):
             kind = lw["kind"]
             if kind == "GATs":
-                self._gats(x3, db, B, N3, L, lw, li)
-                if tcp:
-                    self._split(x3, *x3_p)
+                if single3:
+                    self._gats(x3s, db, 1, N3, L, lw, li)
+                    self._split(x3s, *x3s_p)
+                else:
+                    self._gats(x3, db, B, N3, L, lw, li)
+                    if tcp:
+                        self._split(x3, *x3_p)
                 if self._trace is not None:
-                    self._trace.append((li, x2.clone(), x3.clone()))
+                    self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
                 continue
             # both deltas of a layer are computed from the layer's input (:77-78,82-83): reduce the source
             # side of both calls first, then update the two streams in place.
-            s2, s3 = (x2_p, x3_p) if tcp else (x2, x3)
-            kvf = self._kv_tc if tcp else self._kv
-            if kind == "cross":
-                KVa, Ksa = kvf(s3, B, N3, lw, "a")       # desc2d attends to desc3d
-                KVb, Ksb = kvf(s2, B, N2, lw, "b")       # desc3d attends to desc2d
-                Ma, Mb = N3, N2
-            else:
-                KVa, Ksa = kvf(s2, B, N2, lw, "a")
-                KVb, Ksb = kvf(s3, B, N3, lw, "b")
-                Ma, Mb = N2, N3
-            if tcp:
-                self._propagate_tc(x2, x2_p, B, N2, Ma, KVa, Ksa, lw)
-                self._propagate_tc(x3, x3_p, B, N3, Mb, KVb, Ksb, lw)
-            else:
+            if not tcp:
+                if kind == "cross":
+                    KVa, Ksa = self._kv(x3, B, N3, lw, "a")       # desc2d attends to desc3d
+                    KVb, Ksb = self._kv(x2, B, N2, lw, "b")       # desc3d attends to desc2d
+                    Ma, Mb = N3, N2
+                else:
+                    KVa, Ksa = self._kv(x2, B, N2, lw, "a")
+                    KVb, Ksb = self._kv(x3, B, N3, lw, "b")
+                    Ma, Mb = N2, N3
                 self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
                 self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
+            else:
+                B3 = 1 if single3 else B
+                s3_p = x3s_p if single3 else x3_p
+                if kind == "cross":
+                    ka = self._kv_tc(s3_p, B3, N3, lw, "a")       # desc2d attends to desc3d
+                    kb = self._kv_tc(x2_p, B, N2, lw, "b")        # desc3d attends to desc2d
+                    Ma, Mb = N3, N2
+                    self._propagate_tc(x2, x2_p, B, N2, Ma, *ka, lw, shared_src=single3)
+                    if single3:                                   # from here on the 3D stream is per frame
+                        broadcast3()
+                        single3 = False
+                    self._propagate_tc(x3, x3_p, B, N3, Mb, *kb, lw)
+                else:
+                    ka = self._kv_tc(x2_p, B, N2, lw, "a")
+                    kb = self._kv_tc(s3_p, B3, N3, lw, "b")
+                    Ma, Mb = N2, N3
+                    self._propagate_tc(x2, x2_p, B, N2, Ma, *ka, lw)
+                    if single3:
+                        self._propagate_tc(x3s, x3s_p, 1, N3, Mb, *kb, lw)
+                    else:
+                        self._propagate_tc(x3, x3_p, B, N3, Mb, *kb, lw)
             if self._trace is not None:
-                self._trace.append((li, x2.clone(), x3.clone()))
+                self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
+        if single3:                                               # no cross layer at all (not the shipped layer list)
+            broadcast3()
 
         m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
         m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
