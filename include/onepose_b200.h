@@ -114,11 +114,11 @@ int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B
  * partials of K' (ksum_partial [B][nparts][256][2]) and emits ksum [B,256], optionally KV [B,4,64,64] (:96, scaled by inv_m = 1/M),
  * and the per-frame matrix P_b[o,(h,d)] = sum_q KV_h[d,q] Wm[o,(h,q)] as planes [B,256,256], so that
  * message = (Q' M / (Q'_h.Ksum_h + 1e-6)) P_b^T + bm is one op_linear_tc call (OPB_LIN_ZSCALE on the Q projection,
- * OPB_LIN_WBATCHED on the merge).  Wv [256,256] / bv head-major rows, Wm [256,256] head-major columns. */
+ * OPB_LIN_WBATCHED on the merge).  Head-major weights, transposed for coalesced reads: WvT [4,256,64] = Wv[h*64+q, c], bv [256], WmT [4,64,256] = Wm[o, h*64+q]. */
 int op_atb_chunks(int M);
 int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const void *Bl, int B, int M, float *partial, void *stream);
-int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *Wv, const float *bv,
-               const float *Wm, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream);
+int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *WvT, const float *bv,
+               const float *WmT, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream);
 /* op_attn_apply writing split-precision planes instead of fp32 */
 int op_attn_apply_planes(const float *Qp, const float *KV, const float *Ksum, void *out_hi, void *out_lo, int B, int N,
                          int M, void *stream);

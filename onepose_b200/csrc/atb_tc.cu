@@ -143,8 +143,8 @@ namespace atb {
 constexpr int kPostD = 16;
 __global__ void __launch_bounds__(256)
 k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
-          const float *__restrict__ Wv /* [256][256] head-major rows */, const float *__restrict__ bv,
-          const float *__restrict__ Wm /* [256][256] head-major columns */, float inv_m, float *__restrict__ ksum /* [B][256] */,
+          const float *__restrict__ WvT /* [4][256 c][64 q] = Wv[h*64+q][c] */, const float *__restrict__ bv,
+          const float *__restrict__ WmT /* [4][64 q][256 o] = Wm[o][h*64+q] */, float inv_m, float *__restrict__ ksum /* [B][256] */,
           float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
     __shared__ float G[kPostD][256];
     __shared__ float KV[kPostD][65];
@@ -183,14 +183,12 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
     {   // KV[d][q]: thread = (q, group of 4 d)
         const int q = tid & 63, d0 = (tid >> 6) * 4;
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        const float *w = Wv + (long long)(h * 64 + q) * 256;
-        for (int c = 0; c < 256; c += 4) {
-            const float4 w4 = __ldg(reinterpret_cast<const float4 *>(w + c));
+        const float *w = WvT + (long long)h * 256 * 64 + q;          // coalesced over q
+#pragma unroll 8
+        for (int c = 0; c < 256; ++c) {
+            const float wc = __ldg(w + c * 64);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                acc[i] = fmaf(G[d0 + i][c], w4.x, acc[i]); acc[i] = fmaf(G[d0 + i][c + 1], w4.y, acc[i]);
-                acc[i] = fmaf(G[d0 + i][c + 2], w4.z, acc[i]); acc[i] = fmaf(G[d0 + i][c + 3], w4.w, acc[i]);
-            }
+            for (int i = 0; i < 4; ++i) acc[i] = fmaf(G[d0 + i][c], wc, acc[i]);
         }
         const float bq = bv[h * 64 + q];
 #pragma unroll
@@ -205,10 +203,7 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
         const int o = tid;
         float wm[64];
 #pragma unroll
-        for (int q = 0; q < 64; q += 4) {
-            const float4 w4 = __ldg(reinterpret_cast<const float4 *>(Wm + (long long)o * 256 + h * 64 + q));
-            wm[q] = w4.x; wm[q + 1] = w4.y; wm[q + 2] = w4.z; wm[q + 3] = w4.w;
-        }
+        for (int q = 0; q < 64; ++q) wm[q] = __ldg(WmT + ((long long)h * 64 + q) * 256 + o);     // coalesced over o
         uint32_t hh[kPostD / 2], ll[kPostD / 2];
 #pragma unroll
         for (int d = 0; d < kPostD; d += 2) {
@@ -252,12 +247,12 @@ extern "C" int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const v
     return OPB_OK;
 }
 
-extern "C" int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *Wv, const float *bv,
-                          const float *Wm, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream) {
+extern "C" int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *WvT, const float *bv,
+                          const float *WmT, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream) {
     using namespace opb;
-    OPB_CHECK_ARG(partial && ksum_partial && Wv && bv && Wm && ksum && Ph && Pl, "op_kv_post: null pointer");
+    OPB_CHECK_ARG(partial && ksum_partial && WvT && bv && WmT && ksum && Ph && Pl, "op_kv_post: null pointer");
     OPB_CHECK_ARG(B > 0 && nchunks > 0 && nparts > 0 && B <= 65535, "op_kv_post: bad shape");
-    atb::k_kv_post<<<dim3(4, 64 / atb::kPostD, B), 256, 0, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, Wv, bv, Wm,
+    atb::k_kv_post<<<dim3(4, 64 / atb::kPostD, B), 256, 0, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, WvT, bv, WmT,
                                                                             inv_m, ksum, kv_out, (__half *)Ph, (__half *)Pl);
     OPB_CHECK_LAUNCH();
     return OPB_OK;

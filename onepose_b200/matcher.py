@@ -152,6 +152,8 @@ class GATsSuperGlue(nn.Module):
                 packed.append(dict(
                     kind=kind, Wq=wq.contiguous(), bq=bq.contiguous(), Wk=wk.contiguous(), bk=bk.contiguous(),
                     Wv=wv.contiguous(), bv=bv.contiguous(),
+                    WvT=wv.view(_HEADS, 64, _D).transpose(1, 2).contiguous(),            # [h, c, q] for op_kv_post
+                    WmT=f(at.merge.weight[:, :, 0])[:, perm].view(_D, _HEADS, 64).permute(1, 2, 0).contiguous(),   # [h, q, o]
                     Wkv=torch.cat([wk, wv], 0).contiguous(), bkv=torch.cat([bk, bv], 0).contiguous(),
                     Wm=f(at.merge.weight[:, :, 0])[:, perm].contiguous(), bm=f(at.merge.bias),
                     W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias),
@@ -275,7 +277,7 @@ class GATsSuperGlue(nn.Module):
         call("op_atb_tc", ptr(kp[0]), ptr(kp[1]), ptr(src_p[0]), ptr(src_p[1]), B, M, ptr(part), stream_ptr())
         ksum = self._ws.get("ksum" + tag, (B, _D), torch.float32, dev)
         P = self._planes("P" + tag, (B, _D, _D), dev)
-        call("op_kv_post", ptr(part), nch, ptr(ks_part), parts, ptr(lw["Wv"]), ptr(lw["bv"]), ptr(lw["Wm"]), B, 1.0 / M, ptr(ksum), None,
+        call("op_kv_post", ptr(part), nch, ptr(ks_part), parts, ptr(lw["WvT"]), ptr(lw["bv"]), ptr(lw["WmT"]), B, 1.0 / M, ptr(ksum), None,
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 

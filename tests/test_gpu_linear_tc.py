@@ -144,7 +144,9 @@ def test_atb_tc_and_kv_post_vs_float64_linear_attention(shape):
     ks_part = torch.stack([pad.view(B, nparts, 32, 256).sum(2), torch.zeros(B, nparts, 256, device="cuda")], -1).contiguous()
     ksum = torch.empty(B, 256, device="cuda"); kv = torch.empty(B, 4, 64, 64, device="cuda")
     Ph = torch.empty(B, 256, 256, dtype=torch.float16, device="cuda"); Pl = torch.empty_like(Ph)
-    call("op_kv_post", ptr(part), nch, ptr(ks_part), nparts, ptr(Wv), ptr(bv), ptr(Wm), B, 1.0 / M, ptr(ksum), ptr(kv), ptr(Ph), ptr(Pl), stream_ptr())
+    WvT = Wv.view(4, 64, 256).transpose(1, 2).contiguous()              # [h, c, q]
+    WmT = Wm.view(256, 4, 64).permute(1, 2, 0).contiguous()             # [h, q, o]
+    call("op_kv_post", ptr(part), nch, ptr(ks_part), nparts, ptr(WvT), ptr(bv), ptr(WmT), B, 1.0 / M, ptr(ksum), ptr(kv), ptr(Ph), ptr(Pl), stream_ptr())
     torch.cuda.synchronize()
     V = X.double() @ Wv.double().t() + bv.double()
     Kh = Kp.double().view(B, M, 4, 64); Vh = V.view(B, M, 4, 64)
