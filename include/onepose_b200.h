@@ -67,9 +67,11 @@ int op_gats_leaf_aggregate(const float *leaf, long long leaf_bstride, const floa
 #define OPB_LIN_RESIDUAL 2
 #define OPB_LIN_STATS 4
 #define OPB_LIN_NORM_RELU 8
-#define OPB_LIN_COLSUM 16    /* op_linear_tc: stats_partial = (sum, 0) of the value after bias / elu+1 over the valid rows */
+#define OPB_LIN_COLSUM 16    /* op_linear_tc: stats_partial = (sum, 0) of the stored value over the valid rows */
 #define OPB_LIN_ZSCALE 32    /* op_linear_tc: each 64-column head of a row is multiplied by zscale_num / (row_head . ksum[b, head] + 1e-6) */
 #define OPB_LIN_WBATCHED 64  /* op_linear_tc: W planes are [B, Cout, K], one matrix per frame */
+#define OPB_LIN_BIASB 128     /* op_linear_tc: bias is [B, Cout], one vector per frame */
+#define OPB_LIN_CSTATS_RELU 256 /* op_linear_tc: stats_partial = (sum, sum of squares) of the value after bias over the valid rows, then ReLU */
 int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
               float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,
               const float *mean, const float *rstd, double *stats_partial, void *stream);
@@ -106,6 +108,21 @@ int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, cons
                  const void *Wl, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
                  int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream);
 int op_linear_tc_stat_parts(int rows_per_batch);
+/* InstanceNorm1d of the MLP (:135-147) without a normalisation pass over the hidden tensor:
+ *   - the per-channel mean of layer 0's output is analytic, W0 mean_rows([x | msg]) + b0, from the column sums of its inputs
+ *     (OPB_LIN_COLSUM partials of their producers, or op_colsum_partial [B][op_linear_tc_stat_parts(rows)][C][2] for a plain tensor):
+ *     op_mlp_center_bias writes the per-frame bias -(W0 mean_in) [B,512] (W0T = W0 transposed, [512 k][512 c]);
+ *   - layer 0 then runs with OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU: output planes hold relu(h - mean), stats the centred sums;
+ *   - op_instnorm_finalize_tc gives rstd, op_scale_weight_planes folds it into layer 1's weights: W1s[b,o,c] = W1[o,c] rstd[b,c]
+ *     (planes [B,Cout,K]), used with OPB_LIN_WBATCHED. */
+int op_colsum_partial(const float *x, int B, int rows, int C, float *partial, void *stream);
+int op_mlp_center_bias(const float *xpart, int xparts, const float *mpart, int mparts, const float *W0T, int B, int rows,
+                       float *bias_out, void *stream);
+int op_scale_weight_planes(const float *W, const float *rstd, int B, int Cout, int K, void *hi, void *lo, void *stream);
+/* op_instnorm_finalize_tc + op_scale_weight_planes in one launch: rstd from the CSTATS_RELU partials [B][parts][K][2] straight
+ * into the per-frame layer-1 weight planes [B,Cout,K] (K a multiple of 64); rstd [B,K] is written too when not NULL. */
+int op_instnorm_scale_weight_planes(const float *stats_partial, int B, int parts, int rows_per_batch, float eps, const float *W,
+                                    int Cout, int K, void *hi, void *lo, float *rstd, void *stream);
 int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B, int parts, int C, int rows_per_batch,
                             float eps, float *mean, float *rstd, void *stream);
 /* Source side of linear attention on the tensor cores (:88-99), re-associated so that the V projection is never

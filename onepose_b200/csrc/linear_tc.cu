@@ -3,6 +3,9 @@
 // elementwise producers of the split-precision planes and the C ABI.
 #include "common.cuh"
 #include "linear_tc.cuh"
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
 
 namespace opb {
 
@@ -53,6 +56,108 @@ __global__ void k_instnorm_finalize_tc(const float2 *__restrict__ part, const fl
     rstd[(long long)b * C + c] = (float)(1.0 / sqrt(var + (double)eps));
 }
 
+// (sum, 0) over groups of 32 rows, laid out like the COLSUM partials of op_linear_tc: partial[b][row/32][c]
+__global__ void k_colsum_partial(const float *__restrict__ x, int rows, int C, int parts, float2 *__restrict__ partial) {
+    const int part = blockIdx.x, b = blockIdx.y;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float s = 0.f;
+        const int r0 = part * 32, r1 = min(rows, r0 + 32);
+        for (int r = r0; r < r1; ++r) s += x[((long long)b * rows + r) * C + c];
+        partial[((long long)b * parts + part) * C + c] = make_float2(s, 0.f);
+    }
+}
+
+// Analytic InstanceNorm mean of MLP layer 0 (:135-147): mean_rows([x | msg] W0^T + b0) = W0 mean_rows([x | msg]) + b0, so the
+// centred pre-activation is obtained with the per-frame bias  -(W0 mean_in)  (b0 cancels).  W0T is [512 k][512 c].
+// One cluster of 8 CTAs per frame: CTA r folds the column-sum partials of input channels [64r, 64r+64) (4 slices of
+// the parts per channel, fixed order), the 512 means are exchanged through distributed shared memory, and CTA r then
+// produces output columns [64r, 64r+64) with the k range cut into 4 slices.
+__global__ void __cluster_dims__(1, 8, 1) __launch_bounds__(256)
+k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__restrict__ mpart, int mparts,
+                  const float *__restrict__ W0T, int rows, float *__restrict__ bias_out) {
+    __shared__ float red[4][64];
+    __shared__ float mean_loc[64];
+    __shared__ float mean_in[512];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int b = blockIdx.x, r = blockIdx.y, tid = threadIdx.x, j = tid & 63, sl = tid >> 6;
+    {
+        const float2 *src = r < 4 ? xpart : mpart;
+        const int parts = r < 4 ? xparts : mparts;
+        const int kk = (r & 3) * 64 + j;
+        double s = 0;
+        for (int t = sl; t < parts; t += 4) s += (double)src[((long long)b * parts + t) * 256 + kk].x;
+        red[sl][j] = (float)s;
+    }
+    __syncthreads();
+    if (tid < 64) mean_loc[tid] = (float)(((double)red[0][tid] + (double)red[1][tid] + (double)red[2][tid] + (double)red[3][tid]) / rows);
+    cluster.sync();
+    for (int k = tid; k < 512; k += 256) mean_in[k] = cluster.map_shared_rank(mean_loc, k >> 6)[k & 63];
+    cluster.sync();                                       // nobody leaves (or reuses red) while its means are still being read
+    const int c = r * 64 + j;
+    float acc = 0.f;
+#pragma unroll 8
+    for (int k = sl * 128; k < sl * 128 + 128; ++k) acc = fmaf(__ldg(W0T + (long long)k * 512 + c), mean_in[k], acc);
+    red[sl][j] = acc;
+    __syncthreads();
+    if (tid < 64) bias_out[(long long)b * 512 + r * 64 + tid] = -((red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid]));
+}
+
+// InstanceNorm statistics of the centred layer-0 output (OPB_LIN_CSTATS_RELU partials) -> rstd, folded straight into the
+// per-frame layer-1 weights: W1s[b][o][c] = W1[o][c] * rstd[b][c] as split-precision planes.  CTA (b, g) owns channels
+// [64g, 64g+64): it needs nobody else's statistics.
+__global__ void __launch_bounds__(256)
+k_instnorm_scale_weight_planes(const float2 *__restrict__ part, int parts, int rows, float eps, const float *__restrict__ W,
+                               int Cout, int K, __half *__restrict__ hi, __half *__restrict__ lo, float *__restrict__ rstd_out) {
+    __shared__ double red_s[4][64], red_q[4][64];
+    __shared__ float rs[64];
+    const int b = blockIdx.x, g = blockIdx.y, tid = threadIdx.x, j = tid & 63, sl = tid >> 6;
+    {
+        double s = 0, q = 0;
+        for (int t = sl; t < parts; t += 4) {
+            const float2 v = part[((long long)b * parts + t) * K + g * 64 + j];
+            s += (double)v.x; q += (double)v.y;
+        }
+        red_s[sl][j] = s; red_q[sl][j] = q;
+    }
+    __syncthreads();
+    if (tid < 64) {
+        const double mu = (red_s[0][tid] + red_s[1][tid] + red_s[2][tid] + red_s[3][tid]) / rows;
+        double var = (red_q[0][tid] + red_q[1][tid] + red_q[2][tid] + red_q[3][tid]) / rows - mu * mu;
+        if (var < 0) var = 0;
+        rs[tid] = (float)(1.0 / sqrt(var + (double)eps));
+        if (rstd_out) rstd_out[(long long)b * K + g * 64 + tid] = rs[tid];
+    }
+    __syncthreads();
+    const int c4 = (tid & 15) * 4;                           // 16 threads per weight row segment of 64 channels
+    const float4 r4 = *reinterpret_cast<const float4 *>(rs + c4);
+    for (int o = tid >> 4; o < Cout; o += 16) {
+        const float4 w = __ldg(reinterpret_cast<const float4 *>(W + (long long)o * K + g * 64 + c4));
+        __half h[4], l[4];
+        tc::split_f16(w.x * r4.x * lintc::kScale, h[0], l[0]); tc::split_f16(w.y * r4.y * lintc::kScale, h[1], l[1]);
+        tc::split_f16(w.z * r4.z * lintc::kScale, h[2], l[2]); tc::split_f16(w.w * r4.w * lintc::kScale, h[3], l[3]);
+        const long long off = ((long long)b * Cout + o) * K + g * 64 + c4;
+        *reinterpret_cast<uint2 *>(hi + off) = *reinterpret_cast<uint2 *>(h);
+        *reinterpret_cast<uint2 *>(lo + off) = *reinterpret_cast<uint2 *>(l);
+    }
+}
+
+// W1s[b][o][c] = W1[o][c] * rstd[b][c] as split-precision planes: the 1/std of InstanceNorm folded into the next layer
+__global__ void k_scale_weight_planes(const float *__restrict__ W, const float *__restrict__ rstd, int Cout, int K,
+                                      __half *__restrict__ hi, __half *__restrict__ lo) {
+    const int b = blockIdx.y;
+    const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= (long long)Cout * K) return;
+    const int c = (int)(i % K);
+    const float4 w = *reinterpret_cast<const float4 *>(W + i);
+    const float4 r = *reinterpret_cast<const float4 *>(rstd + (long long)b * K + c);
+    __half h[4], l[4];
+    tc::split_f16(w.x * r.x * lintc::kScale, h[0], l[0]); tc::split_f16(w.y * r.y * lintc::kScale, h[1], l[1]);
+    tc::split_f16(w.z * r.z * lintc::kScale, h[2], l[2]); tc::split_f16(w.w * r.w * lintc::kScale, h[3], l[3]);
+    const long long o = (long long)b * Cout * K + i;
+    *reinterpret_cast<uint2 *>(hi + o) = *reinterpret_cast<uint2 *>(h);
+    *reinterpret_cast<uint2 *>(lo + o) = *reinterpret_cast<uint2 *>(l);
+}
+
 static int sm_count() {
     static int n = 0;
     if (n == 0) {
@@ -84,6 +189,40 @@ extern "C" int op_norm_relu_split(const float *h, const float *mean, const float
     return OPB_OK;
 }
 
+extern "C" int op_colsum_partial(const float *x, int B, int rows, int C, float *partial, void *stream) {
+    OPB_CHECK_ARG(x && partial && B > 0 && rows > 0 && C > 0 && B <= 65535, "op_colsum_partial: bad argument");
+    const int parts = opb::ceil_div(rows, opb::lintc::BM) * 4;
+    opb::k_colsum_partial<<<dim3(parts, B), 256, 0, (cudaStream_t)stream>>>(x, rows, C, parts, (float2 *)partial);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
+
+extern "C" int op_mlp_center_bias(const float *xpart, int xparts, const float *mpart, int mparts, const float *W0T, int B, int rows,
+                                  float *bias_out, void *stream) {
+    OPB_CHECK_ARG(xpart && mpart && W0T && bias_out && B > 0 && rows > 0 && xparts > 0 && mparts > 0 && B <= 65535, "op_mlp_center_bias: bad argument");
+    opb::k_mlp_center_bias<<<dim3(B, 8), 256, 0, (cudaStream_t)stream>>>((const float2 *)xpart, xparts, (const float2 *)mpart, mparts, W0T, rows, bias_out);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
+
+extern "C" int op_scale_weight_planes(const float *W, const float *rstd, int B, int Cout, int K, void *hi, void *lo, void *stream) {
+    OPB_CHECK_ARG(W && rstd && hi && lo && B > 0 && Cout > 0 && K > 0 && K % 4 == 0 && B <= 65535, "op_scale_weight_planes: bad argument");
+    opb::k_scale_weight_planes<<<dim3(opb::ceil_div((long long)Cout * K / 4, 256), B), 256, 0, (cudaStream_t)stream>>>(W, rstd, Cout, K, (__half *)hi, (__half *)lo);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
+
+extern "C" int op_instnorm_scale_weight_planes(const float *stats_partial, int B, int parts, int rows_per_batch, float eps, const float *W,
+                                               int Cout, int K, void *hi, void *lo, float *rstd, void *stream) {
+    OPB_CHECK_ARG(stats_partial && W && hi && lo, "op_instnorm_scale_weight_planes: null pointer");
+    OPB_CHECK_ARG(B > 0 && B <= 65535 && parts > 0 && rows_per_batch > 0 && Cout > 0 && K > 0 && K % 64 == 0,
+                  "op_instnorm_scale_weight_planes: bad shape B=%d parts=%d rows=%d Cout=%d K=%d", B, parts, rows_per_batch, Cout, K);
+    opb::k_instnorm_scale_weight_planes<<<dim3(B, K / 64), 256, 0, (cudaStream_t)stream>>>((const float2 *)stats_partial, parts, rows_per_batch, eps,
+                                                                                           W, Cout, K, (__half *)hi, (__half *)lo, rstd);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
+
 extern "C" int op_linear_tc_stat_parts(int rows_per_batch) { return opb::ceil_div(rows_per_batch, opb::lintc::BM) * 4; }
 
 extern "C" int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B, int parts, int C, int rows_per_batch,
@@ -108,8 +247,12 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(C || Ch, "op_linear_tc: no output requested");
     OPB_CHECK_ARG((Ch == nullptr) == (Cl == nullptr), "op_linear_tc: Ch/Cl must come together");
     OPB_CHECK_ARG(!(flags & OPB_LIN_RESIDUAL) || C, "op_linear_tc: RESIDUAL needs the fp32 output");
-    OPB_CHECK_ARG(!(flags & (OPB_LIN_STATS | OPB_LIN_COLSUM)) || stats_partial, "op_linear_tc: STATS / COLSUM need stats_partial");
-    OPB_CHECK_ARG(!((flags & OPB_LIN_STATS) && (flags & OPB_LIN_COLSUM)), "op_linear_tc: STATS and COLSUM are exclusive");
+    {
+        const int nst = ((flags & OPB_LIN_STATS) != 0) + ((flags & OPB_LIN_COLSUM) != 0) + ((flags & OPB_LIN_CSTATS_RELU) != 0);
+        OPB_CHECK_ARG(nst == 0 || stats_partial, "op_linear_tc: STATS / COLSUM / CSTATS_RELU need stats_partial");
+        OPB_CHECK_ARG(nst <= 1, "op_linear_tc: STATS, COLSUM and CSTATS_RELU are exclusive");
+        OPB_CHECK_ARG(!(flags & OPB_LIN_BIASB) || bias, "op_linear_tc: BIASB needs a bias");
+    }
     OPB_CHECK_ARG(!(flags & OPB_LIN_ZSCALE) || (ksum && Cout == 256), "op_linear_tc: ZSCALE needs ksum and Cout == 256");
     OPB_CHECK_ARG(!(flags & OPB_LIN_NORM_RELU), "op_linear_tc: NORM_RELU is applied by op_norm_relu_split");
     OPB_CHECK_ARG(!(flags & OPB_LIN_ELU1) || elu_cols % 32 == 0, "op_linear_tc: elu_cols must be a multiple of 32");

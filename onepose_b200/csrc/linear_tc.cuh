@@ -102,7 +102,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], EPI_WARPS); }
         tc::fence_barrier_init();
     }
-    for (int i = threadIdx.x; i < BIAS_FLOATS; i += THREADS) s_bias[i] = (p.bias && i < p.Cout) ? kScale * p.bias[i] : 0.f;     // bias in the x64 domain of the planes
+    for (int i = threadIdx.x; i < BIAS_FLOATS; i += THREADS) s_bias[i] = (p.bias && i < p.Cout && !(p.flags & OPB_LIN_BIASB)) ? kScale * p.bias[i] : 0.f;     // bias in the x64 domain of the planes
     if (warp == 9) tc::tmem_alloc<512>(&bar->tmem_base);
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_a1h); tc::tma_prefetch_desc(&tm_a1l); tc::tma_prefetch_desc(&tm_wh); tc::tma_prefetch_desc(&tm_wl);
@@ -233,7 +233,13 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     }
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
-                        const float4 bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
+                        float4 bq;
+                        if (p.flags & OPB_LIN_BIASB) {                       // per-frame bias [B, Cout], brought to the x64 domain here
+                            bq = __ldg(reinterpret_cast<const float4 *>(p.bias + (long long)b * p.Cout + c0) + q);
+                            bq.x *= kScale; bq.y *= kScale; bq.z *= kScale; bq.w *= kScale;
+                        } else {
+                            bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
+                        }
                         vv[4 * q] = fmaf(vv[4 * q], 1.f / kScale, bq.x); vv[4 * q + 1] = fmaf(vv[4 * q + 1], 1.f / kScale, bq.y);
                         vv[4 * q + 2] = fmaf(vv[4 * q + 2], 1.f / kScale, bq.z); vv[4 * q + 3] = fmaf(vv[4 * q + 3], 1.f / kScale, bq.w);
                     }
@@ -245,12 +251,20 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                             vv[i] = vv[i] > 0.f ? vv[i] + kScale : e;
                         }
                     }
-                    if (p.flags & OPB_LIN_COLSUM) {                // column sums of the value over the valid rows (Ksum, :97)
+                    if (p.flags & OPB_LIN_CSTATS_RELU) {
+                        // InstanceNorm1d on a value the caller has already centred through the bias (bias = b - analytic mean):
+                        // (sum, sum of squares) of d over the valid rows, then ReLU -- the 1/std factor commutes with ReLU and is
+                        // folded into the next layer's weights (op_scale_weight_planes), GATs_SuperGlue.py:144-146
                         float s[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
                         const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
-                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) { const float t = row_ok ? vv[i] : 0.f; s[i] = t * t; }
+                        const float cq = transpose_reduce_sum(s, lane) * kInvScale2;
+                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, cq);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) vv[i] = fmaxf(vv[i], 0.f);
                     }
                     if (p.flags & OPB_LIN_ZSCALE) {                // Q'_h . Ksum_h of this row (linear attention normaliser, :97)
                         const float4 *ks = reinterpret_cast<const float4 *>(p.ksum + (long long)b * p.Cout + c0);
@@ -283,6 +297,13 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                                 }
                             }
                         }
+                    }
+                    if (p.flags & OPB_LIN_COLSUM) {                // column sums of the stored value over the valid rows (Ksum :97; means)
+                        float s[32];
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
+                        const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
+                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
                     }
                     if (p.Ch) {
                         uint32_t h[16], l[16];

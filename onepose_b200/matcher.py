@@ -156,7 +156,7 @@ class GATsSuperGlue(nn.Module):
                     WmT=f(at.merge.weight[:, :, 0])[:, perm].view(_D, _HEADS, 64).permute(1, 2, 0).contiguous(),   # [h, q, o]
                     Wkv=torch.cat([wk, wv], 0).contiguous(), bkv=torch.cat([bk, bv], 0).contiguous(),
                     Wm=f(at.merge.weight[:, :, 0])[:, perm].contiguous(), bm=f(at.merge.bias),
-                    W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias),
+                    W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias), W0T=f(mlp[0].weight[:, :, 0].t()),
                     W1=f(mlp[3].weight[:, :, 0]), b1=f(mlp[3].bias)))
         self._packed = dict(layers=packed, Wf=f(self.final_proj.weight[:, :, 0]), bf=f(self.final_proj.bias))
         # split-precision fp16 planes of every projection weight for the tcgen05 path (linear_tc.cuh)
@@ -281,7 +281,7 @@ class GATsSuperGlue(nn.Module):
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 
-    def _propagate_tc(self, x, x_p, B, N, M, ksum, P, lw, shared_src=False):
+    def _propagate_tc(self, x, x_p, xs, B, N, M, ksum, P, lw, shared_src=False):
         """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place.
         message = (Q' / (Q'_h . Ksum_h + 1e-6)) P_b^T + bm  ==  merge(linear_attention(q, k, v))  (:98, :119)."""
         dev = x.device
@@ -293,23 +293,31 @@ class GATsSuperGlue(nn.Module):
             wflag = 64                                                                                            # WBATCHED
         self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 32, elu_cols=_D, ksum=ksum, zscale_num=M, tag="q")     # ELU1 | ZSCALE
         msg_p = self._planes(f"msg{N}", (B, N, _D), dev)
-        self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=wflag, tag="merge")
-        self._mlp_tc(x, x_p, msg_p, B, N, lw)
+        ms = self._ws.get(f"mpart{N}", (B, lib.op_linear_tc_stat_parts(N), _D, 2), torch.float32, dev)
+        self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=wflag | 16, stats=ms, tag="merge")              # COLSUM of the message
+        self._mlp_tc(x, x_p, xs, msg_p, ms, B, N, lw)
 
-    def _mlp_tc(self, x, x_p, msg_p, B, N, lw):
-        """MLP([x | message]) with InstanceNorm + ReLU and the residual add (:135-147, :78,83)."""
+    def _colsum(self, x, B, N, name):
+        """Per-frame column sums of a plain fp32 tensor, in the partial layout of OPB_LIN_COLSUM."""
+        part = self._ws.get(name, (B, lib.op_linear_tc_stat_parts(N), _D, 2), torch.float32, x.device)
+        call("op_colsum_partial", ptr(x), B, N, _D, ptr(part), stream_ptr())
+        return part
+
+    def _mlp_tc(self, x, x_p, xs, msg_p, ms, B, N, lw):
+        """MLP([x | message]) with InstanceNorm + ReLU and the residual add (:135-147, :78,83), without a normalisation
+        pass: the mean is analytic (column sums xs / ms of the inputs through W0), layer 0 writes relu(h - mean) as planes,
+        1/std is folded into per-frame layer-1 weights.  x, x_p and the column sums xs of x are updated in place."""
         dev = x.device
-        h = self._ws.get(f"h{N}", (B, N, 2 * _D), torch.float32, dev)
         parts = lib.op_linear_tc_stat_parts(N)
-        stats = self._ws.get(f"tcstats{N}", (B, parts, 2 * _D, 2), torch.float32, dev)
-        self._linear_tc(x_p, lw["W0_p"], lw["b0"], B, N, A2=msg_p, C=h, flags=4, stats=stats, tag="mlp0")
-        mean = self._ws.get("mean", (B, 2 * _D), torch.float32, dev)
-        rstd = self._ws.get("rstd", (B, 2 * _D), torch.float32, dev)
-        call("op_instnorm_finalize_tc", ptr(stats), ptr(lw["b0"]), B, parts, 2 * _D, N, 1e-5, ptr(mean), ptr(rstd), stream_ptr())
+        cb = self._ws.get("cbias", (B, 2 * _D), torch.float32, dev)
+        call("op_mlp_center_bias", ptr(xs), parts, ptr(ms), parts, ptr(lw["W0T"]), B, N, ptr(cb), stream_ptr())
         hn_p = self._planes(f"hn{N}", (B, N, 2 * _D), dev)
-        timeline.work = 8.0 * B * N * 2 * _D                                    # bytes: fp32 in, two fp16 planes out
-        call("op_norm_relu_split", ptr(h), ptr(mean), ptr(rstd), ptr(hn_p[0]), ptr(hn_p[1]), B, N, 2 * _D, stream_ptr())
-        self._linear_tc(hn_p, lw["W1_p"], lw["b1"], B, N, C=x, Cp=x_p, flags=2, tag="mlp1")     # RESIDUAL, in place
+        stats = self._ws.get(f"tcstats{N}", (B, parts, 2 * _D, 2), torch.float32, dev)
+        self._linear_tc(x_p, lw["W0_p"], cb, B, N, A2=msg_p, Cp=hn_p, flags=128 | 256, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
+        W1s = self._planes("W1s", (B, _D, 2 * _D), dev)
+        call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
+             stream_ptr())
+        self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=x, Cp=x_p, flags=2 | 16 | 64, stats=xs, tag="mlp1")        # RESIDUAL | COLSUM | WBATCHED
 
     def _gats(self, x3, db, B, N3, L, lw, li):
         hp = self.hparams
@@ -386,13 +394,17 @@ class GATsSuperGlue(nn.Module):
             x3s_p = self._planes("x3s", (1, N3, _D), dev)
         else:
             x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
+        xs2 = xs3 = xs3s = None          # per-frame column sums of x2 / x3 (partials), kept current by the mlp1 epilogue
         if tcp:
             x2_p = self._split(x2, *self._planes("x2", (B, N2, _D), dev))
             x3_p = self._planes("x3", (B, N3, _D), dev)          # filled after the first GATs layer
+            xs2 = self._colsum(x2, B, N2, "xs2")
+            xs3 = self._ws.get("xs3", (B, lib.op_linear_tc_stat_parts(N3), _D, 2), torch.float32, dev)
 
         def broadcast3():
             x3.copy_(x3s.expand(B, N3, _D))
             x3_p[0].copy_(x3s_p[0].expand(B, N3, _D)); x3_p[1].copy_(x3s_p[1].expand(B, N3, _D))
+            xs3.copy_(xs3s.expand_as(xs3))
 
         for li, lw in enumerate(pk["layers"]):
             kind = lw["kind"]
@@ -400,10 +412,12 @@ class GATsSuperGlue(nn.Module):
                 if single3:
                     self._gats(x3s, db, 1, N3, L, lw, li)
                     self._split(x3s, *x3s_p)
+                    xs3s = self._colsum(x3s, 1, N3, "xs3s")
                 else:
                     self._gats(x3, db, B, N3, L, lw, li)
                     if tcp:
                         self._split(x3, *x3_p)
+                        self._colsum(x3, B, N3, "xs3")
                 if self._trace is not None:
                     self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
                 continue
@@ -427,20 +441,20 @@ class GATsSuperGlue(nn.Module):
                     ka = self._kv_tc(s3_p, B3, N3, lw, "a")       # desc2d attends to desc3d
                     kb = self._kv_tc(x2_p, B, N2, lw, "b")        # desc3d attends to desc2d
                     Ma, Mb = N3, N2
-                    self._propagate_tc(x2, x2_p, B, N2, Ma, *ka, lw, shared_src=single3)
+                    self._propagate_tc(x2, x2_p, xs2, B, N2, Ma, *ka, lw, shared_src=single3)
                     if single3:                                   # from here on the 3D stream is per frame
                         broadcast3()
                         single3 = False
-                    self._propagate_tc(x3, x3_p, B, N3, Mb, *kb, lw)
+                    self._propagate_tc(x3, x3_p, xs3, B, N3, Mb, *kb, lw)
                 else:
                     ka = self._kv_tc(x2_p, B, N2, lw, "a")
                     kb = self._kv_tc(s3_p, B3, N3, lw, "b")
                     Ma, Mb = N2, N3
-                    self._propagate_tc(x2, x2_p, B, N2, Ma, *ka, lw)
+                    self._propagate_tc(x2, x2_p, xs2, B, N2, Ma, *ka, lw)
                     if single3:
-                        self._propagate_tc(x3s, x3s_p, 1, N3, Mb, *kb, lw)
+                        self._propagate_tc(x3s, x3s_p, xs3s, 1, N3, Mb, *kb, lw)
                     else:
-                        self._propagate_tc(x3, x3_p, B, N3, Mb, *kb, lw)
+                        self._propagate_tc(x3, x3_p, xs3, B, N3, Mb, *kb, lw)
             if self._trace is not None:
                 self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
         if single3:                                               # no cross layer at all (not the shipped layer list)

@@ -32,7 +32,7 @@ def _linear_tc(A1, W, bias, *, A2=None, want_c=True, want_planes=False, flags=0,
     C = (C_init.clone() if C_init is not None else torch.full((B, rows, Cout), float("nan"), device="cuda")) if want_c else None
     Cp = (torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda"), torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda")) if want_planes else None
     parts = lib.op_linear_tc_stat_parts(rows)
-    stats = torch.full((B, parts, Cout, 2), float("nan"), device="cuda") if flags & (4 | 16) else None
+    stats = torch.full((B, parts, Cout, 2), float("nan"), device="cuda") if flags & (4 | 16 | 256) else None
     call("op_linear_tc", ptr(a1[0]), ptr(a1[1]), K1, ptr(a2[0]) if a2 else None, ptr(a2[1]) if a2 else None,
          0 if A2 is None else A2.shape[2], ptr(w[0]), ptr(w[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None,
          ptr(Cp[1]) if Cp else None, B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr())
@@ -169,10 +169,61 @@ def test_q_projection_with_zscale_and_per_frame_merge_equals_attention_readout()
     _, Qp, st = _linear_tc(X, Wq, bq, want_c=False, want_planes=True, flags=1 | 16 | 32, elu_cols=256, ksum=ksum, zscale_num=777.0)
     q1 = torch.nn.functional.elu(X.double() @ Wq.double().t() + bq.double()) + 1
     den = (q1.view(B, N, 4, 64) * ksum.double().view(B, 1, 4, 64)).sum(-1, keepdim=True) + 1e-6
-    # COLSUM sums the activation (after bias / elu+1, before the ZSCALE division) over the valid rows
+    # COLSUM sums the stored value (after the ZSCALE division) over the valid rows
     q2 = (q1.view(B, N, 4, 64) * 777.0 / den).reshape(B, N, 256)
     assert _rel(_unsplit(Qp), q2) < 5e-6
-    np.testing.assert_allclose(st[..., 0].double().sum(1).cpu().numpy(), q1.sum(1).cpu().numpy(), rtol=1e-5)
+    np.testing.assert_allclose(st[..., 0].double().sum(1).cpu().numpy(), q2.sum(1).cpu().numpy(), rtol=1e-5)
     msg, _, _ = _linear_tc(q2.float(), P, bm, flags=64)
     ref = torch.einsum("bnk,bok->bno", q2, P.double()) + bm.double()
     assert _rel(msg, ref) < 5e-6
+
+
+@pytest.mark.parametrize("shape", [(2, 333), (1, 2048), (3, 50)])
+def test_mlp_with_analytic_instancenorm_mean(shape):
+    """The MLP of AttentionPropagation (:135-147) + residual (:78) the way the matcher runs it: column sums ->
+    op_mlp_center_bias -> layer 0 with BIASB | CSTATS_RELU -> op_instnorm_finalize_tc -> op_scale_weight_planes ->
+    layer 1 with RESIDUAL | COLSUM | WBATCHED; against InstanceNorm1d + ReLU in float64."""
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    B, N = shape
+    g = torch.Generator().manual_seed(31 + N)
+    x = (torch.randn(B, N, 256, generator=g) * 0.3 + torch.randn(B, 1, 256, generator=g) * 0.2).cuda()
+    msg = (torch.randn(B, N, 256, generator=g) * 0.5 + torch.randn(B, 1, 256, generator=g)).cuda()
+    W0 = (torch.randn(512, 512, generator=g) / 512 ** 0.5).cuda(); b0 = torch.randn(512, generator=g).cuda()
+    W1 = (torch.randn(256, 512, generator=g) / 512 ** 0.5).cuda(); b1 = (torch.randn(256, generator=g) * 0.1).cuda()
+    parts = lib.op_linear_tc_stat_parts(N)
+    xs = torch.full((B, parts, 256, 2), float("nan"), device="cuda"); ms = torch.full_like(xs, float("nan"))
+    call("op_colsum_partial", ptr(x), B, N, 256, ptr(xs), stream_ptr())
+    call("op_colsum_partial", ptr(msg), B, N, 256, ptr(ms), stream_ptr())
+    np.testing.assert_allclose(xs[..., 0].double().sum(1).cpu().numpy(), x.double().sum(1).cpu().numpy(), rtol=1e-5, atol=1e-4)
+    W0T = W0.t().contiguous()
+    cb = torch.empty(B, 512, device="cuda")
+    call("op_mlp_center_bias", ptr(xs), parts, ptr(ms), parts, ptr(W0T), B, N, ptr(cb), stream_ptr())
+    mean_in = torch.cat([x, msg], 2).double().mean(1)
+    np.testing.assert_allclose(cb.double().cpu().numpy(), -(mean_in @ W0.double().t()).cpu().numpy(), rtol=1e-5, atol=1e-5)
+    # layer 0: centred pre-activation, statistics of it, ReLU, planes out
+    _, hn, st = _linear_tc(x, W0, cb, A2=msg, want_c=False, want_planes=True, flags=128 | 256)
+    h = torch.cat([x, msg], 2).double() @ W0.double().t() + b0.double()
+    d = h - h.mean(1, keepdim=True)                       # b0 cancels in InstanceNorm: the kernel never adds it
+    assert ((_unsplit(hn) - d.clamp_min(0)).abs().max() / d.abs().max()).item() < 5e-6
+    np.testing.assert_allclose(st[..., 1].double().sum(1).cpu().numpy(), (d * d).sum(1).cpu().numpy(), rtol=2e-5)
+    assert float(st[..., 0].double().sum(1).abs().max()) < 1e-3 * N ** 0.5 + 1e-2      # residual mean is rounding noise
+    mean = torch.empty(B, 512, device="cuda"); rstd = torch.empty(B, 512, device="cuda")
+    call("op_instnorm_finalize_tc", ptr(st), None, B, parts, 512, N, 1e-5, ptr(mean), ptr(rstd), stream_ptr())
+    rstd_ref = 1.0 / torch.sqrt(d.var(1, unbiased=False) + 1e-5)
+    np.testing.assert_allclose(rstd.double().cpu().numpy(), rstd_ref.cpu().numpy(), rtol=2e-5)
+    W1h = torch.empty(B, 256, 512, dtype=torch.float16, device="cuda"); W1l = torch.empty_like(W1h)
+    call("op_scale_weight_planes", ptr(W1), ptr(rstd), B, 256, 512, ptr(W1h), ptr(W1l), stream_ptr())
+    assert _rel(_unsplit((W1h, W1l)), W1.double()[None] * rstd.double()[:, None, :]) < 2e-6
+    W2h = torch.zeros_like(W1h); W2l = torch.zeros_like(W1l); rstd2 = torch.zeros_like(rstd)       # the fused form of the two
+    call("op_instnorm_scale_weight_planes", ptr(st), B, parts, N, 1e-5, ptr(W1), 256, 512, ptr(W2h), ptr(W2l), ptr(rstd2), stream_ptr())
+    np.testing.assert_allclose(rstd2.cpu().numpy(), rstd.cpu().numpy(), rtol=1e-6)
+    assert _rel(_unsplit((W2h, W2l)), _unsplit((W1h, W1l))) < 1e-6
+    # layer 1 through the raw entry point (per-frame weight planes are already split)
+    xo = x.clone(); xo_p = (torch.empty(B, N, 256, dtype=torch.float16, device="cuda"), torch.empty(B, N, 256, dtype=torch.float16, device="cuda"))
+    call("op_linear_tc", ptr(hn[0]), ptr(hn[1]), 512, None, None, 0, ptr(W1h), ptr(W1l), ptr(b1), ptr(xo), ptr(xo_p[0]), ptr(xo_p[1]),
+         B, N, 256, 2 | 16 | 64, 0, ptr(xs), None, 1.0, stream_ptr())
+    torch.cuda.synchronize()
+    ref = x.double() + torch.relu(d * rstd_ref[:, None, :]) @ W1.double().t() + b1.double()
+    assert _rel(xo, ref) < 1e-5
+    assert _rel(_unsplit(xo_p), ref) < 1e-5
+    np.testing.assert_allclose(xs[..., 0].double().sum(1).cpu().numpy(), ref.sum(1).cpu().numpy(), rtol=1e-4, atol=1e-3)
