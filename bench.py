@@ -218,10 +218,16 @@ def run_ours(args):
         step_resident()
     clocks = ClockSampler(local_rank)
     clocks.start()
-    ms, pred = timed(step_resident, args.steps, instrument=True)
+    ms, pred = timed(step_resident, args.steps)
     clk = clocks.stop()
+    # per-kernel durations (roofline, shares, launch count): the same K steps once more with CUDA events around every
+    # launch and the 2D / 3D streams serialised on one CUDA stream, so that no launch's interval contains another's
+    model.two_streams = False
+    step_resident()
+    ms_serial, _ = timed(step_resident, args.steps, instrument=True)
+    model.two_streams = True
     summary = timeline.summary()
-    launches = timeline.launches
+    launches = timeline.launches // args.steps
     for _ in range(2):
         step_e2e()
     ms_e2e, pred_e = timed(step_e2e, args.steps)
@@ -270,7 +276,9 @@ def run_ours(args):
                        "db_resident": True, "parallelism": f"dp{world} (objects sharded, no collective)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": launches,
+            "gpu_launches": launches * args.steps, "gpu_launches_per_step": launches,
+            "kernel_timing": {"how": "CUDA events around every launch in a second pass of the same steps with the two matcher "
+                                     "streams serialised on one CUDA stream", "ms_per_step": ms_serial / args.steps},
             "roofline": roofline,
             "roofline_sim_dual_softmax": None if sim is None else {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
             "cpu_baseline": cpu, "clocks": clk, "kernels": kernels, "sanity": sanity,

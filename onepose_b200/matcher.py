@@ -123,6 +123,8 @@ class GATsSuperGlue(nn.Module):
         # projections on the tcgen05 tensor cores (split-precision planes); False = exact-fp32 CUDA-core kernels,
         # kept as the on-device cross-check of the tensor-core path (tests), not as a fallback
         self.use_tensor_cores = True
+        self.two_streams = True      # 2D / 3D streams of a layer on two CUDA streams (tensor-core path)
+        self._side = {}
 
     # ------------------------------------------------------------------ weights in kernel layout
     def _weights_key(self):
@@ -192,6 +194,12 @@ class GATsSuperGlue(nn.Module):
         x = x.contiguous()
         return cls._split(x, torch.empty(x.shape, dtype=torch.float16, device=x.device),
                           torch.empty(x.shape, dtype=torch.float16, device=x.device))
+
+    def _side_stream(self, dev):
+        s = self._side.get(dev.index)
+        if s is None:
+            s = self._side[dev.index] = torch.cuda.Stream(device=dev)
+        return s
 
     def _planes(self, name, shape, dev):
         return (self._ws.get(name + ".hi", shape, torch.float16, dev), self._ws.get(name + ".lo", shape, torch.float16, dev))
@@ -267,12 +275,12 @@ class GATsSuperGlue(nn.Module):
         """Source side of linear attention (:90-97) re-associated for the tensor cores (atb_tc.cu): K' projection with
         column sums, G = K'^T X, then per frame Ksum and P_b = blockdiag(KV') Wm^T.  Returns (ksum, P_b planes)."""
         dev = src_p[0].device
-        kp = self._planes(f"kp{M}", (B, M, _D), dev)
+        kp = self._planes("kp" + tag, (B, M, _D), dev)
         parts = lib.op_linear_tc_stat_parts(M)
-        ks_part = self._ws.get(f"kspart{M}", (B, parts, _D, 2), torch.float32, dev)
+        ks_part = self._ws.get("kspart" + tag, (B, parts, _D, 2), torch.float32, dev)
         self._linear_tc(src_p, lw["Wk_p"], lw["bk"], B, M, Cp=kp, flags=1 | 16, elu_cols=_D, stats=ks_part, tag="k")   # ELU1 | COLSUM
         nch = lib.op_atb_chunks(M)
-        part = self._ws.get(f"gpart{M}", (B, nch, _D, _D), torch.float32, dev)
+        part = self._ws.get("gpart" + tag, (B, nch, _D, _D), torch.float32, dev)
         timeline.work = 2.0 * B * M * _D * _D
         call("op_atb_tc", ptr(kp[0]), ptr(kp[1]), ptr(src_p[0]), ptr(src_p[1]), B, M, ptr(part), stream_ptr())
         ksum = self._ws.get("ksum" + tag, (B, _D), torch.float32, dev)
@@ -281,21 +289,22 @@ class GATsSuperGlue(nn.Module):
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 
-    def _propagate_tc(self, x, x_p, xs, B, N, M, ksum, P, lw, shared_src=False):
+    def _propagate_tc(self, x, x_p, xs, B, N, M, ksum, P, lw, ch, shared_src=False):
         """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place.
-        message = (Q' / (Q'_h . Ksum_h + 1e-6)) P_b^T + bm  ==  merge(linear_attention(q, k, v))  (:98, :119)."""
+        message = (Q' / (Q'_h . Ksum_h + 1e-6)) P_b^T + bm  ==  merge(linear_attention(q, k, v))  (:98, :119).
+        ch names the stream being updated ("2" / "3"): its scratch buffers are its own, the two may run concurrently."""
         dev = x.device
-        q_p = self._planes(f"q{N}", (B, N, _D), dev)
+        q_p = self._planes("q" + ch, (B, N, _D), dev)
         if shared_src:          # one source (ksum [1,256], P_b [1,256,256]) for all B frames: P is an ordinary weight
             ksum = self._ws.get("ksum_bc", (B, _D), torch.float32, dev).copy_(ksum.expand(B, _D))
             P, wflag = (P[0][0], P[1][0]), 0
         else:
             wflag = 64                                                                                            # WBATCHED
         self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 32, elu_cols=_D, ksum=ksum, zscale_num=M, tag="q")     # ELU1 | ZSCALE
-        msg_p = self._planes(f"msg{N}", (B, N, _D), dev)
-        ms = self._ws.get(f"mpart{N}", (B, lib.op_linear_tc_stat_parts(N), _D, 2), torch.float32, dev)
+        msg_p = self._planes("msg" + ch, (B, N, _D), dev)
+        ms = self._ws.get("mpart" + ch, (B, lib.op_linear_tc_stat_parts(N), _D, 2), torch.float32, dev)
         self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=wflag | 16, stats=ms, tag="merge")              # COLSUM of the message
-        self._mlp_tc(x, x_p, xs, msg_p, ms, B, N, lw)
+        self._mlp_tc(x, x_p, xs, msg_p, ms, B, N, lw, ch)
 
     def _colsum(self, x, B, N, name):
         """Per-frame column sums of a plain fp32 tensor, in the partial layout of OPB_LIN_COLSUM."""
@@ -303,18 +312,18 @@ class GATsSuperGlue(nn.Module):
         call("op_colsum_partial", ptr(x), B, N, _D, ptr(part), stream_ptr())
         return part
 
-    def _mlp_tc(self, x, x_p, xs, msg_p, ms, B, N, lw):
+    def _mlp_tc(self, x, x_p, xs, msg_p, ms, B, N, lw, ch):
         """MLP([x | message]) with InstanceNorm + ReLU and the residual add (:135-147, :78,83), without a normalisation
         pass: the mean is analytic (column sums xs / ms of the inputs through W0), layer 0 writes relu(h - mean) as planes,
         1/std is folded into per-frame layer-1 weights.  x, x_p and the column sums xs of x are updated in place."""
         dev = x.device
         parts = lib.op_linear_tc_stat_parts(N)
-        cb = self._ws.get("cbias", (B, 2 * _D), torch.float32, dev)
+        cb = self._ws.get("cbias" + ch, (B, 2 * _D), torch.float32, dev)
         call("op_mlp_center_bias", ptr(xs), parts, ptr(ms), parts, ptr(lw["W0T"]), B, N, ptr(cb), stream_ptr())
-        hn_p = self._planes(f"hn{N}", (B, N, 2 * _D), dev)
-        stats = self._ws.get(f"tcstats{N}", (B, parts, 2 * _D, 2), torch.float32, dev)
+        hn_p = self._planes("hn" + ch, (B, N, 2 * _D), dev)
+        stats = self._ws.get("tcstats" + ch, (B, parts, 2 * _D, 2), torch.float32, dev)
         self._linear_tc(x_p, lw["W0_p"], cb, B, N, A2=msg_p, Cp=hn_p, flags=128 | 256, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
-        W1s = self._planes("W1s", (B, _D, 2 * _D), dev)
+        W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
         call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
              stream_ptr())
         self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=x, Cp=x_p, flags=2 | 16 | 64, stats=xs, tag="mlp1")        # RESIDUAL | COLSUM | WBATCHED
@@ -400,6 +409,10 @@ class GATsSuperGlue(nn.Module):
             x3_p = self._planes("x3", (B, N3, _D), dev)          # filled after the first GATs layer
             xs2 = self._colsum(x2, B, N2, "xs2")
             xs3 = self._ws.get("xs3", (B, lib.op_linear_tc_stat_parts(N3), _D, 2), torch.float32, dev)
+        main = torch.cuda.current_stream(dev)
+        side = self._side_stream(dev) if (tcp and self.two_streams and self._trace is None) else main
+        side.wait_stream(main)
+        ev2 = ev3 = None                 # end of the last cross-layer update of the 2D / 3D stream
 
         def broadcast3():
             x3.copy_(x3s.expand(B, N3, _D))
@@ -435,28 +448,43 @@ class GATsSuperGlue(nn.Module):
                 self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
                 self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
             else:
+                # The 2D stream runs on a side CUDA stream, the 3D stream on the caller's: within a layer the two
+                # updates only meet at the source-side reductions of a 'cross' layer (events below), so the short
+                # launches and the tail of every persistent GEMM of one stream overlap the other's work.
                 B3 = 1 if single3 else B
                 s3_p = x3s_p if single3 else x3_p
+                if ev3 is not None:
+                    side.wait_event(ev3)                          # the 3D stream is done with last layer's "2" reductions
+                if ev2 is not None:
+                    main.wait_event(ev2)
+                ev2 = ev3 = None
                 if kind == "cross":
-                    ka = self._kv_tc(s3_p, B3, N3, lw, "a")       # desc2d attends to desc3d
-                    kb = self._kv_tc(x2_p, B, N2, lw, "b")        # desc3d attends to desc2d
-                    Ma, Mb = N3, N2
-                    self._propagate_tc(x2, x2_p, xs2, B, N2, Ma, *ka, lw, shared_src=single3)
+                    k3 = self._kv_tc(s3_p, B3, N3, lw, "3")       # desc2d attends to desc3d
+                    e3 = main.record_event()
+                    with torch.cuda.stream(side):
+                        k2 = self._kv_tc(x2_p, B, N2, lw, "2")    # desc3d attends to desc2d
+                        e2 = side.record_event()
+                        side.wait_event(e3)
+                        self._propagate_tc(x2, x2_p, xs2, B, N2, N3, *k3, lw, "2", shared_src=single3)
+                        ev2 = side.record_event()
+                    main.wait_event(e2)
                     if single3:                                   # from here on the 3D stream is per frame
                         broadcast3()
                         single3 = False
-                    self._propagate_tc(x3, x3_p, xs3, B, N3, Mb, *kb, lw)
+                    self._propagate_tc(x3, x3_p, xs3, B, N3, N2, *k2, lw, "3")
+                    ev3 = main.record_event()
                 else:
-                    ka = self._kv_tc(x2_p, B, N2, lw, "a")
-                    kb = self._kv_tc(s3_p, B3, N3, lw, "b")
-                    Ma, Mb = N2, N3
-                    self._propagate_tc(x2, x2_p, xs2, B, N2, Ma, *ka, lw)
+                    with torch.cuda.stream(side):
+                        k2 = self._kv_tc(x2_p, B, N2, lw, "2")
+                        self._propagate_tc(x2, x2_p, xs2, B, N2, N2, *k2, lw, "2")
+                    k3 = self._kv_tc(s3_p, B3, N3, lw, "3")
                     if single3:
-                        self._propagate_tc(x3s, x3s_p, xs3s, 1, N3, Mb, *kb, lw)
+                        self._propagate_tc(x3s, x3s_p, xs3s, 1, N3, N3, *k3, lw, "3")
                     else:
-                        self._propagate_tc(x3, x3_p, xs3, B, N3, Mb, *kb, lw)
+                        self._propagate_tc(x3, x3_p, xs3, B, N3, N3, *k3, lw, "3")
             if self._trace is not None:
                 self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
+        main.wait_stream(side)
         if single3:                                               # no cross layer at all (not the shipped layer list)
             broadcast3()
 

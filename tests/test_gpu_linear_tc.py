@@ -120,6 +120,27 @@ def test_matcher_tensor_core_path_vs_cuda_core_path(damped):
         helpers.assert_matches_equal_off_ties(m0_tc[b].cpu(), pred_cc["matches0_batched"][b].cpu(), conf_cc[b].cpu(), axis=2)
 
 
+@pytest.mark.parametrize("n2,n3,shared", [(450, 700, True), (512, 512, False)])
+def test_two_stream_schedule_gives_the_same_bits_as_one_stream(n2, n3, shared):
+    """The 2D / 3D streams of a layer run on two CUDA streams; scratch buffers are per stream (also when N2 == N3) and the
+    cross-layer hand-over is ordered by events, so the result may not depend on the schedule."""
+    from onepose_b200.matcher import GATsSuperGlue
+    obj = synth.make_object(2, n3, 8)
+    frames = [synth.make_frame(obj, f, n2) for f in range(3)]
+    data = {k: v.cuda() for k, v in synth.pack_batch(obj, frames).items()}
+    if not shared:                                   # per-frame DB copies: no shared-prefix shortcut
+        data = {k: v.contiguous() for k, v in data.items()}
+    m = GATsSuperGlue(dict(synth.DEFAULT_HPARAMS)).cuda().eval()
+    m.load_state_dict(synth.make_weights(0, damped=True), strict=True)
+    outs = []
+    for two in (True, False, True):
+        m.two_streams = two
+        pred, conf = m(data)
+        outs.append((conf.clone(), pred["matches0_batched"].clone(), pred["matching_scores0_batched"].clone()))
+    for o in outs[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(outs[0], o))
+
+
 @pytest.mark.parametrize("shape", [(1, 512), (2, 700), (3, 33), (1, 2048)])
 def test_atb_tc_and_kv_post_vs_float64_linear_attention(shape):
     """G = K'^T X on MN-major UMMA operands, then KV' / Ksum / P_b against a float64 restatement of :88-99,119."""
