@@ -72,6 +72,7 @@ int op_gats_leaf_aggregate(const float *leaf, long long leaf_bstride, const floa
 #define OPB_LIN_WBATCHED 64  /* op_linear_tc: W planes are [B, Cout, K], one matrix per frame */
 #define OPB_LIN_BIASB 128     /* op_linear_tc: bias is [B, Cout], one vector per frame */
 #define OPB_LIN_CSTATS_RELU 256 /* op_linear_tc: stats_partial = (sum, sum of squares) of the value after bias over the valid rows, then ReLU */
+#define OPB_LIN_W2BATCHED 512 /* op_linear_tc: the second weight W2 is [B, Cout, K2], one matrix per frame */
 int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
               float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,
               const float *mean, const float *rstd, double *stats_partial, void *stream);
@@ -97,7 +98,8 @@ int op_attn_apply(const float *Qp, const float *KV, const float *Ksum, float *ou
  * (hi*hi + lo*hi + hi*lo) accumulated in fp32 TMEM, which keeps conf_matrix within the 1e-3 bound
  * where a single fp16/bf16/tf32 pass does not (precision).  Plane pointers are void*
  * (fp16 storage), 16-byte aligned; K1, K2 multiples of 64; Cout 256 or 512.
- * op_linear_tc: C = epi([A1|A2] . W^T); outputs fp32 C and/or planes (Ch, Cl) for the next GEMM.
+ * op_linear_tc: C = epi([A1|A2] . W^T), or with W2 planes given C = epi(A1 . W^T + A2 . W2^T) (W [Cout,K1], W2 [Cout,K2] or
+ * [B,Cout,K2] with OPB_LIN_W2BATCHED); outputs fp32 C and/or planes (Ch, Cl) for the next GEMM.
  * flags: OPB_LIN_ELU1, OPB_LIN_RESIDUAL (C += result, needs C), OPB_LIN_STATS (stats_partial
  * [B][op_linear_tc_stat_parts(rows)][Cout][2] fp32 partial sum / sum of squares of the result
  * WITHOUT the bias; op_instnorm_finalize_tc folds them in float64 and adds the bias to the mean). */
@@ -105,19 +107,25 @@ int op_split_planes(const float *x, void *hi, void *lo, long long n, void *strea
 int op_norm_relu_split(const float *h, const float *mean, const float *rstd, void *hi, void *lo, int B, int rows,
                        int C, void *stream);
 int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
-                 const void *Wl, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
-                 int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream);
+                 const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B,
+                 int rows_per_batch, int Cout, int flags, int elu_cols, float *stats_partial, const float *ksum,
+                 float zscale_num, void *stream);
 int op_linear_tc_stat_parts(int rows_per_batch);
-/* InstanceNorm1d of the MLP (:135-147) without a normalisation pass over the hidden tensor:
- *   - the per-channel mean of layer 0's output is analytic, W0 mean_rows([x | msg]) + b0, from the column sums of its inputs
- *     (OPB_LIN_COLSUM partials of their producers, or op_colsum_partial [B][op_linear_tc_stat_parts(rows)][C][2] for a plain tensor):
- *     op_mlp_center_bias writes the per-frame bias -(W0 mean_in) [B,512] (W0T = W0 transposed, [512 k][512 c]);
+/* The merge projection folded into MLP layer 0 (:119,135-147): message = Q'' P_b^T + bm and h = W0 [x | message] + b0, so
+ *   h = W0a x + (W0b P_b) Q'' + const = W0a x + P'_b Q'' + const, with P'_b[c,(h,d)] = sum_q KV_h[d,q] (W0b Wm)[c,(h,q)] straight from
+ *   op_kv_post (n_out = 512, WmT = the static product W0b Wm laid out [4,64,512]); the constant (W0b bm + b0) is removed by
+ *   InstanceNorm1d and never added.  Layer 0 is then op_linear_tc(A1 = x, W = W0a, A2 = Q'', W2 = P'_b, OPB_LIN_W2BATCHED).
+ * InstanceNorm1d of the MLP without a normalisation pass over the hidden tensor:
+ *   - the per-channel mean of layer 0's output is analytic, W0a mean_rows(x) + P'_b mean_rows(Q'') + const, from the column sums of
+ *     its inputs (OPB_LIN_COLSUM partials of their producers, or op_colsum_partial [B][op_linear_tc_stat_parts(rows)][C][2] for a
+ *     plain tensor): op_mlp_center_bias writes the per-frame bias -(W0a mean_x + P'_b mean_q) [B,512] (W0aT = W0[:, :256]
+ *     transposed, [256 k][512 c]; P planes [B or 1][512][256], p_batched says which);
  *   - layer 0 then runs with OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU: output planes hold relu(h - mean), stats the centred sums;
  *   - op_instnorm_finalize_tc gives rstd, op_scale_weight_planes folds it into layer 1's weights: W1s[b,o,c] = W1[o,c] rstd[b,c]
  *     (planes [B,Cout,K]), used with OPB_LIN_WBATCHED. */
 int op_colsum_partial(const float *x, int B, int rows, int C, float *partial, void *stream);
-int op_mlp_center_bias(const float *xpart, int xparts, const float *mpart, int mparts, const float *W0T, int B, int rows,
-                       float *bias_out, void *stream);
+int op_mlp_center_bias(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
+                       const void *Pl, int p_batched, int B, int rows, float *bias_out, void *stream);
 int op_scale_weight_planes(const float *W, const float *rstd, int B, int Cout, int K, void *hi, void *lo, void *stream);
 /* op_instnorm_finalize_tc + op_scale_weight_planes in one launch: rstd from the CSTATS_RELU partials [B][parts][K][2] straight
  * into the per-frame layer-1 weight planes [B,Cout,K] (K a multiple of 64); rstd [B,K] is written too when not NULL. */
@@ -129,13 +137,13 @@ int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B
  * materialised: op_atb_tc computes per-chunk partials of G = K'^T X over the M source points (A = K' planes, B = X
  * planes, both [B, M, 256]; partial [B][op_atb_chunks(M)][256][256] fp32); op_kv_post folds them and the OPB_LIN_COLSUM
  * partials of K' (ksum_partial [B][nparts][256][2]) and emits ksum [B,256], optionally KV [B,4,64,64] (:96, scaled by inv_m = 1/M),
- * and the per-frame matrix P_b[o,(h,d)] = sum_q KV_h[d,q] Wm[o,(h,q)] as planes [B,256,256], so that
+ * and the per-frame matrix P_b[o,(h,d)] = sum_q KV_h[d,q] Wm[o,(h,q)] as planes [B,n_out,256] (n_out = 256 or 512 rows of Wm), so that
  * message = (Q' M / (Q'_h.Ksum_h + 1e-6)) P_b^T + bm is one op_linear_tc call (OPB_LIN_ZSCALE on the Q projection,
- * OPB_LIN_WBATCHED on the merge).  Head-major weights, transposed for coalesced reads: WvT [4,256,64] = Wv[h*64+q, c], bv [256], WmT [4,64,256] = Wm[o, h*64+q]. */
+ * OPB_LIN_WBATCHED on the merge).  Head-major weights, transposed for coalesced reads: WvT [4,256,64] = Wv[h*64+q, c], bv [256], WmT [4,64,n_out] = Wm[o, h*64+q]. */
 int op_atb_chunks(int M);
 int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const void *Bl, int B, int M, float *partial, void *stream);
 int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *WvT, const float *bv,
-               const float *WmT, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream);
+               const float *WmT, int n_out, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream);
 /* op_attn_apply writing split-precision planes instead of fp32 */
 int op_attn_apply_planes(const float *Qp, const float *KV, const float *Ksum, void *out_hi, void *out_lo, int B, int N,
                          int M, void *stream);

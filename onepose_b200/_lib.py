@@ -36,16 +36,16 @@ _SIGS = {
     "op_attn_apply": (i32, [vp, vp, vp, vp, i32, i32, i32, vp]),
     "op_split_planes": (i32, [vp, vp, vp, i64, vp]),
     "op_norm_relu_split": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
-    "op_linear_tc": (i32, [vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, f32, vp]),
+    "op_linear_tc": (i32, [vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, f32, vp]),
     "op_linear_tc_stat_parts": (i32, [i32]),
     "op_colsum_partial": (i32, [vp, i32, i32, i32, vp, vp]),
-    "op_mlp_center_bias": (i32, [vp, i32, vp, i32, vp, i32, i32, vp, vp]),
+    "op_mlp_center_bias": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp]),
     "op_scale_weight_planes": (i32, [vp, vp, i32, i32, i32, vp, vp, vp]),
     "op_instnorm_finalize_tc": (i32, [vp, vp, i32, i32, i32, i32, f32, vp, vp, vp]),
     "op_instnorm_scale_weight_planes": (i32, [vp, i32, i32, i32, f32, vp, i32, i32, vp, vp, vp, vp]),
     "op_atb_chunks": (i32, [i32]),
     "op_atb_tc": (i32, [vp, vp, vp, vp, i32, i32, vp, vp]),
-    "op_kv_post": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, f32, vp, vp, vp, vp, vp]),
+    "op_kv_post": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, f32, vp, vp, vp, vp, vp]),
     "op_attn_apply_planes": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
     "op_l2_normalize_rows": (i32, [vp, vp, i64, i32, vp]),
     "op_sim_dual_softmax_workspace_bytes": (sz, [i32, i32, i32]),

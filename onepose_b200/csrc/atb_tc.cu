@@ -138,13 +138,13 @@ namespace opb {
 namespace atb {
 
 // per (head h, frame b, group of 16 channels d): G = sum of chunk partials; Ksum = sum of column-sum partials;
-// KV_h[d,:] = (G_h[d,:] Wv_h^T + Ksum_h[d] bv_h^T) / M;  P_b[o, h*64+d] = sum_q KV_h[d,q] Wm[o, h*64+q] written as
+// KV_h[d,:] = (G_h[d,:] Wv_h^T + Ksum_h[d] bv_h^T) / M;  P_b[o, h*64+d] = sum_q KV_h[d,q] Wm[o, h*64+q], o < n_out, written as
 // split-precision planes (x64).  All folds in a fixed order.
 constexpr int kPostD = 16;
 __global__ void __launch_bounds__(256)
 k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
           const float *__restrict__ WvT /* [4][256 c][64 q] = Wv[h*64+q][c] */, const float *__restrict__ bv,
-          const float *__restrict__ WmT /* [4][64 q][256 o] = Wm[o][h*64+q] */, float inv_m, float *__restrict__ ksum /* [B][256] */,
+          const float *__restrict__ WmT /* [4][64 q][n_out o] = Wm[o][h*64+q] */, int n_out, float inv_m, float *__restrict__ ksum /* [B][256] */,
           float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
     __shared__ float G[kPostD][256];
     __shared__ float KV[kPostD][65];
@@ -199,11 +199,10 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
         }
     }
     __syncthreads();
-    {   // P[o][ch0 + d], thread = o
-        const int o = tid;
+    for (int o = tid; o < n_out; o += 256) {   // P[o][ch0 + d], thread = o
         float wm[64];
 #pragma unroll
-        for (int q = 0; q < 64; ++q) wm[q] = __ldg(WmT + ((long long)h * 64 + q) * 256 + o);     // coalesced over o
+        for (int q = 0; q < 64; ++q) wm[q] = __ldg(WmT + ((long long)h * 64 + q) * n_out + o);     // coalesced over o
         uint32_t hh[kPostD / 2], ll[kPostD / 2];
 #pragma unroll
         for (int d = 0; d < kPostD; d += 2) {
@@ -215,8 +214,8 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
             hh[d / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
             ll[d / 2] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
         }
-        uint4 *ph = reinterpret_cast<uint4 *>(Ph + ((long long)b * 256 + o) * 256 + ch0);
-        uint4 *pl = reinterpret_cast<uint4 *>(Pl + ((long long)b * 256 + o) * 256 + ch0);
+        uint4 *ph = reinterpret_cast<uint4 *>(Ph + ((long long)b * n_out + o) * 256 + ch0);
+        uint4 *pl = reinterpret_cast<uint4 *>(Pl + ((long long)b * n_out + o) * 256 + ch0);
         ph[0] = make_uint4(hh[0], hh[1], hh[2], hh[3]); ph[1] = make_uint4(hh[4], hh[5], hh[6], hh[7]);
         pl[0] = make_uint4(ll[0], ll[1], ll[2], ll[3]); pl[1] = make_uint4(ll[4], ll[5], ll[6], ll[7]);
     }
@@ -248,12 +247,12 @@ extern "C" int op_atb_tc(const void *Ah, const void *Al, const void *Bh, const v
 }
 
 extern "C" int op_kv_post(const float *partial, int nchunks, const float *ksum_partial, int nparts, const float *WvT, const float *bv,
-                          const float *WmT, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream) {
+                          const float *WmT, int n_out, int B, float inv_m, float *ksum, float *kv_out, void *Ph, void *Pl, void *stream) {
     using namespace opb;
     OPB_CHECK_ARG(partial && ksum_partial && WvT && bv && WmT && ksum && Ph && Pl, "op_kv_post: null pointer");
-    OPB_CHECK_ARG(B > 0 && nchunks > 0 && nparts > 0 && B <= 65535, "op_kv_post: bad shape");
+    OPB_CHECK_ARG(B > 0 && nchunks > 0 && nparts > 0 && B <= 65535 && n_out > 0 && n_out % 256 == 0, "op_kv_post: bad shape (n_out=%d)", n_out);
     atb::k_kv_post<<<dim3(4, 64 / atb::kPostD, B), 256, 0, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, WvT, bv, WmT,
-                                                                            inv_m, ksum, kv_out, (__half *)Ph, (__half *)Pl);
+                                                                            n_out, inv_m, ksum, kv_out, (__half *)Ph, (__half *)Pl);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

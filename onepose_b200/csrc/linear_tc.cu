@@ -67,22 +67,25 @@ __global__ void k_colsum_partial(const float *__restrict__ x, int rows, int C, i
     }
 }
 
-// Analytic InstanceNorm mean of MLP layer 0 (:135-147): mean_rows([x | msg] W0^T + b0) = W0 mean_rows([x | msg]) + b0, so the
-// centred pre-activation is obtained with the per-frame bias  -(W0 mean_in)  (b0 cancels).  W0T is [512 k][512 c].
-// One cluster of 8 CTAs per frame: CTA r folds the column-sum partials of input channels [64r, 64r+64) (4 slices of
-// the parts per channel, fixed order), the 512 means are exchanged through distributed shared memory, and CTA r then
-// produces output columns [64r, 64r+64) with the k range cut into 4 slices.
+// Analytic InstanceNorm mean of MLP layer 0 with the merge projection folded in (:119,135-147):
+//   mean_rows(h) = W0a mean_rows(x) + P'_b mean_rows(Q'') + const, so the centred pre-activation is obtained with the per-frame
+// bias  -(W0a mean_x + P'_b mean_q)  (the constants cancel).  W0aT is [256 k][512 c], P' planes [B or 1][512 c][256 j] (x64).
+// One cluster of 8 CTAs per frame: CTA r folds the column-sum partials of input channels [64r, 64r+64) of [x | Q''] (4 slices
+// of the parts per channel, fixed order), the 512 means are exchanged through distributed shared memory, and CTA r then
+// produces output columns [64r, 64r+64): the W0a part with k cut into 4 slices, the P' part with one warp per row.
 __global__ void __cluster_dims__(1, 8, 1) __launch_bounds__(256)
-k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__restrict__ mpart, int mparts,
-                  const float *__restrict__ W0T, int rows, float *__restrict__ bias_out) {
+k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__restrict__ qpart, int qparts,
+                  const float *__restrict__ W0aT, const __half *__restrict__ Ph, const __half *__restrict__ Pl, int p_batched,
+                  int rows, float *__restrict__ bias_out) {
     __shared__ float red[4][64];
     __shared__ float mean_loc[64];
-    __shared__ float mean_in[512];
+    __shared__ __align__(16) float mean_in[512];
+    __shared__ float pdot[64];
     cg::cluster_group cluster = cg::this_cluster();
     const int b = blockIdx.x, r = blockIdx.y, tid = threadIdx.x, j = tid & 63, sl = tid >> 6;
     {
-        const float2 *src = r < 4 ? xpart : mpart;
-        const int parts = r < 4 ? xparts : mparts;
+        const float2 *src = r < 4 ? xpart : qpart;
+        const int parts = r < 4 ? xparts : qparts;
         const int kk = (r & 3) * 64 + j;
         double s = 0;
         for (int t = sl; t < parts; t += 4) s += (double)src[((long long)b * parts + t) * 256 + kk].x;
@@ -96,10 +99,29 @@ k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__
     const int c = r * 64 + j;
     float acc = 0.f;
 #pragma unroll 8
-    for (int k = sl * 128; k < sl * 128 + 128; ++k) acc = fmaf(__ldg(W0T + (long long)k * 512 + c), mean_in[k], acc);
+    for (int k = sl * 64; k < sl * 64 + 64; ++k) acc = fmaf(__ldg(W0aT + (long long)k * 512 + c), mean_in[k], acc);
     red[sl][j] = acc;
+    {   // P' rows of this CTA: warp w takes rows 8w .. 8w+7, lane l the 8 columns 8l .. 8l+7 of both planes
+        const int warp = tid >> 5, lane = tid & 31;
+        const float4 m0 = *reinterpret_cast<const float4 *>(mean_in + 256 + lane * 8), m1 = *reinterpret_cast<const float4 *>(mean_in + 260 + lane * 8);
+        const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        for (int i = 0; i < 8; ++i) {
+            const long long off = (((long long)(p_batched ? b : 0) * 512) + r * 64 + warp * 8 + i) * 256 + lane * 8;
+            const uint4 h4 = __ldg(reinterpret_cast<const uint4 *>(Ph + off)), l4 = __ldg(reinterpret_cast<const uint4 *>(Pl + off));
+            const __half2 *hh = reinterpret_cast<const __half2 *>(&h4), *ll = reinterpret_cast<const __half2 *>(&l4);
+            float d = 0.f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 a = __half22float2(hh[q]), e = __half22float2(ll[q]);
+                d = fmaf(a.x + e.x, m[2 * q], d); d = fmaf(a.y + e.y, m[2 * q + 1], d);
+            }
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+            if (lane == 0) pdot[warp * 8 + i] = d * (1.f / lintc::kScale);
+        }
+    }
     __syncthreads();
-    if (tid < 64) bias_out[(long long)b * 512 + r * 64 + tid] = -((red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid]));
+    if (tid < 64) bias_out[(long long)b * 512 + r * 64 + tid] = -(((red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid])) + pdot[tid]);
 }
 
 // InstanceNorm statistics of the centred layer-0 output (OPB_LIN_CSTATS_RELU partials) -> rstd, folded straight into the
@@ -197,10 +219,12 @@ extern "C" int op_colsum_partial(const float *x, int B, int rows, int C, float *
     return OPB_OK;
 }
 
-extern "C" int op_mlp_center_bias(const float *xpart, int xparts, const float *mpart, int mparts, const float *W0T, int B, int rows,
-                                  float *bias_out, void *stream) {
-    OPB_CHECK_ARG(xpart && mpart && W0T && bias_out && B > 0 && rows > 0 && xparts > 0 && mparts > 0 && B <= 65535, "op_mlp_center_bias: bad argument");
-    opb::k_mlp_center_bias<<<dim3(B, 8), 256, 0, (cudaStream_t)stream>>>((const float2 *)xpart, xparts, (const float2 *)mpart, mparts, W0T, rows, bias_out);
+extern "C" int op_mlp_center_bias(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
+                                  const void *Pl, int p_batched, int B, int rows, float *bias_out, void *stream) {
+    OPB_CHECK_ARG(xpart && qpart && W0aT && Ph && Pl && bias_out && B > 0 && rows > 0 && xparts > 0 && qparts > 0 && B <= 65535,
+                  "op_mlp_center_bias: bad argument");
+    opb::k_mlp_center_bias<<<dim3(B, 8), 256, 0, (cudaStream_t)stream>>>((const float2 *)xpart, xparts, (const float2 *)qpart, qparts, W0aT,
+                                                                         (const __half *)Ph, (const __half *)Pl, p_batched, rows, bias_out);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }
@@ -237,12 +261,14 @@ extern "C" int op_instnorm_finalize_tc(const float *stats_partial, const float *
 }
 
 extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
-                            const void *Wl, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
+                            const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
                             int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream) {
     using namespace opb;
     OPB_CHECK_ARG(A1h && A1l && Wh && Wl, "op_linear_tc: null operand plane");
     OPB_CHECK_ARG(K1 > 0 && K1 % lintc::BK == 0 && K2 >= 0 && K2 % lintc::BK == 0, "op_linear_tc: K1=%d K2=%d must be multiples of 64", K1, K2);
     OPB_CHECK_ARG((K2 == 0) == (A2h == nullptr) && (A2h == nullptr) == (A2l == nullptr), "op_linear_tc: A2/K2 mismatch");
+    OPB_CHECK_ARG((W2h == nullptr) == (W2l == nullptr) && (!W2h || K2), "op_linear_tc: W2 planes come together and need A2");
+    OPB_CHECK_ARG(!(flags & OPB_LIN_W2BATCHED) || W2h, "op_linear_tc: W2BATCHED without W2");
     OPB_CHECK_ARG(Cout > 0 && Cout % lintc::BN == 0 && Cout <= lintc::BIAS_FLOATS, "op_linear_tc: Cout=%d must be 256 or 512", Cout);
     OPB_CHECK_ARG(C || Ch, "op_linear_tc: no output requested");
     OPB_CHECK_ARG((Ch == nullptr) == (Cl == nullptr), "op_linear_tc: Ch/Cl must come together");
@@ -258,8 +284,8 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(!(flags & OPB_LIN_ELU1) || elu_cols % 32 == 0, "op_linear_tc: elu_cols must be a multiple of 32");
     OPB_CHECK_ARG(B >= 0 && rows_per_batch >= 0, "op_linear_tc: bad B=%d rows=%d", B, rows_per_batch);
     if (B == 0 || rows_per_batch == 0) return OPB_OK;
-    const int K = K1 + K2;
-    CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl, tc_, tch, tcl;
+    const int K = W2h ? K1 : K1 + K2;                 // columns of W
+    CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl;
     int rc;
     if ((rc = make_tmap_f16_3d(&ta1h, A1h, B, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, B, rows_per_batch, K1, lintc::BM)) ||
         (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, lintc::BN)) ||
@@ -270,6 +296,12 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
             return rc;
     } else {
         ta2h = ta1h; ta2l = ta1l;
+    }
+    if (W2h) {
+        const int wb = (flags & OPB_LIN_W2BATCHED) ? B : 1;
+        if ((rc = make_tmap_f16_3d(&tw2h, W2h, wb, Cout, K2, lintc::BN)) || (rc = make_tmap_f16_3d(&tw2l, W2l, wb, Cout, K2, lintc::BN))) return rc;
+    } else {
+        tw2h = twh; tw2l = twl;
     }
     OPB_CHECK_ARG(((uintptr_t)C | (uintptr_t)Ch | (uintptr_t)Cl) % 16 == 0, "op_linear_tc: outputs must be 16-byte aligned");
     if (C) { if ((rc = make_tmap_f32_3d_store(&tc_, C, B, rows_per_batch, Cout, 32))) return rc; } else tc_ = ta1h;
@@ -284,13 +316,14 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     p.total_tiles = (int)total;
     p.bias = bias; p.C = C; p.Ch = (__half *)Ch; p.Cl = (__half *)Cl; p.stats = (float2 *)stats_partial;
     p.ksum = ksum; p.zscale_num = zscale_num; p.w_batched = (flags & OPB_LIN_WBATCHED) ? 1 : 0;
+    p.w2 = W2h ? ((flags & OPB_LIN_W2BATCHED) ? 2 : 1) : 0;
     static bool configured = false;
     if (!configured) {
         OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::SMEM_BYTES));
         configured = true;
     }
     const int grid = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
-    lintc::k_linear_tc<<<grid, lintc::THREADS, lintc::SMEM_BYTES, (cudaStream_t)stream>>>(ta1h, ta1l, ta2h, ta2l, twh, twl, tc_, tch, tcl, p);
+    lintc::k_linear_tc<<<grid, lintc::THREADS, lintc::SMEM_BYTES, (cudaStream_t)stream>>>(ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

@@ -42,6 +42,7 @@ struct Params {
     const float *ksum;             // ZSCALE: [B][Cout] per-frame Ksum; every 64-column head of a row is divided by (row_head . ksum_head + 1e-6)
     float zscale_num;              // ZSCALE numerator: the source length M of :94,98 (z = M / (q.ksum + 1e-6))
     int w_batched;                 // W planes are [B][Cout][K] (one matrix per frame)
+    int w2;                        // 0: W spans K1+K2 columns; 1: the A2 part has its own weight W2 [Cout][K2]; 2: W2 is [B][Cout][K2]
 };
 
 struct Barriers {
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ CUtensorMap tm_a1l,
             const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
             const __grid_constant__ CUtensorMap tm_wh, const __grid_constant__ CUtensorMap tm_wl,
+            const __grid_constant__ CUtensorMap tm_w2h, const __grid_constant__ CUtensorMap tm_w2l,
             const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_ch, const __grid_constant__ CUtensorMap tm_cl,
             const Params p) {
     // SWIZZLE_128B operands need a 1024-byte aligned base: the dynamic shared window of a kernel without static shared memory
@@ -107,6 +109,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_a1h); tc::tma_prefetch_desc(&tm_a1l); tc::tma_prefetch_desc(&tm_wh); tc::tma_prefetch_desc(&tm_wl);
         if (p.K2) { tc::tma_prefetch_desc(&tm_a2h); tc::tma_prefetch_desc(&tm_a2l); }
+        if (p.w2) { tc::tma_prefetch_desc(&tm_w2h); tc::tma_prefetch_desc(&tm_w2l); }
         if (p.C) tc::tma_prefetch_desc(&tm_c);
         if (p.Ch) { tc::tma_prefetch_desc(&tm_ch); tc::tma_prefetch_desc(&tm_cl); }
     }
@@ -129,13 +132,16 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     uint8_t *st = smem + stage * STAGE_BYTES;
                     const bool second = kb >= nkb1;
                     const int ka = (second ? kb - nkb1 : kb) * BK;
+                    const bool own_w2 = second && p.w2;                    // the A2 part multiplies its own (per-frame) weight
+                    const int kw = own_w2 ? ka : kb * BK;
+                    const int wb = own_w2 ? (p.w2 == 2 ? b : 0) : (p.w_batched ? b : 0);
                     tc::mbar_wait(&bar->empty[stage], ph ^ 1);
                     tc::mbar_arrive_expect_tx(&bar->full_hi[stage], HALF_BYTES);
                     tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, b);
-                    tc::tma_load_3d(st + A_PLANE, &tm_wh, &bar->full_hi[stage], kb * BK, ct * BN, p.w_batched ? b : 0);
+                    tc::tma_load_3d(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, &bar->full_hi[stage], kw, ct * BN, wb);
                     tc::mbar_arrive_expect_tx(&bar->full_lo[stage], HALF_BYTES);
                     tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, b);
-                    tc::tma_load_3d(st + HALF_BYTES + A_PLANE, &tm_wl, &bar->full_lo[stage], kb * BK, ct * BN, p.w_batched ? b : 0);
+                    tc::tma_load_3d(st + HALF_BYTES + A_PLANE, own_w2 ? &tm_w2l : &tm_wl, &bar->full_lo[stage], kw, ct * BN, wb);
                 }
             }
         }

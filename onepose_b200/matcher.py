@@ -158,13 +158,21 @@ class GATsSuperGlue(nn.Module):
                     WmT=f(at.merge.weight[:, :, 0])[:, perm].view(_D, _HEADS, 64).permute(1, 2, 0).contiguous(),   # [h, q, o]
                     Wkv=torch.cat([wk, wv], 0).contiguous(), bkv=torch.cat([bk, bv], 0).contiguous(),
                     Wm=f(at.merge.weight[:, :, 0])[:, perm].contiguous(), bm=f(at.merge.bias),
-                    W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias), W0T=f(mlp[0].weight[:, :, 0].t()),
+                    W0=f(mlp[0].weight[:, :, 0]), b0=f(mlp[0].bias),
                     W1=f(mlp[3].weight[:, :, 0]), b1=f(mlp[3].bias)))
+                # merge folded into MLP layer 0 (tensor-core path): h = W0a x + (W0b Wm) attn + const, and the constant
+                # (W0b bm + b0) is removed by InstanceNorm1d -- op_kv_post builds P'_b = KV' (W0b Wm)^T per frame
+                lw = packed[-1]
+                w0 = mlp[0].weight[:, :, 0].detach().to(device=device, dtype=torch.float64)
+                w0m = (w0[:, _D:] @ at.merge.weight[:, :, 0].detach().to(device=device, dtype=torch.float64))[:, perm]
+                lw["W0mT"] = w0m.float().view(2 * _D, _HEADS, 64).permute(1, 2, 0).contiguous()       # [h, q, c]
+                lw["W0a"] = f(w0[:, :_D])
+                lw["W0aT"] = f(w0[:, :_D].t())                                                      # [k, c]
         self._packed = dict(layers=packed, Wf=f(self.final_proj.weight[:, :, 0]), bf=f(self.final_proj.bias))
         # split-precision fp16 planes of every projection weight for the tcgen05 path (linear_tc.cuh)
         with torch.cuda.device(device):
             for lw in packed:
-                for k in ("Wq", "Wk", "Wkv", "Wm", "W0", "W1"):
+                for k in ("Wq", "Wk", "W0a"):
                     if k in lw:
                         lw[k + "_p"] = self._split_new(lw[k])
             self._packed["Wf_p"] = self._split_new(self._packed["Wf"])
@@ -261,19 +269,20 @@ class GATsSuperGlue(nn.Module):
         self._linear(h, lw["W1"], lw["b1"], x, B, N, flags=2 | 8, mean=mean, rstd=rstd, tag="mlp1")   # NORM_RELU in, RESIDUAL out
 
     # ------------------------------------------------------------------ tcgen05 launchers (linear_tc.cuh)
-    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, ksum=None, zscale_num=1.0, tag=""):
-        """A1/A2/W/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp."""
+    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, W2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, ksum=None, zscale_num=1.0, tag=""):
+        """A1/A2/W/W2/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp."""
         K1 = A1[0].shape[-1]
         K2 = 0 if A2 is None else A2[0].shape[-1]
         Cout = W[0].shape[-2]
         timeline.work = 2.0 * B * rows * (K1 + K2) * Cout
         call("op_linear_tc", ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
-             ptr(W[0]), ptr(W[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
+             ptr(W[0]), ptr(W[1]), ptr(W2[0]) if W2 else None, ptr(W2[1]) if W2 else None, ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
              B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr(), tag=tag)
 
     def _kv_tc(self, src_p, B, M, lw, tag):
         """Source side of linear attention (:90-97) re-associated for the tensor cores (atb_tc.cu): K' projection with
-        column sums, G = K'^T X, then per frame Ksum and P_b = blockdiag(KV') Wm^T.  Returns (ksum, P_b planes)."""
+        column sums, G = K'^T X, then per frame Ksum and P'_b = W0b Wm blockdiag(KV')^T [512,256] (merge and the message half
+        of MLP layer 0 in one matrix).  Returns (ksum, P'_b planes)."""
         dev = src_p[0].device
         kp = self._planes("kp" + tag, (B, M, _D), dev)
         parts = lib.op_linear_tc_stat_parts(M)
@@ -284,49 +293,45 @@ class GATsSuperGlue(nn.Module):
         timeline.work = 2.0 * B * M * _D * _D
         call("op_atb_tc", ptr(kp[0]), ptr(kp[1]), ptr(src_p[0]), ptr(src_p[1]), B, M, ptr(part), stream_ptr())
         ksum = self._ws.get("ksum" + tag, (B, _D), torch.float32, dev)
-        P = self._planes("P" + tag, (B, _D, _D), dev)
-        call("op_kv_post", ptr(part), nch, ptr(ks_part), parts, ptr(lw["WvT"]), ptr(lw["bv"]), ptr(lw["WmT"]), B, 1.0 / M, ptr(ksum), None,
+        P = self._planes("P" + tag, (B, 2 * _D, _D), dev)
+        call("op_kv_post", ptr(part), nch, ptr(ks_part), parts, ptr(lw["WvT"]), ptr(lw["bv"]), ptr(lw["W0mT"]), 2 * _D, B, 1.0 / M, ptr(ksum), None,
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 
     def _propagate_tc(self, x, x_p, xs, B, N, M, ksum, P, lw, ch, shared_src=False):
-        """x-side of AttentionPropagation on the tensor cores; x (fp32) and its planes x_p are updated in place.
-        message = (Q' / (Q'_h . Ksum_h + 1e-6)) P_b^T + bm  ==  merge(linear_attention(q, k, v))  (:98, :119).
+        """x-side of AttentionPropagation on the tensor cores; x (fp32), its planes x_p and its column sums xs are updated
+        in place.  With Q'' = Q' M / (Q'_h . Ksum_h + 1e-6)  (:97-98):  message = Q'' P_b^T + bm  (:119), and the MLP's first
+        layer sees it only through W0b, so  h = W0a x + P'_b Q'' + const  -- the merge projection is never run.
+        InstanceNorm + ReLU (:144-146) without a normalisation pass: the mean is analytic (column sums of x and Q'' through
+        W0a / P'_b), layer 0 writes relu(h - mean) as planes, 1/std is folded into per-frame layer-1 weights.
         ch names the stream being updated ("2" / "3"): its scratch buffers are its own, the two may run concurrently."""
         dev = x.device
-        q_p = self._planes("q" + ch, (B, N, _D), dev)
-        if shared_src:          # one source (ksum [1,256], P_b [1,256,256]) for all B frames: P is an ordinary weight
+        parts = lib.op_linear_tc_stat_parts(N)
+        if shared_src:          # one source (ksum [1,256], P'_b [1,512,256]) for all B frames: P' is an ordinary weight
             ksum = self._ws.get("ksum_bc", (B, _D), torch.float32, dev).copy_(ksum.expand(B, _D))
-            P, wflag = (P[0][0], P[1][0]), 0
+            P, pflag = (P[0][0], P[1][0]), 0
         else:
-            wflag = 64                                                                                            # WBATCHED
-        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 32, elu_cols=_D, ksum=ksum, zscale_num=M, tag="q")     # ELU1 | ZSCALE
-        msg_p = self._planes("msg" + ch, (B, N, _D), dev)
-        ms = self._ws.get("mpart" + ch, (B, lib.op_linear_tc_stat_parts(N), _D, 2), torch.float32, dev)
-        self._linear_tc(q_p, P, lw["bm"], B, N, Cp=msg_p, flags=wflag | 16, stats=ms, tag="merge")              # COLSUM of the message
-        self._mlp_tc(x, x_p, xs, msg_p, ms, B, N, lw, ch)
+            pflag = 512                                                                                           # W2BATCHED
+        q_p = self._planes("q" + ch, (B, N, _D), dev)
+        qs = self._ws.get("qpart" + ch, (B, parts, _D, 2), torch.float32, dev)
+        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 16 | 32, elu_cols=_D, stats=qs, ksum=ksum, zscale_num=M,
+                        tag="q")                                                                                  # ELU1 | COLSUM | ZSCALE
+        cb = self._ws.get("cbias" + ch, (B, 2 * _D), torch.float32, dev)
+        call("op_mlp_center_bias", ptr(xs), parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cb),
+             stream_ptr())
+        hn_p = self._planes("hn" + ch, (B, N, 2 * _D), dev)
+        stats = self._ws.get("tcstats" + ch, (B, parts, 2 * _D, 2), torch.float32, dev)
+        self._linear_tc(x_p, lw["W0a_p"], cb, B, N, A2=q_p, W2=P, Cp=hn_p, flags=128 | 256 | pflag, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
+        W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
+        call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
+             stream_ptr())
+        self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=x, Cp=x_p, flags=2 | 16 | 64, stats=xs, tag="mlp1")        # RESIDUAL | COLSUM | WBATCHED
 
     def _colsum(self, x, B, N, name):
         """Per-frame column sums of a plain fp32 tensor, in the partial layout of OPB_LIN_COLSUM."""
         part = self._ws.get(name, (B, lib.op_linear_tc_stat_parts(N), _D, 2), torch.float32, x.device)
         call("op_colsum_partial", ptr(x), B, N, _D, ptr(part), stream_ptr())
         return part
-
-    def _mlp_tc(self, x, x_p, xs, msg_p, ms, B, N, lw, ch):
-        """MLP([x | message]) with InstanceNorm + ReLU and the residual add (:135-147, :78,83), without a normalisation
-        pass: the mean is analytic (column sums xs / ms of the inputs through W0), layer 0 writes relu(h - mean) as planes,
-        1/std is folded into per-frame layer-1 weights.  x, x_p and the column sums xs of x are updated in place."""
-        dev = x.device
-        parts = lib.op_linear_tc_stat_parts(N)
-        cb = self._ws.get("cbias" + ch, (B, 2 * _D), torch.float32, dev)
-        call("op_mlp_center_bias", ptr(xs), parts, ptr(ms), parts, ptr(lw["W0T"]), B, N, ptr(cb), stream_ptr())
-        hn_p = self._planes("hn" + ch, (B, N, 2 * _D), dev)
-        stats = self._ws.get("tcstats" + ch, (B, parts, 2 * _D, 2), torch.float32, dev)
-        self._linear_tc(x_p, lw["W0_p"], cb, B, N, A2=msg_p, Cp=hn_p, flags=128 | 256, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
-        W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
-        call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
-             stream_ptr())
-        self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=x, Cp=x_p, flags=2 | 16 | 64, stats=xs, tag="mlp1")        # RESIDUAL | COLSUM | WBATCHED
 
     def _gats(self, x3, db, B, N3, L, lw, li):
         hp = self.hparams

@@ -23,18 +23,19 @@ def _unsplit(p):
     return (p[0].double() + p[1].double()) / 64.0
 
 
-def _linear_tc(A1, W, bias, *, A2=None, want_c=True, want_planes=False, flags=0, elu_cols=0, C_init=None, ksum=None, zscale_num=1.0):
+def _linear_tc(A1, W, bias, *, A2=None, W2=None, want_c=True, want_planes=False, flags=0, elu_cols=0, C_init=None, ksum=None, zscale_num=1.0):
     from onepose_b200._lib import call, lib, ptr, stream_ptr
     B, rows, K1 = A1.shape
     Cout = W.shape[-2]
     a1 = _planes(A1); w = _planes(W)
     a2 = _planes(A2) if A2 is not None else None
+    w2 = _planes(W2) if W2 is not None else None
     C = (C_init.clone() if C_init is not None else torch.full((B, rows, Cout), float("nan"), device="cuda")) if want_c else None
     Cp = (torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda"), torch.zeros(B, rows, Cout, dtype=torch.float16, device="cuda")) if want_planes else None
     parts = lib.op_linear_tc_stat_parts(rows)
     stats = torch.full((B, parts, Cout, 2), float("nan"), device="cuda") if flags & (4 | 16 | 256) else None
     call("op_linear_tc", ptr(a1[0]), ptr(a1[1]), K1, ptr(a2[0]) if a2 else None, ptr(a2[1]) if a2 else None,
-         0 if A2 is None else A2.shape[2], ptr(w[0]), ptr(w[1]), ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None,
+         0 if A2 is None else A2.shape[2], ptr(w[0]), ptr(w[1]), ptr(w2[0]) if w2 else None, ptr(w2[1]) if w2 else None, ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None,
          ptr(Cp[1]) if Cp else None, B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr())
     torch.cuda.synchronize()
     return C, Cp, stats
@@ -159,15 +160,16 @@ def test_atb_tc_and_kv_post_vs_float64_linear_attention(shape):
     assert _rel(G, G_ref) < 5e-6
     # post: Ksum partials as OPB_LIN_COLSUM would write them (one part per 32 rows here), KV', P_b
     Wv = (torch.randn(256, 256, generator=g) / 16).cuda(); bv = (torch.randn(256, generator=g) * 0.1).cuda()
-    Wm = (torch.randn(256, 256, generator=g) / 16).cuda()
+    n_out = 256 if M % 2 else 512                                       # merge alone / merge folded into MLP layer 0
+    Wm = (torch.randn(n_out, 256, generator=g) / 16).cuda()
     nparts = (M + 31) // 32
     pad = torch.zeros(B, nparts * 32, 256, device="cuda"); pad[:, :M] = Kp
     ks_part = torch.stack([pad.view(B, nparts, 32, 256).sum(2), torch.zeros(B, nparts, 256, device="cuda")], -1).contiguous()
     ksum = torch.empty(B, 256, device="cuda"); kv = torch.empty(B, 4, 64, 64, device="cuda")
-    Ph = torch.empty(B, 256, 256, dtype=torch.float16, device="cuda"); Pl = torch.empty_like(Ph)
+    Ph = torch.empty(B, n_out, 256, dtype=torch.float16, device="cuda"); Pl = torch.empty_like(Ph)
     WvT = Wv.view(4, 64, 256).transpose(1, 2).contiguous()              # [h, c, q]
-    WmT = Wm.view(256, 4, 64).permute(1, 2, 0).contiguous()             # [h, q, o]
-    call("op_kv_post", ptr(part), nch, ptr(ks_part), nparts, ptr(WvT), ptr(bv), ptr(WmT), B, 1.0 / M, ptr(ksum), ptr(kv), ptr(Ph), ptr(Pl), stream_ptr())
+    WmT = Wm.view(n_out, 4, 64).permute(1, 2, 0).contiguous()           # [h, q, o]
+    call("op_kv_post", ptr(part), nch, ptr(ks_part), nparts, ptr(WvT), ptr(bv), ptr(WmT), n_out, B, 1.0 / M, ptr(ksum), ptr(kv), ptr(Ph), ptr(Pl), stream_ptr())
     torch.cuda.synchronize()
     V = X.double() @ Wv.double().t() + bv.double()
     Kh = Kp.double().view(B, M, 4, 64); Vh = V.view(B, M, 4, 64)
@@ -175,7 +177,7 @@ def test_atb_tc_and_kv_post_vs_float64_linear_attention(shape):
     ks_ref = Kp.double().sum(1)
     assert _rel(ksum, ks_ref) < 2e-6
     assert _rel(kv, KV_ref) < 1e-5
-    P_ref = torch.einsum("bhdq,ohq->bohd", KV_ref, Wm.double().view(256, 4, 64)).reshape(B, 256, 256)
+    P_ref = torch.einsum("bhdq,ohq->bohd", KV_ref, Wm.double().view(n_out, 4, 64)).reshape(B, n_out, 256)
     assert _rel(_unsplit((Ph, Pl)), P_ref) < 1e-5
 
 
@@ -199,32 +201,42 @@ def test_q_projection_with_zscale_and_per_frame_merge_equals_attention_readout()
     assert _rel(msg, ref) < 5e-6
 
 
-@pytest.mark.parametrize("shape", [(2, 333), (1, 2048), (3, 50)])
-def test_mlp_with_analytic_instancenorm_mean(shape):
-    """The MLP of AttentionPropagation (:135-147) + residual (:78) the way the matcher runs it: column sums ->
-    op_mlp_center_bias -> layer 0 with BIASB | CSTATS_RELU -> op_instnorm_finalize_tc -> op_scale_weight_planes ->
-    layer 1 with RESIDUAL | COLSUM | WBATCHED; against InstanceNorm1d + ReLU in float64."""
+@pytest.mark.parametrize("shape", [(2, 333, True), (1, 2048, True), (3, 50, False)])
+def test_mlp_with_folded_merge_and_analytic_instancenorm_mean(shape):
+    """merge (:119) + MLP (:135-147) + residual (:78) the way the matcher runs them: column sums -> op_mlp_center_bias ->
+    layer 0 = W0a x + P'_b Q'' with BIASB | CSTATS_RELU (P'_b = W0b P_b per frame) -> op_instnorm_scale_weight_planes ->
+    layer 1 with RESIDUAL | COLSUM | WBATCHED; against merge + Conv1d + InstanceNorm1d + ReLU + Conv1d in float64."""
     from onepose_b200._lib import call, lib, ptr, stream_ptr
-    B, N = shape
+    B, N, batched = shape
     g = torch.Generator().manual_seed(31 + N)
     x = (torch.randn(B, N, 256, generator=g) * 0.3 + torch.randn(B, 1, 256, generator=g) * 0.2).cuda()
-    msg = (torch.randn(B, N, 256, generator=g) * 0.5 + torch.randn(B, 1, 256, generator=g)).cuda()
+    q = (torch.rand(B, N, 256, generator=g) * 2).cuda()                     # Q'' > 0
+    Pb = (torch.randn(B if batched else 1, 256, 256, generator=g) / 16).cuda(); bm = torch.randn(256, generator=g).cuda()
     W0 = (torch.randn(512, 512, generator=g) / 512 ** 0.5).cuda(); b0 = torch.randn(512, generator=g).cuda()
     W1 = (torch.randn(256, 512, generator=g) / 512 ** 0.5).cuda(); b1 = (torch.randn(256, generator=g) * 0.1).cuda()
+    W0a = W0[:, :256].contiguous()
+    Pp = (W0[:, 256:].double() @ Pb.double()).float().contiguous()           # P'_b [B or 1, 512, 256]
     parts = lib.op_linear_tc_stat_parts(N)
-    xs = torch.full((B, parts, 256, 2), float("nan"), device="cuda"); ms = torch.full_like(xs, float("nan"))
+    xs = torch.full((B, parts, 256, 2), float("nan"), device="cuda"); qs = torch.full_like(xs, float("nan"))
     call("op_colsum_partial", ptr(x), B, N, 256, ptr(xs), stream_ptr())
-    call("op_colsum_partial", ptr(msg), B, N, 256, ptr(ms), stream_ptr())
+    call("op_colsum_partial", ptr(q), B, N, 256, ptr(qs), stream_ptr())
     np.testing.assert_allclose(xs[..., 0].double().sum(1).cpu().numpy(), x.double().sum(1).cpu().numpy(), rtol=1e-5, atol=1e-4)
-    W0T = W0.t().contiguous()
+    W0aT = W0a.t().contiguous()
+    pp = _planes(Pp)
     cb = torch.empty(B, 512, device="cuda")
-    call("op_mlp_center_bias", ptr(xs), parts, ptr(ms), parts, ptr(W0T), B, N, ptr(cb), stream_ptr())
-    mean_in = torch.cat([x, msg], 2).double().mean(1)
-    np.testing.assert_allclose(cb.double().cpu().numpy(), -(mean_in @ W0.double().t()).cpu().numpy(), rtol=1e-5, atol=1e-5)
-    # layer 0: centred pre-activation, statistics of it, ReLU, planes out
-    _, hn, st = _linear_tc(x, W0, cb, A2=msg, want_c=False, want_planes=True, flags=128 | 256)
-    h = torch.cat([x, msg], 2).double() @ W0.double().t() + b0.double()
-    d = h - h.mean(1, keepdim=True)                       # b0 cancels in InstanceNorm: the kernel never adds it
+    call("op_mlp_center_bias", ptr(xs), parts, ptr(qs), parts, ptr(W0aT), ptr(pp[0]), ptr(pp[1]), int(batched), B, N, ptr(cb), stream_ptr())
+    msg = q.double() @ Pb.double().transpose(1, 2) + bm.double()             # the reference's merged message
+    h = torch.cat([x.double(), msg], 2) @ W0.double().t() + b0.double()
+    mean_lin = x.double().mean(1) @ W0a.double().t() + torch.einsum("bcj,bj->bc", Pp.double().expand(B, 512, 256), q.double().mean(1))
+    np.testing.assert_allclose(cb.double().cpu().numpy(), -mean_lin.cpu().numpy(), rtol=1e-5, atol=1e-5)
+    # layer 0: centred pre-activation (bm and b0 cancel in InstanceNorm: the kernel never adds them), statistics, ReLU, planes out
+    a1, a2, w, w2 = _planes(x), _planes(q), _planes(W0a), pp
+    hn = (torch.empty(B, N, 512, dtype=torch.float16, device="cuda"), torch.empty(B, N, 512, dtype=torch.float16, device="cuda"))
+    st = torch.full((B, parts, 512, 2), float("nan"), device="cuda")
+    call("op_linear_tc", ptr(a1[0]), ptr(a1[1]), 256, ptr(a2[0]), ptr(a2[1]), 256, ptr(w[0]), ptr(w[1]), ptr(w2[0]), ptr(w2[1]), ptr(cb), None,
+         ptr(hn[0]), ptr(hn[1]), B, N, 512, 128 | 256 | (512 if batched else 0), 0, ptr(st), None, 1.0, stream_ptr())
+    torch.cuda.synchronize()
+    d = h - h.mean(1, keepdim=True)
     assert ((_unsplit(hn) - d.clamp_min(0)).abs().max() / d.abs().max()).item() < 5e-6
     np.testing.assert_allclose(st[..., 1].double().sum(1).cpu().numpy(), (d * d).sum(1).cpu().numpy(), rtol=2e-5)
     assert float(st[..., 0].double().sum(1).abs().max()) < 1e-3 * N ** 0.5 + 1e-2      # residual mean is rounding noise
@@ -241,10 +253,26 @@ def test_mlp_with_analytic_instancenorm_mean(shape):
     assert _rel(_unsplit((W2h, W2l)), _unsplit((W1h, W1l))) < 1e-6
     # layer 1 through the raw entry point (per-frame weight planes are already split)
     xo = x.clone(); xo_p = (torch.empty(B, N, 256, dtype=torch.float16, device="cuda"), torch.empty(B, N, 256, dtype=torch.float16, device="cuda"))
-    call("op_linear_tc", ptr(hn[0]), ptr(hn[1]), 512, None, None, 0, ptr(W1h), ptr(W1l), ptr(b1), ptr(xo), ptr(xo_p[0]), ptr(xo_p[1]),
+    call("op_linear_tc", ptr(hn[0]), ptr(hn[1]), 512, None, None, 0, ptr(W2h), ptr(W2l), None, None, ptr(b1), ptr(xo), ptr(xo_p[0]), ptr(xo_p[1]),
          B, N, 256, 2 | 16 | 64, 0, ptr(xs), None, 1.0, stream_ptr())
     torch.cuda.synchronize()
     ref = x.double() + torch.relu(d * rstd_ref[:, None, :]) @ W1.double().t() + b1.double()
     assert _rel(xo, ref) < 1e-5
     assert _rel(_unsplit(xo_p), ref) < 1e-5
     np.testing.assert_allclose(xs[..., 0].double().sum(1).cpu().numpy(), ref.sum(1).cpu().numpy(), rtol=1e-4, atol=1e-3)
+
+
+def test_linear_tc_second_weight_equals_concatenated_weight():
+    """A1 . W^T + A2 . W2^T (own tensor map for the A2 part) against the single [W | W2] matrix, bit for bit."""
+    B, N = 2, 200
+    g = torch.Generator().manual_seed(77)
+    A1 = (torch.randn(B, N, 256, generator=g) * 0.3).cuda(); A2 = (torch.randn(B, N, 256, generator=g) * 0.3).cuda()
+    W = (torch.randn(512, 256, generator=g) / 16).cuda(); W2 = (torch.randn(512, 256, generator=g) / 16).cuda()
+    bias = torch.randn(512, generator=g).cuda()
+    C1, _, _ = _linear_tc(A1, W, bias, A2=A2, W2=W2)
+    C2, _, _ = _linear_tc(A1, torch.cat([W, W2], 1).contiguous(), bias, A2=A2)
+    assert torch.equal(C1, C2)
+    W2b = torch.stack([W2, -W2]).contiguous()
+    C3, _, _ = _linear_tc(A1, W, bias, A2=A2, W2=W2b, flags=512)
+    ref = A1.double() @ W.double().t() + torch.einsum("bnk,bok->bno", A2.double(), W2b.double()) + bias.double()
+    assert _rel(C3, ref) < 5e-6
