@@ -181,10 +181,28 @@ def run_ours(args):
         pred, conf = model(resident)
         return pred
 
-    def step_e2e():
-        data = dict(db_dev, query_intrinsic=K_dev)
-        for k, v in q_pin.items():
-            data[k] = v.to(dev, non_blocking=True)
+    # End to end: every step uploads its 64 query frames from pinned host memory and reads its results back.  The upload of
+    # step i+1 is issued on a copy stream while step i computes (a double-buffered input pipeline, what a frame loader
+    # does); the first upload of a timed region is not hidden, every upload is inside the region.
+    copy_stream = torch.cuda.Stream(device=dev)
+    pending = []
+
+    def upload():
+        with torch.cuda.stream(copy_stream):
+            up = {k: v.to(dev, non_blocking=True) for k, v in q_pin.items()}
+            pending.append((up, copy_stream.record_event()))
+
+    def step_e2e(prefetch_next=True):
+        if not pending:
+            upload()
+        up, ready = pending.pop(0)
+        main = torch.cuda.current_stream(dev)
+        main.wait_event(ready)
+        for v in up.values():
+            v.record_stream(main)
+        if prefetch_next:
+            upload()
+        data = dict(db_dev, query_intrinsic=K_dev, **up)
         pred, conf = model(data)
         out_pin["pose"].copy_(pred["pose"], non_blocking=True)
         out_pin["n_inliers"].copy_(pred["n_inliers"], non_blocking=True)
@@ -229,8 +247,14 @@ def run_ours(args):
     summary = timeline.summary()
     launches = timeline.launches // args.steps
     for _ in range(2):
-        step_e2e()
-    ms_e2e, pred_e = timed(step_e2e, args.steps)
+        step_e2e(prefetch_next=False)
+    e2e_calls = [0]
+
+    def e2e_step_counted():                     # exactly K uploads inside the timed region: the last step prefetches nothing
+        e2e_calls[0] += 1
+        return step_e2e(prefetch_next=e2e_calls[0] < args.steps)
+
+    ms_e2e, pred_e = timed(e2e_step_counted, args.steps)
 
     total_frames = FRAMES * args.steps * world
     value = total_frames / (ms / 1e3)
@@ -275,7 +299,8 @@ def run_ours(args):
                        "l2": "working set per step (~6 GB of activations + 4 GiB conf) exceeds the 126 MB L2; no flush needed",
                        "db_resident": True, "parallelism": f"dp{world} (objects sharded, no collective)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                    "ms_per_step": ms_e2e / args.steps},
+                    "ms_per_step": ms_e2e / args.steps,
+                    "h2d": "pinned host -> device on a copy stream, step i+1 uploaded while step i computes (all K uploads in the timed region)"},
             "gpu_launches": launches * args.steps, "gpu_launches_per_step": launches,
             "kernel_timing": {"how": "CUDA events around every launch in a second pass of the same steps with the two matcher "
                                      "streams serialised on one CUDA stream", "ms_per_step": ms_serial / args.steps},

@@ -146,8 +146,8 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
           const float *__restrict__ WvT /* [4][256 c][64 q] = Wv[h*64+q][c] */, const float *__restrict__ bv,
           const float *__restrict__ WmT /* [4][64 q][n_out o] = Wm[o][h*64+q] */, int n_out, float inv_m, float *__restrict__ ksum /* [B][256] */,
           float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
-    __shared__ float G[kPostD][256];
-    __shared__ float KV[kPostD][65];
+    __shared__ __align__(16) float G[kPostD][256];
+    __shared__ __align__(16) float KV[kPostD][68];
     __shared__ float Ks[kPostD];
     __shared__ double Kslice[16][kPostD];
     const int h = blockIdx.x, dg = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
@@ -180,15 +180,18 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
         ksum[(long long)b * 256 + ch0 + tid] = (float)s;
     }
     __syncthreads();
-    {   // KV[d][q]: thread = (q, group of 4 d)
+    {   // KV[d][q]: thread = (q, group of 4 d); G rows are read four channels at a time (broadcast LDS.128)
         const int q = tid & 63, d0 = (tid >> 6) * 4;
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
         const float *w = WvT + (long long)h * 256 * 64 + q;          // coalesced over q
-#pragma unroll 8
-        for (int c = 0; c < 256; ++c) {
-            const float wc = __ldg(w + c * 64);
+#pragma unroll 4
+        for (int c = 0; c < 256; c += 4) {
+            const float w0 = __ldg(w + c * 64), w1 = __ldg(w + (c + 1) * 64), w2 = __ldg(w + (c + 2) * 64), w3 = __ldg(w + (c + 3) * 64);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) acc[i] = fmaf(G[d0 + i][c], wc, acc[i]);
+            for (int i = 0; i < 4; ++i) {
+                const float4 g4 = *reinterpret_cast<const float4 *>(&G[d0 + i][c]);
+                acc[i] = fmaf(g4.x, w0, acc[i]); acc[i] = fmaf(g4.y, w1, acc[i]); acc[i] = fmaf(g4.z, w2, acc[i]); acc[i] = fmaf(g4.w, w3, acc[i]);
+            }
         }
         const float bq = bv[h * 64 + q];
 #pragma unroll
@@ -208,7 +211,11 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
         for (int d = 0; d < kPostD; d += 2) {
             float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-            for (int q = 0; q < 64; ++q) { a0 = fmaf(KV[d][q], wm[q], a0); a1 = fmaf(KV[d + 1][q], wm[q], a1); }
+            for (int q = 0; q < 64; q += 4) {
+                const float4 k0 = *reinterpret_cast<const float4 *>(&KV[d][q]), k1 = *reinterpret_cast<const float4 *>(&KV[d + 1][q]);
+                a0 = fmaf(k0.x, wm[q], a0); a0 = fmaf(k0.y, wm[q + 1], a0); a0 = fmaf(k0.z, wm[q + 2], a0); a0 = fmaf(k0.w, wm[q + 3], a0);
+                a1 = fmaf(k1.x, wm[q], a1); a1 = fmaf(k1.y, wm[q + 1], a1); a1 = fmaf(k1.z, wm[q + 2], a1); a1 = fmaf(k1.w, wm[q + 3], a1);
+            }
             __half h0, l0, h1, l1;
             tc::split_f16(a0 * 64.f, h0, l0); tc::split_f16(a1 * 64.f, h1, l1);
             hh[d / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
