@@ -287,9 +287,12 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     const int K = W2h ? K1 : K1 + K2;                 // columns of W
     CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl;
     int rc;
+    // CTA pairs (cta_group::2) by default; OPB_LINEAR_CG=1 selects the one-CTA-per-tile form of the same kernel (A/B runs)
+    static const int cg = [] { const char *e = getenv("OPB_LINEAR_CG"); return (e && e[0] == '1') ? 1 : 2; }();
+    const int wbox = lintc::BN / cg;                  // rows of a W block one CTA loads
     if ((rc = make_tmap_f16_3d(&ta1h, A1h, B, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, B, rows_per_batch, K1, lintc::BM)) ||
-        (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, lintc::BN)) ||
-        (rc = make_tmap_f16_3d(&twl, Wl, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, lintc::BN)))
+        (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)) ||
+        (rc = make_tmap_f16_3d(&twl, Wl, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)))
         return rc;
     if (K2) {
         if ((rc = make_tmap_f16_3d(&ta2h, A2h, B, rows_per_batch, K2, lintc::BM)) || (rc = make_tmap_f16_3d(&ta2l, A2l, B, rows_per_batch, K2, lintc::BM)))
@@ -299,7 +302,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     }
     if (W2h) {
         const int wb = (flags & OPB_LIN_W2BATCHED) ? B : 1;
-        if ((rc = make_tmap_f16_3d(&tw2h, W2h, wb, Cout, K2, lintc::BN)) || (rc = make_tmap_f16_3d(&tw2l, W2l, wb, Cout, K2, lintc::BN))) return rc;
+        if ((rc = make_tmap_f16_3d(&tw2h, W2h, wb, Cout, K2, wbox)) || (rc = make_tmap_f16_3d(&tw2l, W2l, wb, Cout, K2, wbox))) return rc;
     } else {
         tw2h = twh; tw2l = twl;
     }
@@ -311,19 +314,33 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     lintc::Params p{};
     p.B = B; p.rows = rows_per_batch; p.Cout = Cout; p.K1 = K1; p.K2 = K2; p.flags = flags; p.elu_cols = elu_cols;
     p.row_tiles = ceil_div(rows_per_batch, lintc::BM); p.col_tiles = Cout / lintc::BN;
-    const long long total = (long long)B * p.row_tiles * p.col_tiles;
+    p.row_groups = ceil_div(p.row_tiles, cg);
+    const long long total = (long long)B * p.row_groups * p.col_tiles;
     OPB_CHECK_ARG(total < (1ll << 31), "op_linear_tc: too many tiles");
     p.total_tiles = (int)total;
     p.bias = bias; p.C = C; p.Ch = (__half *)Ch; p.Cl = (__half *)Cl; p.stats = (float2 *)stats_partial;
     p.ksum = ksum; p.zscale_num = zscale_num; p.w_batched = (flags & OPB_LIN_WBATCHED) ? 1 : 0;
     p.w2 = W2h ? ((flags & OPB_LIN_W2BATCHED) ? 2 : 1) : 0;
+    static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
+    p.dbg = dbg;
     static bool configured = false;
     if (!configured) {
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::SMEM_BYTES));
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::Cfg<1>::SMEM_BYTES));
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::Cfg<2>::SMEM_BYTES));
         configured = true;
     }
-    const int grid = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
-    lintc::k_linear_tc<<<grid, lintc::THREADS, lintc::SMEM_BYTES, (cudaStream_t)stream>>>(ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p);
+    const int groups = sm_count() / cg;                                   // persistent CTAs (or CTA pairs), one per SM
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    cfg.gridDim = dim3((unsigned)((p.total_tiles < groups ? p.total_tiles : groups) * cg));
+    cfg.blockDim = dim3(lintc::THREADS);
+    cfg.dynamicSmemBytes = cg == 2 ? lintc::Cfg<2>::SMEM_BYTES : lintc::Cfg<1>::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cg; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lintc::k_linear_tc<2>, ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p));
+    else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lintc::k_linear_tc<1>, ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p));
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

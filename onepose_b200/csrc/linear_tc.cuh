@@ -18,22 +18,34 @@
 namespace opb {
 namespace lintc {
 
-constexpr int BM = 128, BN = 256, BK = 64, STAGES = 2;
+constexpr int BM = 128, BN = 256, BK = 64;
 constexpr int A_PLANE = BM * BK * 2;                  // 16384
-constexpr int W_PLANE = BN * BK * 2;                  // 32768
-constexpr int HALF_BYTES = A_PLANE + W_PLANE;         // one precision half of a stage (49152)
-constexpr int STAGE_BYTES = 2 * HALF_BYTES;           // 98304
 constexpr int BIAS_FLOATS = 512;
 constexpr int EPI_WARPS = 8, THREADS = (EPI_WARPS + 2) * 32;
 constexpr int STG_BUF = 32 * 64;                      // TMA-store staging buffer: 32 rows x 64 bytes (16 fp32 or 32 fp16 columns)
 constexpr int STG_BYTES = EPI_WARPS * 2 * STG_BUF;    // two per epilogue warp = 32768
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STG_BYTES + BIAS_FLOATS * 4 + 256;   // 231680 of 232448; base must be 1024-aligned
+constexpr int MAX_STAGES = 3;
+// CG = 1: one CTA per 128 x 256 tile, the whole 256-row W block per stage (96 KB, two stages).
+// CG = 2: a CTA pair (cta_group::2, two SMs of a TPC) per 256 x 256 tile: each CTA stages its own 128 rows of A and HALF of the W
+//         block (64 KB per stage, three stages) -- a third less L2 -> SM traffic per flop, which is what bounds the CG = 1 form
+//         (96 KB per 1536 MMA cycles = 62 B/clk/SM against the ~42 B/clk/SM the L2 delivers chip-wide).
+template <int CG>
+struct Cfg {
+    static constexpr int STAGES = CG == 2 ? 3 : 2;
+    static constexpr int W_ROWS = BN / CG;                       // rows of the W block held by one CTA
+    static constexpr int W_PLANE = W_ROWS * BK * 2;              // 32768 / 16384
+    static constexpr int HALF_BYTES = A_PLANE + W_PLANE;         // one precision half of a stage
+    static constexpr int STAGE_BYTES = 2 * HALF_BYTES;           // 98304 / 65536
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STG_BYTES + BIAS_FLOATS * 4 + 256;   // 231680 of 232448; base must be 1024-aligned
+};
 constexpr float kScale = 64.f;                        // activations and weights are stored as 64*x
 constexpr float kInvScale2 = 1.f / (kScale * kScale);
 
 struct Params {
     int B, rows, Cout, K1, K2, flags, elu_cols;
-    int row_tiles, col_tiles, total_tiles;
+    int row_tiles, col_tiles, total_tiles;   // total_tiles counts (frame, group of CG row tiles, column tile)
+    int row_groups;                          // ceil(row_tiles / CG)
+    int dbg;                                 // experiment switches (env OPB_LIN_DBG): 1 = no output stores, 2 = no residual read, 4 = no MMAs
     const float *bias;
     float *C;                      // fp32 [B, rows, Cout] or null
     __half *Ch, *Cl;               // planes [B, rows, Cout] (x64) or null
@@ -46,7 +58,7 @@ struct Params {
 };
 
 struct Barriers {
-    uint64_t full_hi[STAGES], full_lo[STAGES], empty[STAGES], acc_full[2], acc_empty[2];
+    uint64_t full_hi[MAX_STAGES], full_lo[MAX_STAGES], empty[MAX_STAGES], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
 
@@ -81,6 +93,7 @@ __device__ __forceinline__ void split_planes32(const float *vs, uint32_t *h, uin
     }
 }
 
+template <int CG>
 __global__ void __launch_bounds__(THREADS, 1)
 k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ CUtensorMap tm_a1l,
             const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
@@ -90,8 +103,11 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             const Params p) {
     // SWIZZLE_128B operands need a 1024-byte aligned base: the dynamic shared window of a kernel without static shared memory
     // starts at offset 0; checked below (every byte of the 227 KB is in use, there is no slack to re-align).
+    constexpr int STAGES = Cfg<CG>::STAGES, W_PLANE = Cfg<CG>::W_PLANE, HALF_BYTES = Cfg<CG>::HALF_BYTES, STAGE_BYTES = Cfg<CG>::STAGE_BYTES;
     extern __shared__ __align__(1024) uint8_t smem[];
     if (tc::smem_u32(smem) & 1023u) __trap();
+    const uint32_t rank = CG == 2 ? tc::cluster_ctarank() : 0;            // 0 = leader of the pair: arms the barriers, issues the MMAs
+    const int first_tile = blockIdx.x / CG, tile_step = gridDim.x / CG;
     uint8_t *s_stg = smem + STAGES * STAGE_BYTES;
     float *s_bias = reinterpret_cast<float *>(smem + STAGES * STAGE_BYTES + STG_BYTES);
     Barriers *bar = reinterpret_cast<Barriers *>(smem + STAGES * STAGE_BYTES + STG_BYTES + BIAS_FLOATS * 4);
@@ -101,11 +117,11 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; ++i) { tc::mbar_init(&bar->full_hi[i], 1); tc::mbar_init(&bar->full_lo[i], 1); tc::mbar_init(&bar->empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], EPI_WARPS); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], EPI_WARPS * CG); }
         tc::fence_barrier_init();
     }
     for (int i = threadIdx.x; i < BIAS_FLOATS; i += THREADS) s_bias[i] = (p.bias && i < p.Cout && !(p.flags & OPB_LIN_BIASB)) ? kScale * p.bias[i] : 0.f;     // bias in the x64 domain of the planes
-    if (warp == 9) tc::tmem_alloc<512>(&bar->tmem_base);
+    if (warp == 9) { if (CG == 2) tc::tmem_alloc_cg2<512>(&bar->tmem_base); else tc::tmem_alloc<512>(&bar->tmem_base); }
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_a1h); tc::tma_prefetch_desc(&tm_a1l); tc::tma_prefetch_desc(&tm_wh); tc::tma_prefetch_desc(&tm_wl);
         if (p.K2) { tc::tma_prefetch_desc(&tm_a2h); tc::tma_prefetch_desc(&tm_a2l); }
@@ -114,19 +130,24 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         if (p.Ch) { tc::tma_prefetch_desc(&tm_ch); tc::tma_prefetch_desc(&tm_cl); }
     }
     tc::tcgen05_fence_before();
-    __syncthreads();
+    if (CG == 2) tc::cluster_sync(); else __syncthreads();                // the peer's barriers exist before anything is sent to them
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = bar->tmem_base;
 
-    // tile t -> (frame b, row tile, column tile); the column tile is the fastest index so neighbouring CTAs share A rows
-    auto decode = [&](int t, int &b, int &rt, int &ct) { ct = t % p.col_tiles; const int r = t / p.col_tiles; rt = r % p.row_tiles; b = r / p.row_tiles; };
+    // tile t -> (frame b, row tile, column tile); the column tile is the fastest index so neighbouring CTAs share A rows.
+    // In a pair the two CTAs take row tiles 2g and 2g+1 of group g; a row tile past the end is a ghost (zero-filled loads,
+    // clipped stores, no statistics).
+    auto decode = [&](int t, int &b, int &rt, int &ct) {
+        ct = t % p.col_tiles; const int r = t / p.col_tiles; rt = (r % p.row_groups) * CG + (int)rank; b = r / p.row_groups;
+    };
 
     if (warp == 8) {
         // ================= TMA producer =================
         if (lane == 0) {
             uint32_t it = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+            for (int t = first_tile; t < p.total_tiles; t += tile_step) {
                 int b, rt, ct; decode(t, b, rt, ct);
+                const int wrow = ct * BN + (int)rank * Cfg<CG>::W_ROWS;       // this CTA's rows of the W block
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
                     uint8_t *st = smem + stage * STAGE_BYTES;
@@ -136,24 +157,37 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     const int kw = own_w2 ? ka : kb * BK;
                     const int wb = own_w2 ? (p.w2 == 2 ? b : 0) : (p.w_batched ? b : 0);
                     tc::mbar_wait(&bar->empty[stage], ph ^ 1);
-                    tc::mbar_arrive_expect_tx(&bar->full_hi[stage], HALF_BYTES);
-                    tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, b);
-                    tc::tma_load_3d(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, &bar->full_hi[stage], kw, ct * BN, wb);
-                    tc::mbar_arrive_expect_tx(&bar->full_lo[stage], HALF_BYTES);
-                    tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, b);
-                    tc::tma_load_3d(st + HALF_BYTES + A_PLANE, own_w2 ? &tm_w2l : &tm_wl, &bar->full_lo[stage], kw, ct * BN, wb);
+                    if (CG == 2) {
+                        // both CTAs load into their own shared memory; the bytes of both are credited to the leader's barriers
+                        const uint32_t fh = tc::mapa(tc::smem_u32(&bar->full_hi[stage]), 0), fl = tc::mapa(tc::smem_u32(&bar->full_lo[stage]), 0);
+                        if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_hi[stage], 2 * HALF_BYTES);
+                        tc::tma_load_3d_cg2(st, second ? &tm_a2h : &tm_a1h, fh, ka, rt * BM, b);
+                        tc::tma_load_3d_cg2(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, fh, kw, wrow, wb);
+                        if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_lo[stage], 2 * HALF_BYTES);
+                        tc::tma_load_3d_cg2(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, fl, ka, rt * BM, b);
+                        tc::tma_load_3d_cg2(st + HALF_BYTES + A_PLANE, own_w2 ? &tm_w2l : &tm_wl, fl, kw, wrow, wb);
+                    } else {
+                        tc::mbar_arrive_expect_tx(&bar->full_hi[stage], HALF_BYTES);
+                        tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, b);
+                        tc::tma_load_3d(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, &bar->full_hi[stage], kw, wrow, wb);
+                        tc::mbar_arrive_expect_tx(&bar->full_lo[stage], HALF_BYTES);
+                        tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, b);
+                        tc::tma_load_3d(st + HALF_BYTES + A_PLANE, own_w2 ? &tm_w2l : &tm_wl, &bar->full_lo[stage], kw, wrow, wb);
+                    }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 9) {
         // ================= MMA issuer =================
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN);
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = tc::umma_idesc_f16(BM * CG, BN);
+            auto mma = [](uint32_t d, uint64_t a, uint64_t b, uint32_t acc) { if (CG == 2) tc::umma_f16_cg2(d, a, b, idesc, acc); else tc::umma_f16(d, a, b, idesc, acc); };
+            auto commit = [](uint64_t *barrier) { if (CG == 2) tc::umma_commit_cg2(barrier); else tc::umma_commit(barrier); };
             const uint32_t base = tc::smem_u32(smem);
             uint32_t it = 0;
             int j = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
+            for (int t = first_tile; t < p.total_tiles; t += tile_step, ++j) {
                 const uint32_t as = j & 1, aph = (j >> 1) & 1;
                 tc::mbar_wait(&bar->acc_empty[as], aph ^ 1);
                 tc::tcgen05_fence_after();
@@ -165,18 +199,19 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     const uint64_t al = tc::umma_desc_k128(sb + HALF_BYTES), wl = tc::umma_desc_k128(sb + HALF_BYTES + A_PLANE);
                     tc::mbar_wait(&bar->full_hi[stage], ph);
                     tc::tcgen05_fence_after();
+                    if (p.dbg & 4) { tc::mbar_wait(&bar->full_lo[stage], ph); commit(&bar->empty[stage]); continue; }
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) tc::umma_f16(d, ah + 2 * k, wh + 2 * k, idesc, (kb | k) != 0);   // UMMA_K = 16 fp16 = 32 B
+                    for (int k = 0; k < 4; ++k) mma(d, ah + 2 * k, wh + 2 * k, (kb | k) != 0);   // UMMA_K = 16 fp16 = 32 B
                     tc::mbar_wait(&bar->full_lo[stage], ph);
                     tc::tcgen05_fence_after();
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        tc::umma_f16(d, al + 2 * k, wh + 2 * k, idesc, 1);
-                        tc::umma_f16(d, ah + 2 * k, wl + 2 * k, idesc, 1);
+                        mma(d, al + 2 * k, wh + 2 * k, 1);
+                        mma(d, ah + 2 * k, wl + 2 * k, 1);
                     }
-                    tc::umma_commit(&bar->empty[stage]);          // frees the stage when these MMAs retire
+                    commit(&bar->empty[stage]);                   // frees the stage (in both CTAs of a pair) when these MMAs retire
                 }
-                tc::umma_commit(&bar->acc_full[as]);
+                commit(&bar->acc_full[as]);
             }
         }
         __syncwarp();
@@ -188,6 +223,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         // rows past the end are clipped by the TMA unit.  Two staging buffers per warp, at most one store still reading.
         uint32_t nst = 0;
         auto stage_store = [&](const CUtensorMap *tm, int col, const uint4 *data, int bb, int r0) {
+            if (p.dbg & 1) return;
             uint8_t *buf = s_stg + (warp * 2 + (nst & 1)) * STG_BUF;
             if (lane == 0) tc::tma_store_wait_read1();
             __syncwarp();
@@ -199,8 +235,9 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             ++nst;
         };
         int j = 0;
-        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
+        for (int t = first_tile; t < p.total_tiles; t += tile_step, ++j) {
             int b, rt, ct; decode(t, b, rt, ct);
+            const bool tile_ok = rt < p.row_tiles;                // false: ghost row tile of an odd pair
             const uint32_t as = j & 1, aph = (j >> 1) & 1;
             const int row = rt * BM + quad * 32 + lane;
             const bool row_ok = row < p.rows;
@@ -219,7 +256,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 if (hh == 1) {                                    // this warp has drained its part of the accumulator
                     tc::tcgen05_fence_before();
                     __syncwarp();
-                    if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
+                    if (lane == 0) { if (CG == 2) tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&bar->acc_empty[as]), 0)); else tc::mbar_arrive(&bar->acc_empty[as]); }
                 }
                 // The epilogue math runs on vs = 64 * value (the scale of the output planes): acc holds 4096 * value.
                 float den = 0.f;
@@ -227,7 +264,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 for (int cc = 0; cc < 2; ++cc) {
                     float *vv = v[cc];
                     const int c0 = col0 + cc * 32;
-                    if (p.flags & OPB_LIN_STATS) {
+                    if ((p.flags & OPB_LIN_STATS) && tile_ok) {
                         float s[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = vv[i] * kInvScale2;     // rows past the end are exact zeros (TMA zero fill, no bias yet)
@@ -268,7 +305,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
 #pragma unroll
                         for (int i = 0; i < 32; ++i) { const float t = row_ok ? vv[i] : 0.f; s[i] = t * t; }
                         const float cq = transpose_reduce_sum(s, lane) * kInvScale2;
-                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, cq);
+                        if (tile_ok) p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, cq);
 #pragma unroll
                         for (int i = 0; i < 32; ++i) vv[i] = fmaxf(vv[i], 0.f);
                     }
@@ -293,7 +330,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     const int c0 = col0 + cc * 32;
                     if (p.C) {
                         if (p.flags & OPB_LIN_RESIDUAL) {            // x64 domain: vs += 64 * old
-                            if (row_ok) {
+                            if (row_ok && !(p.dbg & 2)) {
                                 const float4 *src = reinterpret_cast<const float4 *>(p.C + grow * p.Cout + c0);
 #pragma unroll
                                 for (int q = 0; q < 8; ++q) {
@@ -309,7 +346,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
                         const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
-                        p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
+                        if (tile_ok) p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
                     }
                     if (p.Ch) {
                         uint32_t h[16], l[16];
@@ -329,8 +366,8 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         if (lane == 0) tc::tma_store_wait_all();
     }
     tc::tcgen05_fence_before();
-    __syncthreads();
-    if (warp == 9) tc::tmem_dealloc<512>(tmem_base);
+    if (CG == 2) tc::cluster_sync(); else __syncthreads();                // nothing is in flight to or from the peer any more
+    if (warp == 9) { if (CG == 2) tc::tmem_dealloc_cg2<512>(tmem_base); else tc::tmem_dealloc<512>(tmem_base); }
 }
 
 }  // namespace lintc
