@@ -54,6 +54,15 @@ int op_gats_leaf_aggregate(const float *leaf, long long leaf_bstride, const floa
                            const float *v1, const float *v2, float *out, int B, int N3, int L,
                            float alpha, int include_self, int apply_elu, void *stream);
 
+/* The same layer in place on the split-precision planes (xh, xl: [B, N3, 256] fp16, section 2b) of the 3D stream, for
+ * h3L == the stream itself (with_linear_transform = False); add_self = (additional && include_self); ELU always applied.
+ * Also writes the per-frame column sums of the output as partials colsum_partial[B][op_gats_planes_parts(N3)][256][2]
+ * ((sum, 0), the layout op_mlp_center_bias folds). */
+int op_gats_planes_parts(int N3);
+int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_bstride, void *xh, void *xl, const float *v1, const float *v2,
+                                  float *colsum_partial, int B, int N3, int L, float alpha, int include_self, int add_self,
+                                  void *stream);
+
 /* ---- (2) self/cross AttentionPropagation building blocks: GATs_SuperGlue.py:88-147 -----------
  * Generic fused linear: C[b,n,:] = epi( [A1[b,n,:K1] | A2[b,n,:K2]] . W^T + bias ), W is [Cout, K1+K2]
  * row-major.  Rows are addressed as b*rows_per_batch + n.  Flags select the fusions:
@@ -100,7 +109,7 @@ int op_attn_apply(const float *Qp, const float *KV, const float *Ksum, float *ou
  * (fp16 storage), 16-byte aligned; K1, K2 multiples of 64; Cout 256 or 512.
  * op_linear_tc: C = epi([A1|A2] . W^T), or with W2 planes given C = epi(A1 . W^T + A2 . W2^T) (W [Cout,K1], W2 [Cout,K2] or
  * [B,Cout,K2] with OPB_LIN_W2BATCHED); outputs fp32 C and/or planes (Ch, Cl) for the next GEMM.
- * flags: OPB_LIN_ELU1, OPB_LIN_RESIDUAL (C += result, needs C), OPB_LIN_STATS (stats_partial
+ * flags: OPB_LIN_ELU1, OPB_LIN_RESIDUAL (C += result; without C the old value is read from the output planes, in place), OPB_LIN_STATS (stats_partial
  * [B][op_linear_tc_stat_parts(rows)][Cout][2] fp32 partial sum / sum of squares of the result
  * WITHOUT the bias; op_instnorm_finalize_tc folds them in float64 and adds the bias to the mean). */
 int op_split_planes(const float *x, void *hi, void *lo, long long n, void *stream);

@@ -272,7 +272,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(Cout > 0 && Cout % lintc::BN == 0 && Cout <= lintc::BIAS_FLOATS, "op_linear_tc: Cout=%d must be 256 or 512", Cout);
     OPB_CHECK_ARG(C || Ch, "op_linear_tc: no output requested");
     OPB_CHECK_ARG((Ch == nullptr) == (Cl == nullptr), "op_linear_tc: Ch/Cl must come together");
-    OPB_CHECK_ARG(!(flags & OPB_LIN_RESIDUAL) || C, "op_linear_tc: RESIDUAL needs the fp32 output");
+    OPB_CHECK_ARG(!(flags & OPB_LIN_RESIDUAL) || C || Ch, "op_linear_tc: RESIDUAL needs an output to add to");
     {
         const int nst = ((flags & OPB_LIN_STATS) != 0) + ((flags & OPB_LIN_COLSUM) != 0) + ((flags & OPB_LIN_CSTATS_RELU) != 0);
         OPB_CHECK_ARG(nst == 0 || stats_partial, "op_linear_tc: STATS / COLSUM / CSTATS_RELU need stats_partial");

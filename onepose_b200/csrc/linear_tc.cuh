@@ -328,15 +328,26 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 for (int cc = 0; cc < 2; ++cc) {
                     float *vv = v[cc];
                     const int c0 = col0 + cc * 32;
-                    if (p.C) {
-                        if (p.flags & OPB_LIN_RESIDUAL) {            // x64 domain: vs += 64 * old
-                            if (row_ok && !(p.dbg & 2)) {
-                                const float4 *src = reinterpret_cast<const float4 *>(p.C + grow * p.Cout + c0);
+                    if ((p.flags & OPB_LIN_RESIDUAL) && row_ok && !(p.dbg & 2)) {
+                        if (p.C) {                                   // x64 domain: vs += 64 * old
+                            const float4 *src = reinterpret_cast<const float4 *>(p.C + grow * p.Cout + c0);
 #pragma unroll
-                                for (int q = 0; q < 8; ++q) {
-                                    const float4 o = src[q];
-                                    vv[4 * q] = fmaf(o.x, kScale, vv[4 * q]); vv[4 * q + 1] = fmaf(o.y, kScale, vv[4 * q + 1]);
-                                    vv[4 * q + 2] = fmaf(o.z, kScale, vv[4 * q + 2]); vv[4 * q + 3] = fmaf(o.w, kScale, vv[4 * q + 3]);
+                            for (int q = 0; q < 8; ++q) {
+                                const float4 o = src[q];
+                                vv[4 * q] = fmaf(o.x, kScale, vv[4 * q]); vv[4 * q + 1] = fmaf(o.y, kScale, vv[4 * q + 1]);
+                                vv[4 * q + 2] = fmaf(o.z, kScale, vv[4 * q + 2]); vv[4 * q + 3] = fmaf(o.w, kScale, vv[4 * q + 3]);
+                            }
+                        } else {                                     // no fp32 copy: the old value is the output planes' (hi + lo), in place
+                            const uint4 *sh = reinterpret_cast<const uint4 *>(p.Ch + grow * p.Cout + c0);
+                            const uint4 *sl = reinterpret_cast<const uint4 *>(p.Cl + grow * p.Cout + c0);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const uint4 h4 = sh[q], l4 = sl[q];
+                                const __half2 *hh = reinterpret_cast<const __half2 *>(&h4), *ll = reinterpret_cast<const __half2 *>(&l4);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const float2 a = __half22float2(hh[i]), e = __half22float2(ll[i]);
+                                    vv[8 * q + 2 * i] += a.x + e.x; vv[8 * q + 2 * i + 1] += a.y + e.y;
                                 }
                             }
                         }

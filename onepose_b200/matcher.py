@@ -298,14 +298,16 @@ class GATsSuperGlue(nn.Module):
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 
-    def _propagate_tc(self, x, x_p, xs, B, N, M, ksum, P, lw, ch, shared_src=False):
-        """x-side of AttentionPropagation on the tensor cores; x (fp32), its planes x_p and its column sums xs are updated
-        in place.  With Q'' = Q' M / (Q'_h . Ksum_h + 1e-6)  (:97-98):  message = Q'' P_b^T + bm  (:119), and the MLP's first
+    def _propagate_tc(self, st, M, ksum, P, lw, shared_src=False):
+        """x-side of AttentionPropagation on the tensor cores; the stream state st (planes st.p, column sums st.xs, and the
+        fp32 copy st.x when one is kept) is updated in place.
+        With Q'' = Q' M / (Q'_h . Ksum_h + 1e-6)  (:97-98):  message = Q'' P_b^T + bm  (:119), and the MLP's first
         layer sees it only through W0b, so  h = W0a x + P'_b Q'' + const  -- the merge projection is never run.
         InstanceNorm + ReLU (:144-146) without a normalisation pass: the mean is analytic (column sums of x and Q'' through
         W0a / P'_b), layer 0 writes relu(h - mean) as planes, 1/std is folded into per-frame layer-1 weights.
-        ch names the stream being updated ("2" / "3"): its scratch buffers are its own, the two may run concurrently."""
-        dev = x.device
+        st.ch names the stream ("2" / "3"): its scratch buffers are its own, the two may run concurrently."""
+        B, N, ch, x_p = st.B, st.N, st.ch, st.p
+        dev = x_p[0].device
         parts = lib.op_linear_tc_stat_parts(N)
         if shared_src:          # one source (ksum [1,256], P'_b [1,512,256]) for all B frames: P' is an ordinary weight
             ksum = self._ws.get("ksum_bc", (B, _D), torch.float32, dev).copy_(ksum.expand(B, _D))
@@ -317,7 +319,7 @@ class GATsSuperGlue(nn.Module):
         self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 16 | 32, elu_cols=_D, stats=qs, ksum=ksum, zscale_num=M,
                         tag="q")                                                                                  # ELU1 | COLSUM | ZSCALE
         cb = self._ws.get("cbias" + ch, (B, 2 * _D), torch.float32, dev)
-        call("op_mlp_center_bias", ptr(xs), parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cb),
+        call("op_mlp_center_bias", ptr(st.xs), st.parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cb),
              stream_ptr())
         hn_p = self._planes("hn" + ch, (B, N, 2 * _D), dev)
         stats = self._ws.get("tcstats" + ch, (B, parts, 2 * _D, 2), torch.float32, dev)
@@ -325,7 +327,49 @@ class GATsSuperGlue(nn.Module):
         W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
         call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
              stream_ptr())
-        self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=x, Cp=x_p, flags=2 | 16 | 64, stats=xs, tag="mlp1")        # RESIDUAL | COLSUM | WBATCHED
+        # residual add (:78,83) onto the fp32 copy when there is one, else onto the planes themselves
+        self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
+        st.parts = parts
+
+    def _new_stream(self, ch, B, N, dev, keep_fp32, name=None):
+        """Buffers of one descriptor stream of the tensor-core path: planes, column-sum partials (sized for either
+        producer: the projection epilogue or the GATs kernel) and, only when something still reads it, an fp32 copy."""
+        st = _StreamState()
+        st.ch, st.B, st.N = ch, B, N
+        name = name or ch
+        st.p = self._planes("x" + name, (B, N, _D), dev)
+        maxparts = max(lib.op_linear_tc_stat_parts(N), lib.op_gats_planes_parts(N))
+        st.xs = self._ws.get("xs" + name, (B, maxparts, _D, 2), torch.float32, dev)
+        st.parts = 0
+        st.x = self._ws.get("xf" + name, (B, N, _D), torch.float32, dev) if keep_fp32 else None
+        return st
+
+    def _load_stream(self, st, x):
+        """st <- fp32 x [B, N, 256]: planes + column sums (+ the fp32 copy)."""
+        call("op_split_planes", ptr(x), ptr(st.p[0]), ptr(st.p[1]), x.numel(), stream_ptr())
+        call("op_colsum_partial", ptr(x), st.B, st.N, _D, ptr(st.xs), stream_ptr())
+        st.parts = lib.op_linear_tc_stat_parts(st.N)
+        if st.x is not None and st.x.data_ptr() != x.data_ptr():
+            st.x.copy_(x)
+
+    @staticmethod
+    def _stream_fp32(st):
+        return st.x if st.x is not None else (st.p[0].float() + st.p[1].float()) / 64.0
+
+    def _gats_tc(self, st, db, L, lw, li):
+        """GATs layer on a tensor-core stream state: in place on the planes when no linear transform is configured,
+        else through the fp32 kernel and a re-split."""
+        hp = self.hparams
+        inc, add = hp["include_self"], hp["additional"]
+        if st.x is None:
+            leaves = db["leaves"]
+            timeline.work = 4.0 * _D * (leaves.shape[0] * st.N * L + 2 * st.B * st.N)
+            call("op_gats_leaf_aggregate_planes", ptr(leaves), 0 if db["shared"] else st.N * L * _D, ptr(st.p[0]), ptr(st.p[1]),
+                 ptr(lw["v1"]), ptr(lw["v2"]), ptr(st.xs), st.B, st.N, L, 0.2, int(inc), int(add and inc), stream_ptr())
+            st.parts = lib.op_gats_planes_parts(st.N)
+        else:
+            self._gats(st.x, db, st.B, st.N, L, lw, li)
+            self._load_stream(st, st.x)
 
     def _colsum(self, x, B, N, name):
         """Per-frame column sums of a plain fp32 tensor, in the partial layout of OPB_LIN_COLSUM."""
@@ -354,6 +398,106 @@ class GATsSuperGlue(nn.Module):
         timeline.work = 4.0 * _D * (Bl * N3 * L + 2 * B * N3)               # algorithmic bytes: leaves once, h3 in/out
         call("op_gats_leaf_aggregate", ptr(leaf_src), leaf_bstride, ptr(h3L), ptr(h3_add), ptr(v1), ptr(v2), ptr(x3),
                                          B, N3, L, 0.2, int(inc), 1, stream_ptr())
+
+    # ------------------------------------------------------------------ the 12 GNN layers + final_proj (:232-241)
+    def _encode_simt(self, x2, db, pk, B, N2, N3, L, m2, m3, dev):
+        """Exact-fp32 CUDA-core path (cross-check of the tensor-core path in the tests)."""
+        x3 = self._ws.get("x3", (B, N3, _D), torch.float32, dev)
+        x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
+        for li, lw in enumerate(pk["layers"]):
+            kind = lw["kind"]
+            if kind == "GATs":
+                self._gats(x3, db, B, N3, L, lw, li)
+            else:
+                # both deltas of a layer are computed from the layer's input (:77-78,82-83): reduce the source
+                # side of both calls first, then update the two streams in place.
+                if kind == "cross":
+                    KVa, Ksa = self._kv(x3, B, N3, lw, "a")       # desc2d attends to desc3d
+                    KVb, Ksb = self._kv(x2, B, N2, lw, "b")       # desc3d attends to desc2d
+                    Ma, Mb = N3, N2
+                else:
+                    KVa, Ksa = self._kv(x2, B, N2, lw, "a")
+                    KVb, Ksb = self._kv(x3, B, N3, lw, "b")
+                    Ma, Mb = N2, N3
+                self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
+                self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
+            if self._trace is not None:
+                self._trace.append((li, x2.clone(), x3.clone()))
+        self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")
+        self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
+
+    def _encode_tc(self, x2, db, pk, B, N2, N3, L, m2, m3, dev):
+        """Tensor-core path.  The streams live as split-precision planes + per-frame column sums; an fp32 copy is kept
+        only when the GATs layers need one (with_linear_transform)."""
+        keep = bool(self.hparams["with_linear_transform"])
+        s2 = self._new_stream("2", B, N2, dev, keep)
+        self._load_stream(s2, x2)
+        s3 = self._new_stream("3", B, N3, dev, keep)
+        # With one object DB shared by the whole batch the 3D stream does not depend on the query frame until it first
+        # receives a message from the 2D stream (the x-side update of the first 'cross' layer): up to there it is
+        # computed once (batch of 1) and then broadcast -- the same bits per frame, 1/B of the work.
+        single3 = bool(db["shared"])
+        if single3:
+            s3s = self._new_stream("3", 1, N3, dev, keep, name="3s")
+            self._load_stream(s3s, db["d3"])
+        else:
+            self._load_stream(s3, db["d3"])
+        main = torch.cuda.current_stream(dev)
+        side = self._side_stream(dev) if (self.two_streams and self._trace is None) else main
+        side.wait_stream(main)
+        ev2 = ev3 = None                 # end of the last cross-layer update of the 2D / 3D stream
+
+        def broadcast3():
+            s3.p[0].copy_(s3s.p[0].expand(B, N3, _D)); s3.p[1].copy_(s3s.p[1].expand(B, N3, _D))
+            s3.xs.copy_(s3s.xs.expand_as(s3.xs))
+            s3.parts = s3s.parts
+            if s3.x is not None:
+                s3.x.copy_(s3s.x.expand(B, N3, _D))
+
+        for li, lw in enumerate(pk["layers"]):
+            kind = lw["kind"]
+            cur3 = s3s if single3 else s3
+            if kind == "GATs":
+                self._gats_tc(cur3, db, L, lw, li)
+            else:
+                # The 2D stream runs on a side CUDA stream, the 3D stream on the caller's: within a layer the two
+                # updates only meet at the source-side reductions of a 'cross' layer (events below), so the short
+                # launches and the tail of every persistent GEMM of one stream overlap the other's work.
+                # Both deltas of a layer are computed from the layer's input (:77-78,82-83).
+                if ev3 is not None:
+                    side.wait_event(ev3)                          # the 3D stream is done with last layer's "2" reductions
+                if ev2 is not None:
+                    main.wait_event(ev2)
+                ev2 = ev3 = None
+                if kind == "cross":
+                    k3 = self._kv_tc(cur3.p, cur3.B, N3, lw, "3")     # desc2d attends to desc3d
+                    e3 = main.record_event()
+                    with torch.cuda.stream(side):
+                        k2 = self._kv_tc(s2.p, B, N2, lw, "2")        # desc3d attends to desc2d
+                        e2 = side.record_event()
+                        side.wait_event(e3)
+                        self._propagate_tc(s2, N3, *k3, lw, shared_src=single3)
+                        ev2 = side.record_event()
+                    main.wait_event(e2)
+                    if single3:                                   # from here on the 3D stream is per frame
+                        broadcast3()
+                        single3 = False
+                    self._propagate_tc(s3, N2, *k2, lw)
+                    ev3 = main.record_event()
+                else:
+                    with torch.cuda.stream(side):
+                        k2 = self._kv_tc(s2.p, B, N2, lw, "2")
+                        self._propagate_tc(s2, N2, *k2, lw)
+                    k3 = self._kv_tc(cur3.p, cur3.B, N3, lw, "3")
+                    self._propagate_tc(cur3, N3, *k3, lw)
+            if self._trace is not None:
+                cur3 = s3s if single3 else s3
+                self._trace.append((li, self._stream_fp32(s2).clone(), self._stream_fp32(cur3).expand(B, N3, _D).clone()))
+        main.wait_stream(side)
+        if single3:                                               # no cross layer at all (not the shipped layer list)
+            broadcast3()
+        self._linear_tc(s2.p, pk["Wf_p"], pk["bf"], B, N2, C=m2, tag="final")          # final_proj, :241
+        self._linear_tc(s3.p, pk["Wf_p"], pk["bf"], B, N3, C=m3, tag="final")
 
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
@@ -396,111 +540,12 @@ class GATsSuperGlue(nn.Module):
         pk = self._pack_weights(dev)
         db = self._static_db(desc3d, leaves[:, :, :N3 * L], L)
         x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
-        x3 = self._ws.get("x3", (B, N3, _D), torch.float32, dev)
-        tcp = self.use_tensor_cores
-        # With one object DB shared by the whole batch the 3D stream does not depend on the query frame until it first
-        # receives a message from the 2D stream (the x-side update of the first 'cross' layer): up to there it is
-        # computed once (batch of 1) and then broadcast -- the same bits per frame, 1/B of the work.
-        single3 = bool(tcp and db["shared"])
-        if single3:
-            x3s = self._ws.get("x3s", (1, N3, _D), torch.float32, dev)
-            x3s.copy_(db["d3"])
-            x3s_p = self._planes("x3s", (1, N3, _D), dev)
-        else:
-            x3.copy_(db["d3"] if not db["shared"] else db["d3"].expand(B, N3, _D))
-        xs2 = xs3 = xs3s = None          # per-frame column sums of x2 / x3 (partials), kept current by the mlp1 epilogue
-        if tcp:
-            x2_p = self._split(x2, *self._planes("x2", (B, N2, _D), dev))
-            x3_p = self._planes("x3", (B, N3, _D), dev)          # filled after the first GATs layer
-            xs2 = self._colsum(x2, B, N2, "xs2")
-            xs3 = self._ws.get("xs3", (B, lib.op_linear_tc_stat_parts(N3), _D, 2), torch.float32, dev)
-        main = torch.cuda.current_stream(dev)
-        side = self._side_stream(dev) if (tcp and self.two_streams and self._trace is None) else main
-        side.wait_stream(main)
-        ev2 = ev3 = None                 # end of the last cross-layer update of the 2D / 3D stream
-
-        def broadcast3():
-            x3.copy_(x3s.expand(B, N3, _D))
-            x3_p[0].copy_(x3s_p[0].expand(B, N3, _D)); x3_p[1].copy_(x3s_p[1].expand(B, N3, _D))
-            xs3.copy_(xs3s.expand_as(xs3))
-
-        for li, lw in enumerate(pk["layers"]):
-            kind = lw["kind"]
-            if kind == "GATs":
-                if single3:
-                    self._gats(x3s, db, 1, N3, L, lw, li)
-                    self._split(x3s, *x3s_p)
-                    xs3s = self._colsum(x3s, 1, N3, "xs3s")
-                else:
-                    self._gats(x3, db, B, N3, L, lw, li)
-                    if tcp:
-                        self._split(x3, *x3_p)
-                        self._colsum(x3, B, N3, "xs3")
-                if self._trace is not None:
-                    self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
-                continue
-            # both deltas of a layer are computed from the layer's input (:77-78,82-83): reduce the source
-            # side of both calls first, then update the two streams in place.
-            if not tcp:
-                if kind == "cross":
-                    KVa, Ksa = self._kv(x3, B, N3, lw, "a")       # desc2d attends to desc3d
-                    KVb, Ksb = self._kv(x2, B, N2, lw, "b")       # desc3d attends to desc2d
-                    Ma, Mb = N3, N2
-                else:
-                    KVa, Ksa = self._kv(x2, B, N2, lw, "a")
-                    KVb, Ksb = self._kv(x3, B, N3, lw, "b")
-                    Ma, Mb = N2, N3
-                self._propagate(x2, B, N2, Ma, KVa, Ksa, lw)
-                self._propagate(x3, B, N3, Mb, KVb, Ksb, lw)
-            else:
-                # The 2D stream runs on a side CUDA stream, the 3D stream on the caller's: within a layer the two
-                # updates only meet at the source-side reductions of a 'cross' layer (events below), so the short
-                # launches and the tail of every persistent GEMM of one stream overlap the other's work.
-                B3 = 1 if single3 else B
-                s3_p = x3s_p if single3 else x3_p
-                if ev3 is not None:
-                    side.wait_event(ev3)                          # the 3D stream is done with last layer's "2" reductions
-                if ev2 is not None:
-                    main.wait_event(ev2)
-                ev2 = ev3 = None
-                if kind == "cross":
-                    k3 = self._kv_tc(s3_p, B3, N3, lw, "3")       # desc2d attends to desc3d
-                    e3 = main.record_event()
-                    with torch.cuda.stream(side):
-                        k2 = self._kv_tc(x2_p, B, N2, lw, "2")    # desc3d attends to desc2d
-                        e2 = side.record_event()
-                        side.wait_event(e3)
-                        self._propagate_tc(x2, x2_p, xs2, B, N2, N3, *k3, lw, "2", shared_src=single3)
-                        ev2 = side.record_event()
-                    main.wait_event(e2)
-                    if single3:                                   # from here on the 3D stream is per frame
-                        broadcast3()
-                        single3 = False
-                    self._propagate_tc(x3, x3_p, xs3, B, N3, N2, *k2, lw, "3")
-                    ev3 = main.record_event()
-                else:
-                    with torch.cuda.stream(side):
-                        k2 = self._kv_tc(x2_p, B, N2, lw, "2")
-                        self._propagate_tc(x2, x2_p, xs2, B, N2, N2, *k2, lw, "2")
-                    k3 = self._kv_tc(s3_p, B3, N3, lw, "3")
-                    if single3:
-                        self._propagate_tc(x3s, x3s_p, xs3s, 1, N3, N3, *k3, lw, "3")
-                    else:
-                        self._propagate_tc(x3, x3_p, xs3, B, N3, N3, *k3, lw, "3")
-            if self._trace is not None:
-                self._trace.append((li, x2.clone(), (x3s.expand(B, N3, _D) if single3 else x3).clone()))
-        main.wait_stream(side)
-        if single3:                                               # no cross layer at all (not the shipped layer list)
-            broadcast3()
-
         m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
         m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
-        if tcp:
-            self._linear_tc(x2_p, pk["Wf_p"], pk["bf"], B, N2, C=m2, tag="final")          # final_proj, :241
-            self._linear_tc(x3_p, pk["Wf_p"], pk["bf"], B, N3, C=m3, tag="final")
+        if self.use_tensor_cores:
+            self._encode_tc(x2, db, pk, B, N2, N3, L, m2, m3, dev)
         else:
-            self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")
-            self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
+            self._encode_simt(x2, db, pk, B, N2, N3, L, m2, m3, dev)
         call("op_l2_normalize_rows", ptr(m2), ptr(m2), B * N2, _D, stream_ptr())
         call("op_l2_normalize_rows", ptr(m3), ptr(m3), B * N3, _D, stream_ptr())
 
@@ -526,6 +571,11 @@ class GATsSuperGlue(nn.Module):
             from . import pnp
             pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
         return pred, conf
+
+
+class _StreamState:
+    """One descriptor stream (2D query / 3D object) of the tensor-core path: see GATsSuperGlue._new_stream."""
+    __slots__ = ("ch", "B", "N", "p", "xs", "parts", "x")
 
 
 class LitModelGATsSPG(nn.Module):

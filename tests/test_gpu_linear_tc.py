@@ -276,3 +276,66 @@ def test_linear_tc_second_weight_equals_concatenated_weight():
     C3, _, _ = _linear_tc(A1, W, bias, A2=A2, W2=W2b, flags=512)
     ref = A1.double() @ W.double().t() + torch.einsum("bnk,bok->bno", A2.double(), W2b.double()) + bias.double()
     assert _rel(C3, ref) < 5e-6
+
+
+def test_residual_onto_the_output_planes_in_place():
+    """OPB_LIN_RESIDUAL without an fp32 output: the old value is read from the output planes (hi + lo) and the sum written back."""
+    from onepose_b200._lib import call, ptr, stream_ptr
+    B, N = 2, 333
+    g = torch.Generator().manual_seed(12)
+    A = (torch.randn(B, N, 512, generator=g) * 0.3).cuda(); W = (torch.randn(256, 512, generator=g) / 512 ** 0.5).cuda()
+    bias = (torch.randn(256, generator=g) * 0.1).cuda(); x0 = torch.randn(B, N, 256, generator=g).cuda()
+    a, w, xp = _planes(A), _planes(W), _planes(x0)
+    x0q = _unsplit(xp)                                        # what the planes actually hold (22 bits)
+    call("op_linear_tc", ptr(a[0]), ptr(a[1]), 512, None, None, 0, ptr(w[0]), ptr(w[1]), None, None, ptr(bias), None, ptr(xp[0]), ptr(xp[1]),
+         B, N, 256, 2, 0, None, None, 1.0, stream_ptr())
+    torch.cuda.synchronize()
+    ref = x0q + A.double() @ W.double().t() + bias.double()
+    assert _rel(_unsplit(xp), ref) < 5e-6
+
+
+@pytest.mark.parametrize("inc,add,shared,n3", [(1, 0, True, 100), (1, 1, True, 64), (0, 0, False, 37), (1, 0, False, 8)])
+def test_gats_on_planes_vs_fp32_kernel(inc, add, shared, n3):
+    """op_gats_leaf_aggregate_planes (in place on the planes, column sums out) against the fp32 kernel (GATs.py:62-123)."""
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    B, L = 3, 6
+    g = torch.Generator().manual_seed(n3)
+    leaves = torch.randn(1 if shared else B, n3, L, 256, generator=g).cuda()
+    h3 = torch.randn(B, n3, 256, generator=g).cuda()
+    v1 = (torch.randn(256, generator=g) / 16).cuda(); v2 = (torch.randn(256, generator=g) / 16).cuda()
+    hp = _planes(h3)
+    h3q = _unsplit(hp).float()                                # the fp32 kernel sees exactly what the planes hold
+    ref = torch.empty_like(h3q)
+    bstride = 0 if shared else n3 * L * 256
+    call("op_gats_leaf_aggregate", ptr(leaves), bstride, ptr(h3q), ptr(h3q) if (add and inc) else None, ptr(v1), ptr(v2), ptr(ref), B, n3, L,
+         0.2, inc, 1, stream_ptr())
+    parts = lib.op_gats_planes_parts(n3)
+    cs = torch.full((B, parts, 256, 2), float("nan"), device="cuda")
+    call("op_gats_leaf_aggregate_planes", ptr(leaves), bstride, ptr(hp[0]), ptr(hp[1]), ptr(v1), ptr(v2), ptr(cs), B, n3, L, 0.2, inc,
+         int(add and inc), stream_ptr())
+    torch.cuda.synchronize()
+    assert _rel(_unsplit(hp), ref.double()) < 2e-6
+    np.testing.assert_allclose(cs[..., 0].double().sum(1).cpu().numpy(), ref.double().sum(1).cpu().numpy(), rtol=1e-5, atol=1e-4)
+    assert float(cs[..., 1].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("flags", [dict(with_linear_transform=True), dict(include_self=False), dict(additional=True),
+                                   dict(with_linear_transform=True, additional=True)])
+def test_matcher_gats_variants_tensor_core_vs_cuda_core(flags):
+    """The non-shipped GATs flags (GATs.py:23-31) through both paths: planes-only streams without the linear transform,
+    an fp32 copy of the streams with it."""
+    from onepose_b200.matcher import GATsSuperGlue
+    from tests import helpers
+    hp = dict(synth.DEFAULT_HPARAMS); hp.update(flags)
+    obj = synth.make_object(4, 300, 5)
+    frames = [synth.make_frame(obj, f, 200) for f in range(2)]
+    data = {k: v.cuda() for k, v in synth.pack_batch(obj, frames).items()}
+    m = GATsSuperGlue(hp).cuda().eval()
+    m.load_state_dict(synth.make_weights(3, damped=True), strict=True)
+    pred_tc, conf_tc = m(data)
+    conf_tc = conf_tc.clone(); m0_tc = pred_tc["matches0_batched"].clone()
+    m.use_tensor_cores = False
+    pred_cc, conf_cc = m(data)
+    assert helpers.conf_rel_err(conf_tc.cpu(), conf_cc.cpu()) < helpers.CONF_RTOL
+    for b in range(2):
+        helpers.assert_matches_equal_off_ties(m0_tc[b].cpu(), pred_cc["matches0_batched"][b].cpu(), conf_cc[b].cpu(), axis=2)
