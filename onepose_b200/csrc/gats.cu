@@ -109,7 +109,7 @@ __device__ __forceinline__ void f4_to_planes(const float4 &v, uint2 &h, uint2 &l
 // ELU through MUFU.EX2 (absolute error ~2e-7, below the 22-bit planes the result is stored in)
 __device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : tc::ex2(x * 1.4426950408889634f) - 1.f; }
 
-__global__ void __launch_bounds__(kGatsPW * kGatsFW * 32)
+__global__ void __launch_bounds__(kGatsPW * kGatsFW * 32, 2)
 k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh, __half *xl, const float *__restrict__ v1,
               const float *__restrict__ v2, float2 *__restrict__ colsum, int B, int N3, int L, float alpha, int include_self,
               int add_self) {
@@ -121,7 +121,7 @@ k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh
     float4 *sl = smem4 + (size_t)pt * L * 64;
     float4 *red = smem4 + (size_t)kGatsPW * L * 64;          // [2][kGatsFW][kGatsPW][64] float4
     const float4 *v1v = reinterpret_cast<const float4 *>(v1), *v2v = reinterpret_cast<const float4 *>(v2);
-    const float4 a0 = v1v[lane], a1 = v1v[lane + 32], c0 = v2v[lane], c1 = v2v[lane + 32];
+    const float4 c0 = v2v[lane], c1 = v2v[lane + 32];
     // lane l owns channels 4l..4l+3 and 128+4l..128+4l+3 (the float4 pattern of the staged leaves)
     auto load_row = [&](int b, uint2 (&r)[4]) {
         const long long e = ((long long)b * N3 + n) * kD + 4 * lane;
@@ -139,6 +139,7 @@ k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh
         }
     };
     auto leaf_logits = [&]() {
+        const float4 a0 = v1v[lane], a1 = v1v[lane + 32];
         for (int j = 0; j < L; ++j) {
             const float d = warp_sum(dot8(sl[j * 64 + lane], sl[j * 64 + 32 + lane], a0, a1));
             if (lane == j) s_leaf = d;
