@@ -269,12 +269,14 @@ class GATsSuperGlue(nn.Module):
         self._linear(h, lw["W1"], lw["b1"], x, B, N, flags=2 | 8, mean=mean, rstd=rstd, tag="mlp1")   # NORM_RELU in, RESIDUAL out
 
     # ------------------------------------------------------------------ tcgen05 launchers (linear_tc.cuh)
-    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, W2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, ksum=None, zscale_num=1.0, tag=""):
-        """A1/A2/W/W2/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp."""
+    def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, W2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, ksum=None, zscale_num=1.0, tag="",
+                   work_k=None):
+        """A1/A2/W/W2/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp.  work_k: the K of the reference's
+        own projection when the GEMM carries extra columns (the identity block of the in-GEMM residual add)."""
         K1 = A1[0].shape[-1]
         K2 = 0 if A2 is None else A2[0].shape[-1]
         Cout = W[0].shape[-2]
-        timeline.work = 2.0 * B * rows * (K1 + K2) * Cout
+        timeline.work = 2.0 * B * rows * (work_k or (K1 + K2)) * Cout
         call("op_linear_tc", ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
              ptr(W[0]), ptr(W[1]), ptr(W2[0]) if W2 else None, ptr(W2[1]) if W2 else None, ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
              B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr(), tag=tag)
@@ -327,9 +329,22 @@ class GATsSuperGlue(nn.Module):
         W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
         call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
              stream_ptr())
-        # residual add (:78,83) onto the fp32 copy when there is one, else onto the planes themselves
-        self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
+        if st.x is None:
+            # residual add (:78,83) inside the GEMM: x_new = [hn | x] [W1 diag(rstd) | I]^T.  The old value streams through the
+            # prefetched TMA pipeline as a second operand instead of being fetched by the epilogue (exposed latency); the
+            # identity's planes are exact (64, 0), so the tensor core reproduces hi + lo of x to fp32 rounding.  In place: a
+            # row tile is read completely (all MMAs retired) before its epilogue stores, and Cout = 256 is one column tile.
+            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._identity_planes(dev), Cp=x_p, flags=16 | 64, stats=st.xs,
+                            tag="mlp1", work_k=2 * _D)                                                                             # COLSUM | WBATCHED
+        else:   # an fp32 copy is kept (with_linear_transform): residual add onto it in the epilogue
+            self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
         st.parts = parts
+
+    def _identity_planes(self, dev):
+        eye = self._db_cache.get("eye")
+        if eye is None or eye[0].device != dev:
+            eye = self._db_cache["eye"] = self._split_new(torch.eye(_D, dtype=torch.float32, device=dev))
+        return eye
 
     def _new_stream(self, ch, B, N, dev, keep_fp32, name=None):
         """Buffers of one descriptor stream of the tensor-core path: planes, column-sum partials (sized for either
