@@ -45,7 +45,7 @@ struct Params {
     int B, rows, Cout, K1, K2, flags, elu_cols;
     int row_tiles, col_tiles, total_tiles;   // total_tiles counts (frame, group of CG row tiles, column tile)
     int row_groups;                          // ceil(row_tiles / CG)
-    int dbg;                                 // experiment switches (env OPB_LIN_DBG): 1 = no output stores, 2 = no residual read, 4 = no MMAs
+    int dbg;                                 // experiment switches (env OPB_LIN_DBG): 1 = no output stores, 2 = no residual read, 4 = no MMAs, 8 = no wait for the staging buffer (racy: timing only)
     const float *bias;
     float *C;                      // fp32 [B, rows, Cout] or null
     __half *Ch, *Cl;               // planes [B, rows, Cout] (x64) or null
@@ -225,7 +225,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         auto stage_store = [&](const CUtensorMap *tm, int col, const uint4 *data, int bb, int r0) {
             if (p.dbg & 1) return;
             uint8_t *buf = s_stg + (warp * 2 + (nst & 1)) * STG_BUF;
-            if (lane == 0) tc::tma_store_wait_read1();
+            if (lane == 0 && !(p.dbg & 8)) tc::tma_store_wait_read1();
             __syncwarp();
 #pragma unroll
             for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4 *>(buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) = data[q];
@@ -234,11 +234,23 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             if (lane == 0) { tc::tma_store_3d(tm, buf, col, r0, bb); tc::tma_store_commit(); }
             ++nst;
         };
-        int j = 0;
+        int j = 0, cur_b = -1;
         for (int t = first_tile; t < p.total_tiles; t += tile_step, ++j) {
             int b, rt, ct; decode(t, b, rt, ct);
             const bool tile_ok = rt < p.row_tiles;                // false: ghost row tile of an odd pair
             const uint32_t as = j & 1, aph = (j >> 1) & 1;
+            if ((p.flags & (OPB_LIN_BIASB | OPB_LIN_ZSCALE)) && b != cur_b) {
+                // per-frame vectors (bias [B, Cout], Ksum [B, 256]) are staged in shared memory when the tile sequence enters a
+                // new frame -- every epilogue warp walks the same sequence, so they all meet here -- instead of being fetched
+                // from global memory inside each tile's critical path
+                asm volatile("bar.sync 1, 256;" ::: "memory");             // nobody still reads the previous frame's copy
+                const int tt = threadIdx.x;                               // 0..255: the epilogue warps
+                if (p.flags & OPB_LIN_BIASB)
+                    for (int i = tt; i < p.Cout; i += EPI_WARPS * 32) s_bias[i] = kScale * __ldg(p.bias + (long long)b * p.Cout + i);
+                if (p.flags & OPB_LIN_ZSCALE) s_bias[256 + tt] = __ldg(p.ksum + (long long)b * p.Cout + tt);   // Cout == 256: upper half is free
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                cur_b = b;
+            }
             const int row = rt * BM + quad * 32 + lane;
             const bool row_ok = row < p.rows;
             const long long grow = (long long)b * p.rows + (row_ok ? row : 0);
@@ -276,13 +288,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     }
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
-                        float4 bq;
-                        if (p.flags & OPB_LIN_BIASB) {                       // per-frame bias [B, Cout], brought to the x64 domain here
-                            bq = __ldg(reinterpret_cast<const float4 *>(p.bias + (long long)b * p.Cout + c0) + q);
-                            bq.x *= kScale; bq.y *= kScale; bq.z *= kScale; bq.w *= kScale;
-                        } else {
-                            bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
-                        }
+                        const float4 bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
                         vv[4 * q] = fmaf(vv[4 * q], 1.f / kScale, bq.x); vv[4 * q + 1] = fmaf(vv[4 * q + 1], 1.f / kScale, bq.y);
                         vv[4 * q + 2] = fmaf(vv[4 * q + 2], 1.f / kScale, bq.z); vv[4 * q + 3] = fmaf(vv[4 * q + 3], 1.f / kScale, bq.w);
                     }
@@ -310,10 +316,10 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         for (int i = 0; i < 32; ++i) vv[i] = fmaxf(vv[i], 0.f);
                     }
                     if (p.flags & OPB_LIN_ZSCALE) {                // Q'_h . Ksum_h of this row (linear attention normaliser, :97)
-                        const float4 *ks = reinterpret_cast<const float4 *>(p.ksum + (long long)b * p.Cout + c0);
+                        const float4 *ks = reinterpret_cast<const float4 *>(s_bias + 256 + c0);
 #pragma unroll
                         for (int q = 0; q < 8; ++q) {
-                            const float4 k4 = __ldg(ks + q);
+                            const float4 k4 = ks[q];
                             den = fmaf(vv[4 * q], k4.x, den); den = fmaf(vv[4 * q + 1], k4.y, den);
                             den = fmaf(vv[4 * q + 2], k4.z, den); den = fmaf(vv[4 * q + 3], k4.w, den);
                         }
