@@ -82,6 +82,7 @@ int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_bstride, voi
 #define OPB_LIN_BIASB 128     /* op_linear_tc: bias is [B, Cout], one vector per frame */
 #define OPB_LIN_CSTATS_RELU 256 /* op_linear_tc: stats_partial = (sum, sum of squares) of the value after bias over the valid rows, then ReLU */
 #define OPB_LIN_W2BATCHED 512 /* op_linear_tc: the second weight W2 is [B, Cout, K2], one matrix per frame */
+#define OPB_LIN_W2_EXACT_HI 1024 /* op_linear_tc: W2's lo plane is all zeros (e.g. the identity of the in-GEMM residual add): its MMA pass is skipped */
 int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
               float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,
               const float *mean, const float *rstd, double *stats_partial, void *stream);

@@ -185,6 +185,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             auto mma = [](uint32_t d, uint64_t a, uint64_t b, uint32_t acc) { if (CG == 2) tc::umma_f16_cg2(d, a, b, idesc, acc); else tc::umma_f16(d, a, b, idesc, acc); };
             auto commit = [](uint64_t *barrier) { if (CG == 2) tc::umma_commit_cg2(barrier); else tc::umma_commit(barrier); };
             const uint32_t base = tc::smem_u32(smem);
+            const bool w2_exact = (p.flags & OPB_LIN_W2_EXACT_HI) != 0;
             uint32_t it = 0;
             int j = 0;
             for (int t = first_tile; t < p.total_tiles; t += tile_step, ++j) {
@@ -207,7 +208,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
                         mma(d, al + 2 * k, wh + 2 * k, 1);
-                        mma(d, ah + 2 * k, wl + 2 * k, 1);
+                        if (!(w2_exact && kb >= nkb1)) mma(d, ah + 2 * k, wl + 2 * k, 1);   // W2's lo plane is all zeros: nothing to add
                     }
                     commit(&bar->empty[stage]);                   // frees the stage (in both CTAs of a pair) when these MMAs retire
                 }
