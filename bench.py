@@ -278,8 +278,15 @@ def run_ours(args):
             kernels[name] = ent
         dom = next(k for k in kernels if "frac" in kernels[k])
         d = kernels[dom]
+        try:        # DRAM bytes per launch of that kernel from the committed ncu capture (profiles/traffic.json), else null
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+                traffic = json.load(f)
+        except (OSError, ValueError):
+            traffic = {}
+        tr = traffic.get(dom)
         roofline = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"], "peak": d["peak"], "unit": d["unit"],
-                    "frac": d["frac"], "traffic": None, "peak_source": peaks["source"] + (", sustained" if d["bound"] == "tensor" else ""),
+                    "frac": d["frac"], "traffic": None if tr is None else tr["traffic_bytes"],
+                    "traffic_launch": None if tr is None else tr["launch"], "peak_source": peaks["source"] + (", sustained" if d["bound"] == "tensor" else ""),
                     "share_of_step": d["share"]}
         sim = kernels.get("op_sim_dual_softmax")
         cpu = None
@@ -305,7 +312,9 @@ def run_ours(args):
             "kernel_timing": {"how": "CUDA events around every launch in a second pass of the same steps with the two matcher "
                                      "streams serialised on one CUDA stream", "ms_per_step": ms_serial / args.steps},
             "roofline": roofline,
-            "roofline_sim_dual_softmax": None if sim is None else {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
+            "roofline_sim_dual_softmax": None if sim is None else dict(
+                {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
+                traffic=(traffic.get("op_sim_dual_softmax") or {}).get("traffic_bytes")),
             "cpu_baseline": cpu, "clocks": clk, "kernels": kernels, "sanity": sanity,
         }))
     if world > 1:
