@@ -137,94 +137,104 @@ k_atb_tc(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUte
 namespace opb {
 namespace atb {
 
-// per (head h, frame b, group of 16 channels d): G = sum of chunk partials; Ksum = sum of column-sum partials;
+// per (head h, frame b): G_h = sum of chunk partials; Ksum_h = sum of column-sum partials;
 // KV_h[d,:] = (G_h[d,:] Wv_h^T + Ksum_h[d] bv_h^T) / M;  P_b[o, h*64+d] = sum_q KV_h[d,q] Wm[o, h*64+q], o < n_out, written as
-// split-precision planes (x64).  All folds in a fixed order.
-constexpr int kPostD = 16;
-__global__ void __launch_bounds__(256)
+// split-precision planes (x64).  All folds in a fixed order.  One CTA owns a whole head, so the head's slices of WvT / WmT
+// (64 KB + 64..128 KB) cross L2 -> SM once per frame-head; 512 threads, G (64 KB) and KV' (17 KB) in shared memory.
+constexpr int kPostThreads = 512;
+constexpr int kPostSmem = (64 * 256 + 64 * 68 + 64) * 4 + 8 * 64 * 8;
+__global__ void __launch_bounds__(kPostThreads)
 k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
           const float *__restrict__ WvT /* [4][256 c][64 q] = Wv[h*64+q][c] */, const float *__restrict__ bv,
           const float *__restrict__ WmT /* [4][64 q][n_out o] = Wm[o][h*64+q] */, int n_out, float inv_m, float *__restrict__ ksum /* [B][256] */,
           float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
-    __shared__ __align__(16) float G[kPostD][256];
-    __shared__ __align__(16) float KV[kPostD][68];
-    __shared__ float Ks[kPostD];
-    __shared__ double Kslice[16][kPostD];
-    const int h = blockIdx.x, dg = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
-    const int ch0 = h * 64 + dg * kPostD;                       // first K' channel of this block
-    {   // G fold: thread = column c, 16 independent loads in flight per chunk; chunks summed in order
-        float acc[kPostD];
+    extern __shared__ __align__(16) float post_smem[];
+    float (*G)[256] = reinterpret_cast<float (*)[256]>(post_smem);                        // [64 d][256 c]
+    float (*KV)[68] = reinterpret_cast<float (*)[68]>(post_smem + 64 * 256);              // [64 d][64 q] (+4 pad)
+    float *Ks = post_smem + 64 * 256 + 64 * 68;                                           // [64 d]
+    double (*Kslice)[64] = reinterpret_cast<double (*)[64]>(post_smem + 64 * 256 + 64 * 68 + 64);   // [8 slices][64 d]
+    const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const int ch0 = h * 64;                                     // first K' channel of this head
+    {   // G fold: thread = (column c, half of the head's 64 rows), 32 independent loads in flight per chunk; chunks summed in order
+        const int c = tid & 255, d0 = (tid >> 8) * 32;
+        float acc[32];
 #pragma unroll
-        for (int d = 0; d < kPostD; ++d) acc[d] = 0.f;
+        for (int d = 0; d < 32; ++d) acc[d] = 0.f;
         for (int k = 0; k < nchunks; ++k) {
-            const float *src = partial + (((long long)b * nchunks + k) * 256 + ch0) * 256 + tid;
+            const float *src = partial + (((long long)b * nchunks + k) * 256 + ch0 + d0) * 256 + c;
 #pragma unroll
-            for (int d = 0; d < kPostD; ++d) acc[d] += __ldg(src + d * 256);
+            for (int d = 0; d < 32; ++d) acc[d] += __ldg(src + d * 256);
         }
 #pragma unroll
-        for (int d = 0; d < kPostD; ++d) G[d][tid] = acc[d];
+        for (int d = 0; d < 32; ++d) G[d0 + d][c] = acc[d];
     }
-    {   // Ksum fold: 16 slices of the partial list per channel in float64, then the slices in order
-        const int d = tid & (kPostD - 1), slice = tid / kPostD;              // 16 slices
-        const int per = (nparts + 15) / 16, k0 = slice * per, k1 = min(nparts, k0 + per);
+    {   // Ksum fold: 8 slices of the partial list per channel in float64, then the slices in order
+        const int d = tid & 63, slice = tid >> 6;
+        const int per = (nparts + 7) / 8, k0 = slice * per, k1 = min(nparts, k0 + per);
         double s = 0;
         for (int k = k0; k < k1; ++k) s += (double)__ldg(&ksum_part[((long long)b * nparts + k) * 256 + ch0 + d].x);
         Kslice[slice][d] = s;
     }
     __syncthreads();
-    if (tid < kPostD) {
+    if (tid < 64) {
         double s = 0;
 #pragma unroll
-        for (int k = 0; k < 16; ++k) s += Kslice[k][tid];
+        for (int k = 0; k < 8; ++k) s += Kslice[k][tid];
         Ks[tid] = (float)s;
         ksum[(long long)b * 256 + ch0 + tid] = (float)s;
     }
     __syncthreads();
-    {   // KV[d][q]: thread = (q, group of 4 d); G rows are read four channels at a time (broadcast LDS.128)
-        const int q = tid & 63, d0 = (tid >> 6) * 4;
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    {   // KV[d][q]: thread = (q, group of 8 d); G rows are read four channels at a time (broadcast LDS.128)
+        const int q = tid & 63, d0 = (tid >> 6) * 8;
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
         const float *w = WvT + (long long)h * 256 * 64 + q;          // coalesced over q
-#pragma unroll 4
+#pragma unroll 2
         for (int c = 0; c < 256; c += 4) {
             const float w0 = __ldg(w + c * 64), w1 = __ldg(w + (c + 1) * 64), w2 = __ldg(w + (c + 2) * 64), w3 = __ldg(w + (c + 3) * 64);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < 8; ++i) {
                 const float4 g4 = *reinterpret_cast<const float4 *>(&G[d0 + i][c]);
                 acc[i] = fmaf(g4.x, w0, acc[i]); acc[i] = fmaf(g4.y, w1, acc[i]); acc[i] = fmaf(g4.z, w2, acc[i]); acc[i] = fmaf(g4.w, w3, acc[i]);
             }
         }
         const float bq = bv[h * 64 + q];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < 8; ++i) {
             const float v = fmaf(Ks[d0 + i], bq, acc[i]) * inv_m;        // value / v_length, :93-94
             KV[d0 + i][q] = v;
-            if (kv_out) kv_out[(((long long)b * 4 + h) * 64 + dg * kPostD + d0 + i) * 64 + q] = v;
+            if (kv_out) kv_out[(((long long)b * 4 + h) * 64 + d0 + i) * 64 + q] = v;
         }
     }
     __syncthreads();
-    for (int o = tid; o < n_out; o += 256) {   // P[o][ch0 + d], thread = o
+    for (int o = tid; o < n_out; o += kPostThreads) {   // P[o][ch0 + d], thread = o, 16 d at a time
         float wm[64];
 #pragma unroll
         for (int q = 0; q < 64; ++q) wm[q] = __ldg(WmT + ((long long)h * 64 + q) * n_out + o);     // coalesced over o
-        uint32_t hh[kPostD / 2], ll[kPostD / 2];
+#pragma unroll 1
+        for (int dg = 0; dg < 4; ++dg) {
+            uint32_t hh[8], ll[8];
 #pragma unroll
-        for (int d = 0; d < kPostD; d += 2) {
-            float a0 = 0.f, a1 = 0.f;
+            for (int d = 0; d < 16; d += 2) {
+                const float *k0p = KV[dg * 16 + d], *k1p = KV[dg * 16 + d + 1];
+                float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-            for (int q = 0; q < 64; q += 4) {
-                const float4 k0 = *reinterpret_cast<const float4 *>(&KV[d][q]), k1 = *reinterpret_cast<const float4 *>(&KV[d + 1][q]);
-                a0 = fmaf(k0.x, wm[q], a0); a0 = fmaf(k0.y, wm[q + 1], a0); a0 = fmaf(k0.z, wm[q + 2], a0); a0 = fmaf(k0.w, wm[q + 3], a0);
-                a1 = fmaf(k1.x, wm[q], a1); a1 = fmaf(k1.y, wm[q + 1], a1); a1 = fmaf(k1.z, wm[q + 2], a1); a1 = fmaf(k1.w, wm[q + 3], a1);
+                for (int q = 0; q < 64; q += 4) {
+                    const float4 k0 = *reinterpret_cast<const float4 *>(k0p + q), k1 = *reinterpret_cast<const float4 *>(k1p + q);
+                    a0 = fmaf(k0.x, wm[q], a0); a0 = fmaf(k0.y, wm[q + 1], a0); a0 = fmaf(k0.z, wm[q + 2], a0); a0 = fmaf(k0.w, wm[q + 3], a0);
+                    a1 = fmaf(k1.x, wm[q], a1); a1 = fmaf(k1.y, wm[q + 1], a1); a1 = fmaf(k1.z, wm[q + 2], a1); a1 = fmaf(k1.w, wm[q + 3], a1);
+                }
+                __half h0, l0, h1, l1;
+                tc::split_f16(a0 * 64.f, h0, l0); tc::split_f16(a1 * 64.f, h1, l1);
+                hh[d / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+                ll[d / 2] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
             }
-            __half h0, l0, h1, l1;
-            tc::split_f16(a0 * 64.f, h0, l0); tc::split_f16(a1 * 64.f, h1, l1);
-            hh[d / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
-            ll[d / 2] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+            uint4 *ph = reinterpret_cast<uint4 *>(Ph + ((long long)b * n_out + o) * 256 + ch0 + dg * 16);
+            uint4 *pl = reinterpret_cast<uint4 *>(Pl + ((long long)b * n_out + o) * 256 + ch0 + dg * 16);
+            ph[0] = make_uint4(hh[0], hh[1], hh[2], hh[3]); ph[1] = make_uint4(hh[4], hh[5], hh[6], hh[7]);
+            pl[0] = make_uint4(ll[0], ll[1], ll[2], ll[3]); pl[1] = make_uint4(ll[4], ll[5], ll[6], ll[7]);
         }
-        uint4 *ph = reinterpret_cast<uint4 *>(Ph + ((long long)b * n_out + o) * 256 + ch0);
-        uint4 *pl = reinterpret_cast<uint4 *>(Pl + ((long long)b * n_out + o) * 256 + ch0);
-        ph[0] = make_uint4(hh[0], hh[1], hh[2], hh[3]); ph[1] = make_uint4(hh[4], hh[5], hh[6], hh[7]);
-        pl[0] = make_uint4(ll[0], ll[1], ll[2], ll[3]); pl[1] = make_uint4(ll[4], ll[5], ll[6], ll[7]);
     }
 }
 
@@ -258,7 +268,12 @@ extern "C" int op_kv_post(const float *partial, int nchunks, const float *ksum_p
     using namespace opb;
     OPB_CHECK_ARG(partial && ksum_partial && WvT && bv && WmT && ksum && Ph && Pl, "op_kv_post: null pointer");
     OPB_CHECK_ARG(B > 0 && nchunks > 0 && nparts > 0 && B <= 65535 && n_out > 0 && n_out % 256 == 0, "op_kv_post: bad shape (n_out=%d)", n_out);
-    atb::k_kv_post<<<dim3(4, 64 / atb::kPostD, B), 256, 0, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, WvT, bv, WmT,
+    static bool post_configured = false;
+    if (!post_configured) {
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(atb::k_kv_post, cudaFuncAttributeMaxDynamicSharedMemorySize, atb::kPostSmem));
+        post_configured = true;
+    }
+    atb::k_kv_post<<<dim3(4, B), atb::kPostThreads, atb::kPostSmem, (cudaStream_t)stream>>>(partial, nchunks, (const float2 *)ksum_partial, nparts, WvT, bv, WmT,
                                                                             n_out, inv_m, ksum, kv_out, (__half *)Ph, (__half *)Pl);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
