@@ -296,14 +296,18 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         OPB_CHECK_LAUNCH();
         CUtensorMap t2h, t2l, t3h, t3l, tconf;
         int rc;
+        // One CTA per row tile by default; OPB_SIM_CG=2 selects the CTA-pair (cta_group::2) form of the same kernel.  Measured at the
+        // headline shape (64 frames): pair 1.30 + 1.97 ms, single 1.26 + 1.87 ms -- the pair halves the L2 -> SM stream of B per CTA
+        // but its 8 KB ring units double the per-unit round trip, so it does not win here.
+        static const int cg = [] { const char *e = getenv("OPB_SIM_CG"); return (e && e[0] == '2') ? 2 : 1; }();
         if ((rc = make_tmap_f16_3d(&t2h, w.m2h, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) ||
-            (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, simtc::BN)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, simtc::BN)))
+            (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, simtc::BN / cg)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, simtc::BN / cg)))
             return rc;
         // enough CTAs for ~2 waves over 148 SMs: split the column tiles when frames x row tiles is small
         int splits = ceil_div(2 * 148, (long long)B * p.tiles_m);
         splits = splits < 1 ? 1 : (splits > p.tiles_n ? p.tiles_n : splits);
         simtc::Params q{};
-        q.N2 = N2; q.N3 = N3; q.tiles_n = p.tiles_n; q.tiles_per_split = ceil_div(p.tiles_n, splits);
+        q.N2 = N2; q.N3 = N3; q.tiles_n = p.tiles_n; q.tiles_m = p.tiles_m; q.tiles_per_split = ceil_div(p.tiles_n, splits);
         splits = ceil_div(p.tiles_n, q.tiles_per_split);
         row_parts = splits * 2;
         const double log2e = 1.4426950408889634;
@@ -317,18 +321,28 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         q.rowmax_part = w.rowmax_part; q.colmax_part = w.colmax_part; q.conf = conf;
         static bool configured = false;
         if (!configured) {
-            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
-            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
             configured = true;
         }
-        dim3 grid(splits, p.tiles_m, B);
-        simtc::k_sim_tc<1><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, tconf, q);
-        OPB_CHECK_LAUNCH();
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute attr[1];
+        cfg.gridDim = dim3(ceil_div(p.tiles_m, cg) * cg, splits, B);       // a ghost row tile completes the last pair
+        cfg.blockDim = dim3(320);
+        cfg.dynamicSmemBytes = simtc::SMEM_BYTES;
+        cfg.stream = st;
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = cg; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 2>, t2h, t2l, t3h, t3l, tconf, q));
+        else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 1>, t2h, t2l, t3h, t3l, tconf, q));
         k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n * 2, N2, w.invR, 1);
         k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC, 1);
         OPB_CHECK_LAUNCH();
-        simtc::k_sim_tc<2><<<grid, 320, simtc::SMEM_BYTES, st>>>(t2h, t2l, t3h, t3l, tconf, q);
-        OPB_CHECK_LAUNCH();
+        if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 2>, t2h, t2l, t3h, t3l, tconf, q));
+        else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 1>, t2h, t2l, t3h, t3l, tconf, q));
     }
     k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, N3, w.idx0, w.val0);
     k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, N2, w.idx1, w.val1);

@@ -17,10 +17,24 @@
 namespace opb {
 namespace simtc {
 
-constexpr int BM = 128, BN = 128, NKB = 4, UNITS = 4;
+constexpr int BM = 128, BN = 128, NKB = 4;
 constexpr int TILE_BYTES = 128 * 128;                 // 128 rows x 64 fp16
 constexpr int A_BYTES = 2 * NKB * TILE_BYTES;         // 131072
-constexpr int RING_BYTES = UNITS * TILE_BYTES;        // 81920
+constexpr int RING_BYTES = 4 * TILE_BYTES;            // 65536
+constexpr int MAX_UNITS = 8;
+// CG = 1: one CTA per 128 query rows; a ring unit is a whole 128-column k-block of B (16 KB, 4 units).
+// CG = 2: a CTA pair (cta_group::2) per 256 query rows: each CTA keeps its own 128 rows of A resident and stages HALF of every
+//         B k-block (64 columns, 8 KB, 8 units), the leader issues M256 N128 MMAs.  Every row tile re-streams all of the frame's
+//         3D descriptors from L2, and that L2 -> SM stream (17 GB per 64 frames and two passes, against ~12 TB/s chip-wide) is
+//         what bounds the kernel: with MMAs, conf arithmetic and stores switched off (OPB_SIM_DBG = 25) 0.86 + 0.81 of the
+//         1.26 + 1.87 ms remain (37 B/clk/SM of ring traffic).  The pair halves the bytes per CTA but, with 8 KB units, not the
+//         time (the ring is round-trip bound), so CG = 1 stays the default.
+template <int CG>
+struct SimCfg {
+    static constexpr int UNITS = 4 * CG;
+    static constexpr int B_ROWS = BN / CG;            // columns of a B k-block held by one CTA
+    static constexpr int UNIT_BYTES = B_ROWS * 128;   // 16384 / 8192
+};
 constexpr int STG_WARP_BYTES = 32 * 16 * 4;            // per epilogue warp: 32 rows x 16 fp32 columns, TMA-store staging
 constexpr int STG_BYTES = 8 * STG_WARP_BYTES;         // 16384
 constexpr int SCRATCH_BYTES = 2 * 4 * BN * 8;         // double-buffered [4 warps][128] u64
@@ -36,12 +50,13 @@ struct Params {
     const float *lgR, *lgC;                           // log2(1/R_n), log2(1/C_m)
     unsigned long long *rowmax_part, *colmax_part;
     float *conf;
+    int tiles_m;                                      // row tiles of a frame (the grid may carry one ghost row tile to fill a pair)
     int tma_store;                                    // conf rows are 16-byte aligned: write conf through TMA stores
     int dbg;                                          // experiment switches (OPB_SIM_DBG), 0 in production
 };
 
 struct Barriers {
-    uint64_t a_full, b_full[UNITS], b_empty[UNITS], acc_full[2], acc_empty[2];
+    uint64_t a_full, b_full[MAX_UNITS], b_empty[MAX_UNITS], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
 
@@ -76,7 +91,7 @@ __device__ __forceinline__ unsigned long long transpose_reduce_max(unsigned long
     return v[0];
 }
 
-template <int PASS>
+template <int PASS, int CG>
 __global__ void __launch_bounds__(320, 1)
 k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l,
          const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l,
@@ -90,8 +105,11 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     float *s_lgc = reinterpret_cast<float *>(smem + A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES);
     Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES + LGC_BYTES);
 
+    constexpr int UNITS = SimCfg<CG>::UNITS, UNIT_BYTES = SimCfg<CG>::UNIT_BYTES;
+    const uint32_t rank = CG == 2 ? tc::cluster_ctarank() : 0;            // 0 = leader of the pair (cluster dims (2, 1, 1): row tiles 2i, 2i+1)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int split = blockIdx.x, row_tile = blockIdx.y, b = blockIdx.z;
+    const int split = blockIdx.y, row_tile = blockIdx.x, b = blockIdx.z;
+    const bool tile_ok = row_tile < p.tiles_m;                            // false: ghost row tile completing a pair
     const int m0 = row_tile * BM;
     const int t0 = split * p.tiles_per_split;
     const int t1 = min(p.tiles_n, t0 + p.tiles_per_split);
@@ -100,41 +118,58 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     if (threadIdx.x == 0) {
         tc::mbar_init(&bar->a_full, 1);
         for (int i = 0; i < UNITS; ++i) { tc::mbar_init(&bar->b_full[i], 1); tc::mbar_init(&bar->b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], 8); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], 8 * CG); }
         tc::fence_barrier_init();
     }
-    if (warp == 9) tc::tmem_alloc<256>(&bar->tmem_base);
+    if (warp == 9) { if (CG == 2) tc::tmem_alloc_cg2<256>(&bar->tmem_base); else tc::tmem_alloc<256>(&bar->tmem_base); }
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_m2h); tc::tma_prefetch_desc(&tm_m2l); tc::tma_prefetch_desc(&tm_m3h); tc::tma_prefetch_desc(&tm_m3l);
         if (PASS == 2 && p.tma_store) tc::tma_prefetch_desc(&tm_conf);
     }
     tc::tcgen05_fence_before();
-    __syncthreads();
+    if (CG == 2) tc::cluster_sync(); else __syncthreads();                // the peer's barriers exist before anything is sent to them
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = bar->tmem_base;
 
     if (warp == 8) {
         // ================= TMA producer =================
         if (lane == 0) {
-            tc::mbar_arrive_expect_tx(&bar->a_full, A_BYTES);
-            for (int plane = 0; plane < 2; ++plane)
-                for (int kb = 0; kb < NKB; ++kb)
-                    tc::tma_load_3d(sA + (plane * NKB + kb) * TILE_BYTES, plane ? &tm_m2l : &tm_m2h, &bar->a_full, kb * 64, m0, b);
+            if (CG == 2) {
+                // both CTAs load into their own shared memory; the bytes of both are credited to the leader's barriers
+                const uint32_t af = tc::mapa(tc::smem_u32(&bar->a_full), 0);
+                if (rank == 0) tc::mbar_arrive_expect_tx(&bar->a_full, 2 * A_BYTES);
+                for (int plane = 0; plane < 2; ++plane)
+                    for (int kb = 0; kb < NKB; ++kb)
+                        tc::tma_load_3d_cg2(sA + (plane * NKB + kb) * TILE_BYTES, plane ? &tm_m2l : &tm_m2h, af, kb * 64, m0, b);
+            } else {
+                tc::mbar_arrive_expect_tx(&bar->a_full, A_BYTES);
+                for (int plane = 0; plane < 2; ++plane)
+                    for (int kb = 0; kb < NKB; ++kb)
+                        tc::tma_load_3d(sA + (plane * NKB + kb) * TILE_BYTES, plane ? &tm_m2l : &tm_m2h, &bar->a_full, kb * 64, m0, b);
+            }
             uint32_t u = 0;
             for (int t = t0; t < t1; ++t)
                 for (int kb = 0; kb < NKB; ++kb)
                     for (int plane = 0; plane < 2; ++plane, ++u) {
                         const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
                         tc::mbar_wait(&bar->b_empty[stage], ph ^ 1);
-                        tc::mbar_arrive_expect_tx(&bar->b_full[stage], TILE_BYTES);
-                        tc::tma_load_3d(sB + stage * TILE_BYTES, plane ? &tm_m3l : &tm_m3h, &bar->b_full[stage], kb * 64, t * BN, b);
+                        if (CG == 2) {
+                            if (rank == 0) tc::mbar_arrive_expect_tx(&bar->b_full[stage], 2 * UNIT_BYTES);
+                            tc::tma_load_3d_cg2(sB + stage * UNIT_BYTES, plane ? &tm_m3l : &tm_m3h, tc::mapa(tc::smem_u32(&bar->b_full[stage]), 0),
+                                                kb * 64, t * BN + (int)rank * SimCfg<CG>::B_ROWS, b);
+                        } else {
+                            tc::mbar_arrive_expect_tx(&bar->b_full[stage], UNIT_BYTES);
+                            tc::tma_load_3d(sB + stage * UNIT_BYTES, plane ? &tm_m3l : &tm_m3h, &bar->b_full[stage], kb * 64, t * BN, b);
+                        }
                     }
         }
         __syncwarp();
     } else if (warp == 9) {
         // ================= MMA issuer =================
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN);
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = tc::umma_idesc_f16(BM * CG, BN);
+            auto mma = [](uint32_t dd, uint64_t a, uint64_t bq, uint32_t acc) { if (CG == 2) tc::umma_f16_cg2(dd, a, bq, idesc, acc); else tc::umma_f16(dd, a, bq, idesc, acc); };
+            auto commit = [](uint64_t *barrier) { if (CG == 2) tc::umma_commit_cg2(barrier); else tc::umma_commit(barrier); };
             tc::mbar_wait(&bar->a_full, 0);
             tc::tcgen05_fence_after();
             const uint32_t a_base = tc::smem_u32(sA), b_base = tc::smem_u32(sB);
@@ -150,21 +185,22 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                         const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
                         tc::mbar_wait(&bar->b_full[stage], ph);
                         tc::tcgen05_fence_after();
-                        const uint64_t bd = tc::umma_desc_k128(b_base + stage * TILE_BYTES);
+                        const uint64_t bd = tc::umma_desc_k128(b_base + stage * UNIT_BYTES);
                         const uint64_t ah = tc::umma_desc_k128(a_base + kb * TILE_BYTES);
                         const uint64_t al = tc::umma_desc_k128(a_base + (NKB + kb) * TILE_BYTES);
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {            // UMMA_K = 16 fp16 = 32 bytes -> +2 in the address field
+                            if (p.dbg & 8) continue;
                             if (plane == 0) {
-                                tc::umma_f16(d, ah + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
-                                tc::umma_f16(d, al + 2 * k, bd + 2 * k, idesc, 1);
+                                mma(d, ah + 2 * k, bd + 2 * k, (kb | k) != 0);
+                                mma(d, al + 2 * k, bd + 2 * k, 1);
                             } else {
-                                tc::umma_f16(d, ah + 2 * k, bd + 2 * k, idesc, 1);
+                                mma(d, ah + 2 * k, bd + 2 * k, 1);
                             }
                         }
-                        tc::umma_commit(&bar->b_empty[stage]);    // frees the ring unit when these MMAs retire
+                        commit(&bar->b_empty[stage]);             // frees the ring unit (in both CTAs of a pair) when these MMAs retire
                     }
-                tc::umma_commit(&bar->acc_full[as]);
+                commit(&bar->acc_full[as]);
             }
         }
         __syncwarp();
@@ -185,16 +221,16 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         auto fold_columns = [&](int tt, int jj) {
             const unsigned long long *scr = scratch + (jj & 1) * 4 * BN;
             const int tid = threadIdx.x, col = tt * BN + tid;
-            if (tid < BN && col < p.N3) {
+            if (tid < BN && col < p.N3 && tile_ok) {
                 if (PASS == 1) {
                     const float *sf = reinterpret_cast<const float *>(scr);
-                    p.colsum_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] = ((sf[tid] + sf[BN + tid]) + sf[2 * BN + tid]) + sf[3 * BN + tid];
+                    p.colsum_part[((long long)b * p.tiles_m + row_tile) * p.N3 + col] = ((sf[tid] + sf[BN + tid]) + sf[2 * BN + tid]) + sf[3 * BN + tid];
                 } else {
                     const uint32_t *su = reinterpret_cast<const uint32_t *>(scr);
                     uint32_t k = su[tid];
 #pragma unroll
                     for (int w = 1; w < 4; ++w) k = su[w * BN + tid] > k ? su[w * BN + tid] : k;
-                    p.colmax_part[((long long)b * gridDim.y + row_tile) * p.N3 + col] =
+                    p.colmax_part[((long long)b * p.tiles_m + row_tile) * p.N3 + col] =
                         ((unsigned long long)(k & 0xFFFFFF80u) << 32) | (unsigned long long)(0xffffffffu - (unsigned)(m0 + 127 - (int)(k & 127u)));
                 }
             }
@@ -222,7 +258,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
             tc::tmem_ld_wait();
             tc::tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
+            if (lane == 0) { if (CG == 2) tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&bar->acc_empty[as]), 0)); else tc::mbar_arrive(&bar->acc_empty[as]); }
             uint32_t tile_rk = 0u;
             float row_sum = 0.f;
 #pragma unroll
@@ -246,6 +282,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                     uint32_t ck = 0u;
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
+                        if (p.dbg & 16) continue;
                         const float4 l4 = *reinterpret_cast<const float4 *>(lgc + ccol + 4 * q);
                         const float l[4] = {l4.x, l4.y, l4.z, l4.w};
 #pragma unroll
@@ -305,11 +342,11 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         epi_bar_sync();
         fold_columns(t1 - 1, j - 1);
         if (PASS == 2 && lane == 0) tc::tma_store_wait_all();
-        if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * (gridDim.x * 2) + split * 2 + half) * p.N2 + row] = row_key;
+        if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * (gridDim.y * 2) + split * 2 + half) * p.N2 + row] = row_key;
     }
     tc::tcgen05_fence_before();
-    __syncthreads();
-    if (warp == 9) tc::tmem_dealloc<256>(tmem_base);
+    if (CG == 2) tc::cluster_sync(); else __syncthreads();                // nothing is in flight to or from the peer any more
+    if (warp == 9) { if (CG == 2) tc::tmem_dealloc_cg2<256>(tmem_base); else tc::tmem_dealloc<256>(tmem_base); }
 }
 
 // fp32 rows -> scaled fp16 hi / lo planes

@@ -41,3 +41,29 @@ run("two streams", two_streams=True)
 run("one stream", two_streams=False)
 run("two streams", two_streams=True)
 run("one stream", two_streams=False)
+
+# whole step as one CUDA graph (launch gaps removed): capture once, replay
+try:
+    m.two_streams = True
+    g = torch.cuda.CUDAGraph()
+    s_cap = torch.cuda.Stream()
+    s_cap.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s_cap):
+        m(data)
+    torch.cuda.current_stream().wait_stream(s_cap)
+    torch.cuda.synchronize()
+    with torch.cuda.graph(g):
+        out = m(data)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(steps):
+        g.replay()
+    e.record()
+    torch.cuda.synchronize()
+    print(f"{'CUDA graph replay':30s} {s.elapsed_time(e) / steps:8.3f} ms/step  {F * steps / s.elapsed_time(e) * 1e3:8.1f} frames/s", flush=True)
+    print("poses finite:", bool(torch.isfinite(out[0]["pose"]).all()), "inliers mean:", float(out[0]["n_inliers"].float().mean()))
+except Exception as ex:                                  # noqa: BLE001
+    print("graph capture failed:", type(ex).__name__, str(ex)[:300])
