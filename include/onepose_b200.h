@@ -185,6 +185,17 @@ int op_gather_matches(const int64_t *matches0, const float *scores0, const float
                       long long kp3_bstride, int B, int N2, int N3, double scale, double *out2d, double *out3d,
                       float *out_conf, int32_t *out_query_idx, int32_t *count, void *stream);
 
+/* ---- (3b) SURVEY.md 8(f): the data either side of the matcher -----------------------------------
+ * op_gather_rows: out[r,:] = src[idx[r],:] (rows of 256 fp32), or the all-ones dustbin descriptor where idx[r] < 0 -- the
+ *   leaf tensor of build_features3d_leaves (data_utils.py:163-205) directly in the matcher's point-major layout.
+ * op_segment_mean: out[i,:] = mean(src[offsets[i]:offsets[i+1],:]) in fp32, rows added in order
+ *   (mean_descriptors / mean_scores, feature_process.py:297-319).
+ * op_pose_errors: per frame translation error in cm and rotation error in degrees of [3,4] float64 poses, as
+ *   Evaluator.cm_degree_*_metric / query_pose_error (cmd_evaluator.py:11-33, eval_utils.py:45-63). */
+int op_gather_rows(const float *src, const int64_t *idx, long long n_src, long long n_out, float *out, void *stream);
+int op_segment_mean(const float *src, const int64_t *offsets, long long n_seg, int C, float *out, void *stream);
+int op_pose_errors(const double *pose_pred, const double *pose_gt, int F, double *t_err_cm, double *r_err_deg, void *stream);
+
 /* ---- (4) batched PnP-RANSAC: eval_utils.py:18-42 (cv2.solvePnPRansac, EPnP, 5 px, 10000 it) ---
  * Correspondences of frame f are rows [f*stride, f*stride + count[f]) of pts2d/pts3d (float64,
  * converted to float32 inside as cv2 does).  samples: [n_samples_sets, H, 5] int32 minimal-sample

@@ -38,6 +38,9 @@ _SIGS = {
     "op_norm_relu_split": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
     "op_gats_planes_parts": (i32, [i32]),
     "op_gats_leaf_aggregate_planes": (i32, [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp]),
+    "op_gather_rows": (i32, [vp, vp, i64, i64, vp, vp]),
+    "op_segment_mean": (i32, [vp, vp, i64, i32, vp, vp]),
+    "op_pose_errors": (i32, [vp, vp, i32, vp, vp, vp]),
     "op_linear_tc": (i32, [vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, f32, vp]),
     "op_linear_tc_stat_parts": (i32, [i32]),
     "op_colsum_partial": (i32, [vp, i32, i32, i32, vp, vp]),

@@ -212,9 +212,24 @@ class GATsSuperGlue(nn.Module):
     def _planes(self, name, shape, dev):
         return (self._ws.get(name + ".hi", shape, torch.float16, dev), self._ws.get(name + ".lo", shape, torch.float16, dev))
 
+    def register_static_db(self, descriptors3d_db, descriptors2d_db, avg_pm, leaves_pm, num_leaf):
+        """An object DB that already exists in the internal point-major layout (``onepose_b200.objectdb.ObjectDB``):
+        ``forward`` calls whose DB tensors are (batch-expanded views of) descriptors3d_db [256,N3] / descriptors2d_db
+        [256,N3*L] use avg_pm [N3,256] / leaves_pm [N3*L,256] directly."""
+        N3 = avg_pm.shape[0]
+        if leaves_pm.shape[0] != N3 * num_leaf or avg_pm.shape[1] != _D or leaves_pm.shape[1] != _D:
+            raise ValueError("register_static_db: inconsistent DB shapes")
+        entry = dict(d3=avg_pm[None].float().contiguous(), leaves=leaves_pm[None].float().contiguous(), shared=True, wh_leaf={},
+                     _src=(descriptors3d_db, descriptors2d_db))
+        self._db_cache["registered"] = ((descriptors3d_db.data_ptr(), descriptors2d_db.data_ptr(), N3, N3 * num_leaf), entry)
+
     def _static_db(self, d3, lv, L):
         """Point-major copy of the object DB, cached while the caller keeps handing the same tensors."""
         shared = d3.shape[0] == 1 or (d3.stride(0) == 0 and lv.stride(0) == 0)
+        reg = self._db_cache.get("registered")
+        if reg is not None and shared and reg[0] == (d3.data_ptr(), lv.data_ptr(), d3.shape[2], lv.shape[2]) \
+                and d3.stride(1) == 1 and lv.stride(1) == 1:
+            return reg[1]
         Bd = 1 if shared else d3.shape[0]
         key = (d3.data_ptr(), lv.data_ptr(), tuple(d3.shape), tuple(lv.shape), d3._version, lv._version, Bd)
         hit = self._db_cache.get("db")

@@ -11,6 +11,10 @@
 * pnp_*.npz      : outputs of the reference ``ransac_PnP`` (src/utils/eval_utils.py:18-42, i.e.
   cv2.solvePnPRansac of this image, cv2 4.13.0) on ``synth.make_pnp_problem`` inputs, plus
   per-sample ``cv2.solvePnP(EPNP)`` poses on all-inlier 5-point samples.
+* db_builder.npz : outputs of the reference's DB-side helpers (src/utils/data_utils.py:143-205 pad_features3d_random /
+  build_features3d_leaves under np.random.seed(5), src/sfm/postprocess/feature_process.py:297-319 mean_descriptors --
+  the module imports h5py, absent here, so the function's own source is exec'd unmodified), of
+  src/evaluators/cmd_evaluator.py Evaluator and of eval_utils.query_pose_error on ``oracle.objectdb_oracle.db_builder_inputs``.
 The reference has no tests or golden vectors of its own; these fixtures, made from
 the live reference, are what pins the oracle.
 """
@@ -117,6 +121,40 @@ def main():
         edge[f"pose_{n}"] = pose; edge[f"inl_{n}"] = np.asarray(inl).ravel()
         print("edge n=%d inliers=%d" % (n, len(inl)))
     np.savez_compressed(os.path.join(HERE, "pnp_edge.npz"), **edge)
+
+    # DB builder + evaluator
+    import ast
+    from src.utils import data_utils
+    from src.utils.eval_utils import query_pose_error
+    from src.evaluators.cmd_evaluator import Evaluator
+    from oracle.objectdb_oracle import db_builder_inputs
+    src_path = "/root/reference/src/sfm/postprocess/feature_process.py"
+    tree = ast.parse(open(src_path).read())
+    ns = {"np": np}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("mean_descriptors", "mean_scores"):
+            exec(compile(ast.Module([node], []), src_path, "exec"), ns)
+    inp = db_builder_inputs()
+    out = {}
+    out["avg"] = ns["mean_descriptors"](inp["desc"], inp["idxs"])
+    out["avg_scores"] = ns["mean_scores"](inp["scores"], inp["idxs"])
+    clt = inp["desc"].transpose(1, 0)                               # on-disk layout [256, n] (save_3d_anno)
+    for tag, n_target, num_leaf in (("pad", 14, 4), ("trunc", 9, 4), ("wide", 12, 16)):
+        np.random.seed(5)
+        d, s_ = data_utils.pad_features3d_random(out["avg"].transpose(1, 0), out["avg_scores"], n_target)
+        dl, sl = data_utils.build_features3d_leaves(clt, inp["scores"], inp["idxs"], n_target, num_leaf)
+        out[f"{tag}_avg"] = d.numpy(); out[f"{tag}_avg_scores"] = s_.numpy()
+        out[f"{tag}_leaves"] = dl.numpy(); out[f"{tag}_leaf_scores"] = sl.numpy()
+    ev = Evaluator()
+    errs = []
+    for p_, g_ in zip(inp["poses_pred"], inp["poses_gt"]):
+        ev.evaluate(p_, g_)
+        errs.append(query_pose_error(p_, g_))
+    with contextlib.redirect_stdout(io.StringIO()):
+        summ = ev.summarize()
+    out["pose_errs"] = np.asarray(errs); out["cmd"] = np.asarray([summ["cmd1"], summ["cmd3"], summ["cmd5"]])
+    np.savez_compressed(os.path.join(HERE, "db_builder.npz"), **out)
+    print("db_builder", {k: v.shape for k, v in out.items()})
 
 
 if __name__ == "__main__":
