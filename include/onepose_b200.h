@@ -196,6 +196,24 @@ int op_gather_rows(const float *src, const int64_t *idx, long long n_src, long l
 int op_segment_mean(const float *src, const int64_t *offsets, long long n_seg, int C, float *out, void *stream);
 int op_pose_errors(const double *pose_pred, const double *pose_gt, int F, double *t_err_cm, double *r_err_deg, void *stream);
 
+/* ---- (3c) SURVEY.md 8(f) row f3: SuperPoint's post-network stages (src/models/extractors/SuperPoint/superpoint.py) ---------
+ * op_sp_softmax_shuffle: logits [B,65,h,w] -> scores [B,8h,8w]: channel softmax, dustbin dropped, 8x8 depth-to-space (:207-211).
+ * op_sp_nms: simple_nms (:47-69), five fused max-pool stages; workspace = op_sp_nms_workspace_bytes(B,H,W) bytes.
+ * op_sp_select: score > threshold (torch.nonzero, row-major order), remove_borders (:72-83), top_k_keypoints (:86-93; sorted by
+ *   score descending, ties by position) and the (h,w)->(x,y) flip (:228).  kpts [B,out_stride,2] fp32, kscores [B,out_stride],
+ *   count [B] int32; overflow[b] != 0 reports an image with more than 16384 NMS survivors (not expected: maxima are > r apart).
+ *   out_stride >= max_keypoints (>= 16384 when max_keypoints < 0).
+ * op_sp_desc_prepare: dense descriptors [B,256,h*w] -> L2-normalised pixel-major [B,h*w,256] (:235-236).
+ * op_sp_sample: sample_descriptors (:96-113) at kpts -> [B,out_stride,256] point-major, L2-normalised; rows >= count[b] are 0. */
+int op_sp_softmax_shuffle(const float *logits, int B, int h, int w, float *scores, void *stream);
+size_t op_sp_nms_workspace_bytes(int B, int H, int W);
+int op_sp_nms(const float *scores, int B, int H, int W, int radius, float *out, void *workspace, size_t workspace_bytes, void *stream);
+int op_sp_select(const float *nms_scores, int B, int H, int W, float threshold, int border, int max_keypoints, int out_stride,
+                 float *kpts, float *kscores, int32_t *count, int32_t *overflow, void *stream);
+int op_sp_desc_prepare(const float *dense, int B, int hw, float *desc_pm, void *stream);
+int op_sp_sample(const float *desc_pm, const float *kpts, const int32_t *count, int B, int stride, int h, int w, int s,
+                 int align_corners, float *out_pm, void *stream);
+
 /* ---- (4) batched PnP-RANSAC: eval_utils.py:18-42 (cv2.solvePnPRansac, EPnP, 5 px, 10000 it) ---
  * Correspondences of frame f are rows [f*stride, f*stride + count[f]) of pts2d/pts3d (float64,
  * converted to float32 inside as cv2 does).  samples: [n_samples_sets, H, 5] int32 minimal-sample

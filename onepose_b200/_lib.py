@@ -41,6 +41,12 @@ _SIGS = {
     "op_gather_rows": (i32, [vp, vp, i64, i64, vp, vp]),
     "op_segment_mean": (i32, [vp, vp, i64, i32, vp, vp]),
     "op_pose_errors": (i32, [vp, vp, i32, vp, vp, vp]),
+    "op_sp_softmax_shuffle": (i32, [vp, i32, i32, i32, vp, vp]),
+    "op_sp_nms_workspace_bytes": (sz, [i32, i32, i32]),
+    "op_sp_nms": (i32, [vp, i32, i32, i32, i32, vp, vp, sz, vp]),
+    "op_sp_select": (i32, [vp, i32, i32, i32, f32, i32, i32, i32, vp, vp, vp, vp, vp]),
+    "op_sp_desc_prepare": (i32, [vp, i32, i32, vp, vp]),
+    "op_sp_sample": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "op_linear_tc": (i32, [vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, f32, vp]),
     "op_linear_tc_stat_parts": (i32, [i32]),
     "op_colsum_partial": (i32, [vp, i32, i32, i32, vp, vp]),
