@@ -197,7 +197,8 @@ int op_segment_mean(const float *src, const int64_t *offsets, long long n_seg, i
 int op_pose_errors(const double *pose_pred, const double *pose_gt, int F, double *t_err_cm, double *r_err_deg, void *stream);
 
 /* ---- (3c) SURVEY.md 8(f) row f3: SuperPoint's post-network stages (src/models/extractors/SuperPoint/superpoint.py) ---------
- * op_sp_softmax_shuffle: logits [B,65,h,w] -> scores [B,8h,8w]: channel softmax, dustbin dropped, 8x8 depth-to-space (:207-211).
+ * op_sp_softmax_shuffle: logits [B,65,h,w] (cell_stride = 0) or [B,h,w,cell_stride] (pixel-major, cell_stride >= 65) -> scores
+ *   [B,8h,8w]: channel softmax, dustbin dropped, 8x8 depth-to-space (:207-211).
  * op_sp_nms: simple_nms (:47-69), five fused max-pool stages; workspace = op_sp_nms_workspace_bytes(B,H,W) bytes.
  * op_sp_select: score > threshold (torch.nonzero, row-major order), remove_borders (:72-83), top_k_keypoints (:86-93; sorted by
  *   score descending, ties by position) and the (h,w)->(x,y) flip (:228).  kpts [B,out_stride,2] fp32, kscores [B,out_stride],
@@ -205,7 +206,7 @@ int op_pose_errors(const double *pose_pred, const double *pose_gt, int F, double
  *   out_stride >= max_keypoints (>= 16384 when max_keypoints < 0).
  * op_sp_desc_prepare: dense descriptors [B,256,h*w] -> L2-normalised pixel-major [B,h*w,256] (:235-236).
  * op_sp_sample: sample_descriptors (:96-113) at kpts -> [B,out_stride,256] point-major, L2-normalised; rows >= count[b] are 0. */
-int op_sp_softmax_shuffle(const float *logits, int B, int h, int w, float *scores, void *stream);
+int op_sp_softmax_shuffle(const float *logits, int B, int h, int w, int cell_stride, float *scores, void *stream);
 size_t op_sp_nms_workspace_bytes(int B, int H, int W);
 int op_sp_nms(const float *scores, int B, int H, int W, int radius, float *out, void *workspace, size_t workspace_bytes, void *stream);
 int op_sp_select(const float *nms_scores, int B, int H, int W, float threshold, int border, int max_keypoints, int out_stride,
@@ -213,6 +214,19 @@ int op_sp_select(const float *nms_scores, int B, int H, int W, float threshold, 
 int op_sp_desc_prepare(const float *dense, int B, int hw, float *desc_pm, void *stream);
 int op_sp_sample(const float *desc_pm, const float *kpts, const int32_t *count, int B, int stride, int h, int w, int s,
                  int align_corners, float *out_pm, void *stream);
+
+/* ---- (3d) row f3: SuperPoint's convolution stack (superpoint.py:147-166,177-206,231-234) on the tensor cores ------------------
+ * Activations are NHWC split-precision planes (hi, lo) of 64*x, as the matcher's streams (op_split_planes).
+ * op_conv_tc: 3x3/pad 1 (ntaps = 9) or 1x1 (ntaps = 1) convolution + bias (+ ReLU).  x planes [B,H,W,Cin] (Cin % 64 == 0);
+ *   weight planes [ntaps, Cout_pad, Cin] = 64 * weight[co, ci, ky, kx] at tap ky*3+kx, rows >= Cout zero, Cout_pad = 64 or a multiple
+ *   of 128 (<= 256); bias [Cout] fp32.  Outputs: planes yh/yl [B,H,W,Cout] (Cout % 32 == 0) and/or fp32 y32 [B,H,W,y32_stride]
+ *   (columns >= Cout of a row receive zeros up to the stride).  Three fp16 MMAs per product, fp32 accumulation in TMEM.
+ * op_conv1a_planes: the first layer, image [B,1,H,W] fp32 -> planes [B,H,W,64], weights [64,1,3,3], ReLU (fp32 CUDA cores, K = 9).
+ * op_pool2_planes: MaxPool2d(2,2) on planes [B,H,W,C] -> [B,H/2,W/2,C]. */
+int op_conv_tc(const void *xh, const void *xl, int B, int H, int W, int Cin, const void *wh, const void *wl, int Cout_pad,
+               const float *bias, int Cout, int ntaps, int relu, void *yh, void *yl, float *y32, int y32_stride, void *stream);
+int op_conv1a_planes(const float *img, const float *w, const float *bias, int B, int H, int W, void *yh, void *yl, void *stream);
+int op_pool2_planes(const void *xh, const void *xl, int B, int H, int W, int C, void *yh, void *yl, void *stream);
 
 /* ---- (4) batched PnP-RANSAC: eval_utils.py:18-42 (cv2.solvePnPRansac, EPnP, 5 px, 10000 it) ---
  * Correspondences of frame f are rows [f*stride, f*stride + count[f]) of pts2d/pts3d (float64,

@@ -41,7 +41,10 @@ _SIGS = {
     "op_gather_rows": (i32, [vp, vp, i64, i64, vp, vp]),
     "op_segment_mean": (i32, [vp, vp, i64, i32, vp, vp]),
     "op_pose_errors": (i32, [vp, vp, i32, vp, vp, vp]),
-    "op_sp_softmax_shuffle": (i32, [vp, i32, i32, i32, vp, vp]),
+    "op_sp_softmax_shuffle": (i32, [vp, i32, i32, i32, i32, vp, vp]),
+    "op_conv_tc": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp, i32, i32, i32, vp, vp, vp, i32, vp]),
+    "op_conv1a_planes": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp]),
+    "op_pool2_planes": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, vp]),
     "op_sp_nms_workspace_bytes": (sz, [i32, i32, i32]),
     "op_sp_nms": (i32, [vp, i32, i32, i32, i32, vp, vp, sz, vp]),
     "op_sp_select": (i32, [vp, i32, i32, i32, f32, i32, i32, i32, vp, vp, vp, vp, vp]),

@@ -13,15 +13,19 @@
 namespace opb {
 namespace sp {
 
-__global__ void k_sp_softmax_shuffle(const float *__restrict__ logits, int h, int w, float *__restrict__ scores) {
+// cell_stride == 0: logits are [B,65,h,w] (channel-major, the library convolution's layout);
+// cell_stride  > 0: logits are [B,h,w,cell_stride] (pixel-major, op_conv_tc's layout), 65 <= cell_stride
+__global__ void k_sp_softmax_shuffle(const float *__restrict__ logits, int h, int w, int cell_stride, float *__restrict__ scores) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
     if (x >= w) return;
     const long long plane = (long long)h * w;
-    const float *p = logits + (long long)b * 65 * plane + (long long)y * w + x;
+    const float *p = cell_stride ? logits + ((long long)b * plane + (long long)y * w + x) * cell_stride
+                                 : logits + (long long)b * 65 * plane + (long long)y * w + x;
+    const long long cs = cell_stride ? 1 : plane;
     float v[65];
     float m = -INFINITY;
 #pragma unroll
-    for (int c = 0; c < 65; ++c) { v[c] = p[c * plane]; m = fmaxf(m, v[c]); }
+    for (int c = 0; c < 65; ++c) { v[c] = p[c * cs]; m = fmaxf(m, v[c]); }
     float s = 0.f;
 #pragma unroll
     for (int c = 0; c < 65; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
@@ -216,9 +220,10 @@ k_sp_sample(const float *__restrict__ desc_pm, const float *__restrict__ kpts, c
 }  // namespace sp
 }  // namespace opb
 
-extern "C" int op_sp_softmax_shuffle(const float *logits, int B, int h, int w, float *scores, void *stream) {
+extern "C" int op_sp_softmax_shuffle(const float *logits, int B, int h, int w, int cell_stride, float *scores, void *stream) {
     OPB_CHECK_ARG(logits && scores && B > 0 && h > 0 && w > 0 && h <= 65535 && B <= 65535, "op_sp_softmax_shuffle: bad argument");
-    opb::sp::k_sp_softmax_shuffle<<<dim3(opb::ceil_div(w, 64), h, B), 64, 0, (cudaStream_t)stream>>>(logits, h, w, scores);
+    OPB_CHECK_ARG(cell_stride == 0 || cell_stride >= 65, "op_sp_softmax_shuffle: cell_stride=%d", cell_stride);
+    opb::sp::k_sp_softmax_shuffle<<<dim3(opb::ceil_div(w, 64), h, B), 64, 0, (cudaStream_t)stream>>>(logits, h, w, cell_stride, scores);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

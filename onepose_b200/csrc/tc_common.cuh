@@ -55,6 +55,13 @@ __device__ __forceinline__ void tma_load_3d(void *smem_dst, const CUtensorMap *m
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(void *smem_dst, const CUtensorMap *m, uint64_t *bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m, uint64_t *bar, int c0, int c1) {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
@@ -215,5 +222,8 @@ int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, in
 int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // same for fp16: box = {32 cols, box_rows, 1} (64-byte rows), 64-byte swizzle
 int make_tmap_f16_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// host: tensor map of an fp16 NHWC image batch [B, H, W, C], box = {64 channels, box_w pixels, box_h rows, 1}, 128-byte swizzle.
+// Coordinates may be negative or past the end: out-of-range pixels are zero-filled (the convolution's zero padding).
+int make_tmap_f16_nhwc(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h);
 
 }  // namespace opb

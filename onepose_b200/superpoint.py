@@ -6,8 +6,10 @@ names (a reference ``state_dict`` -- superpoint_v1.pth -- loads with ``strict=Tr
 
 What runs where:
 
-* the twelve convolutions are library work (cuDNN through ``torch.nn.functional.conv2d``, fp32 with TF32 switched off for
-  the call, so the dense maps agree with the reference's fp32 ones to rounding) -- plumbing, not the product;
+* the twelve convolutions run on the tensor cores at fp32-class accuracy (``csrc/conv_tc.cu``: tcgen05 implicit GEMMs over
+  NHWC split-precision fp16 planes, three MMAs per product, fp32 TMEM accumulation; the 1-channel first layer and the 2x2
+  max-pools are small CUDA-core kernels).  ``conv_impl='cudnn'`` (or env ``OPB_SP_CONV=cudnn``) runs them through the library
+  instead (fp32, TF32 off) -- kept as the measurement baseline and the parity cross-check, not as a fallback;
 * everything after them is this repo's CUDA (``csrc/superpoint.cu``): channel softmax + 8x8 depth-to-space, the five
   max-pool stages of ``simple_nms``, threshold + border removal + ordered compaction + top-k in one kernel per image,
   descriptor normalisation into a pixel-major map, bilinear sampling + L2 normalisation.  A whole batch of frames is
@@ -17,6 +19,8 @@ What runs where:
 ``forward_batched`` returns padded device tensors + counts (what ``GATsSuperGlue`` wants for a block of frames);
 ``forward`` cuts them into the reference's lists.  CUDA only; no CPU fallback.
 """
+import os
+
 import torch
 from torch import nn
 
@@ -34,7 +38,7 @@ class SuperPoint(nn.Module):
         'remove_borders': 4,
     }
 
-    def __init__(self, config, align_corners=True):
+    def __init__(self, config, align_corners=True, conv_impl=None):
         """``config`` as the reference's (superpoint.py:133-139; unknown keys are carried but ignored, which is how the
         'keypoints_threshold' key of extract_features.py:9-17 leaves the 0.005 default in force).  ``align_corners``: the
         reference picks grid_sample's align_corners from the torch version string (:106); True is what its pinned
@@ -42,6 +46,10 @@ class SuperPoint(nn.Module):
         super().__init__()
         self.config = {**self.default_config, **config}
         self.align_corners = bool(align_corners)
+        self.conv_impl = conv_impl or os.environ.get("OPB_SP_CONV", "tc")
+        if self.conv_impl not in ("tc", "cudnn"):
+            raise ValueError("conv_impl must be 'tc' or 'cudnn'")
+        self._packed = None
         c1, c2, c3, c4, c5 = 64, 64, 128, 128, 256
         self.relu = nn.ReLU(inplace=True)
         self.pool = nn.MaxPool2d(kernel_size=2, stride=2)
@@ -89,20 +97,98 @@ class SuperPoint(nn.Module):
             torch.backends.cudnn.allow_tf32 = tf32
         return logits, dense
 
+    # ------------------------------------------------------------------------------------------ network on the tensor cores
+    _TC_LAYERS = ("conv1b", "conv2a", "conv2b", "conv3a", "conv3b", "conv4a", "conv4b", "convPa", "convPb", "convDa", "convDb")
+
+    def _pack(self, dev):
+        """Weight planes [taps, Cout_pad, Cin] of 64*w (op_split_planes), cached until a parameter changes."""
+        key = (dev, tuple((p.data_ptr(), p._version) for p in self.parameters()))
+        if self._packed is not None and self._packed[0] == key:
+            return self._packed[1]
+        packed = {}
+        for name in self._TC_LAYERS:
+            conv = getattr(self, name)
+            w = conv.weight.detach().float()
+            co, ci, k, _ = w.shape
+            cp = 64 if co == 64 else -(-co // 128) * 128
+            wt = torch.zeros(k * k, cp, ci, dtype=torch.float32, device=dev)
+            wt[:, :co] = w.permute(2, 3, 0, 1).reshape(k * k, co, ci)
+            hi, lo = torch.empty_like(wt, dtype=torch.float16), torch.empty_like(wt, dtype=torch.float16)
+            call("op_split_planes", ptr(wt), ptr(hi), ptr(lo), wt.numel(), stream_ptr())
+            packed[name] = (hi, lo, conv.bias.detach().float().contiguous(), co, cp, ci, k * k)
+        packed["conv1a"] = (self.conv1a.weight.detach().float().reshape(64, 9).contiguous(), self.conv1a.bias.detach().float().contiguous())
+        self._packed = (key, packed)
+        return packed
+
+    @torch.no_grad()
+    def dense_maps_tc(self, inp):
+        """The network of ``dense_maps`` on this repo's kernels.  image [B,1,H,W] -> (detector logits [B,H/8,W/8,72] fp32,
+        pixel-major with columns 65..71 zero, descriptor map [B,H/8,W/8,256] fp32 pixel-major)."""
+        self._require_cuda(inp, "dense_maps_tc")
+        B, one, H, W = inp.shape
+        if one != 1 or H % 8 or W % 8:
+            raise ValueError("onepose_b200.SuperPoint: images must be [B,1,H,W] with H and W multiples of 8")
+        dev = inp.device
+        img = inp.float().contiguous()
+        f16 = dict(dtype=torch.float16, device=dev)
+
+        def planes(h, w, c):
+            return torch.empty(B, h, w, c, **f16), torch.empty(B, h, w, c, **f16)
+
+        with torch.cuda.device(dev):
+            pk = self._pack(dev)
+            st = stream_ptr()
+
+            def conv(name, x, h, w, relu=True, f32_stride=0):
+                hi, lo, bias, co, cp, ci, taps = pk[name]
+                if f32_stride:
+                    y32 = torch.empty(B, h, w, f32_stride, dtype=torch.float32, device=dev)
+                    call("op_conv_tc", ptr(x[0]), ptr(x[1]), B, h, w, ci, ptr(hi), ptr(lo), cp, ptr(bias), co, taps, int(relu), None, None,
+                         ptr(y32), f32_stride, st, tag=name)
+                    return y32
+                y = planes(h, w, co)
+                call("op_conv_tc", ptr(x[0]), ptr(x[1]), B, h, w, ci, ptr(hi), ptr(lo), cp, ptr(bias), co, taps, int(relu), ptr(y[0]), ptr(y[1]),
+                     None, 0, st, tag=name)
+                return y
+
+            def pool(x, h, w, c):
+                y = planes(h // 2, w // 2, c)
+                call("op_pool2_planes", ptr(x[0]), ptr(x[1]), B, h, w, c, ptr(y[0]), ptr(y[1]), st, tag="pool")
+                return y
+
+            x = planes(H, W, 64)
+            call("op_conv1a_planes", ptr(img), ptr(pk["conv1a"][0]), ptr(pk["conv1a"][1]), B, H, W, ptr(x[0]), ptr(x[1]), st, tag="conv1a")
+            x = conv("conv1b", x, H, W)
+            x = pool(x, H, W, 64); H, W = H // 2, W // 2
+            x = conv("conv2a", x, H, W)
+            x = conv("conv2b", x, H, W)
+            x = pool(x, H, W, 64); H, W = H // 2, W // 2
+            x = conv("conv3a", x, H, W)
+            x = conv("conv3b", x, H, W)
+            x = pool(x, H, W, 128); H, W = H // 2, W // 2
+            x = conv("conv4a", x, H, W)
+            x = conv("conv4b", x, H, W)
+            logits = conv("convPb", conv("convPa", x, H, W), H, W, relu=False, f32_stride=72)
+            dense = conv("convDb", conv("convDa", x, H, W), H, W, relu=False, f32_stride=256)
+        return logits, dense
+
     # ------------------------------------------------------------------------------------------ this repo's kernels
     @staticmethod
     def _require_cuda(t, what):
         if not t.is_cuda:
             raise RuntimeError("onepose_b200.SuperPoint.%s: CUDA tensors only (no CPU fallback)" % what)
 
-    def score_map(self, logits):
-        """:207-211 -- [B,65,h,w] -> [B,8h,8w]."""
+    def score_map(self, logits, pixel_major=False):
+        """:207-211 -- [B,65,h,w] (or pixel-major [B,h,w,stride]) -> [B,8h,8w]."""
         self._require_cuda(logits, "score_map")
         logits = logits.float().contiguous()
-        B, _, h, w = logits.shape
+        if pixel_major:
+            B, h, w, stride = logits.shape
+        else:
+            (B, _, h, w), stride = logits.shape, 0
         out = torch.empty(B, h * 8, w * 8, dtype=torch.float32, device=logits.device)
         with torch.cuda.device(logits.device):
-            call("op_sp_softmax_shuffle", ptr(logits), B, h, w, ptr(out), stream_ptr())
+            call("op_sp_softmax_shuffle", ptr(logits), B, h, w, stride, ptr(out), stream_ptr())
         return out
 
     def nms(self, scores, radius=None):
@@ -134,16 +220,24 @@ class SuperPoint(nn.Module):
                  mk, S, ptr(kpts), ptr(sc), ptr(count), ptr(self._overflow), stream_ptr())
         return kpts, sc, count
 
-    def sample(self, dense, kpts, count, s=8):
-        """:235-241 -> [B,S,256] point-major, L2-normalised (rows >= count are zero)."""
+    def sample(self, dense, kpts, count, s=8, pixel_major=False):
+        """:235-241 -> [B,S,256] point-major, L2-normalised (rows >= count are zero).  dense [B,256,h,w], or [B,h,w,256] with
+        ``pixel_major`` (normalised in place)."""
         self._require_cuda(dense, "sample")
         dense = dense.float().contiguous()
-        B, C, h, w = dense.shape
+        if pixel_major:
+            B, h, w, C = dense.shape
+        else:
+            B, C, h, w = dense.shape
         S = kpts.shape[1]
-        pm = torch.empty(B, h * w, C, dtype=torch.float32, device=dense.device)
         out = torch.empty(B, S, C, dtype=torch.float32, device=dense.device)
         with torch.cuda.device(dense.device):
-            call("op_sp_desc_prepare", ptr(dense), B, h * w, ptr(pm), stream_ptr())
+            if pixel_major:
+                pm = dense
+                call("op_l2_normalize_rows", ptr(pm), ptr(pm), B * h * w, C, stream_ptr())
+            else:
+                pm = torch.empty(B, h * w, C, dtype=torch.float32, device=dense.device)
+                call("op_sp_desc_prepare", ptr(dense), B, h * w, ptr(pm), stream_ptr())
             call("op_sp_sample", ptr(pm), ptr(kpts), ptr(count), B, S, h, w, s, int(self.align_corners), ptr(out), stream_ptr())
         return out
 
@@ -152,9 +246,10 @@ class SuperPoint(nn.Module):
         """image batch [B,1,H,W] (H, W multiples of 8) -> dict of padded device tensors: keypoints [B,S,2], scores [B,S],
         descriptors_pm [B,S,256] (point-major), count [B] int32.  No host synchronisation."""
         self._require_cuda(inp, "forward")
-        logits, dense = self.dense_maps(inp)
-        kpts, sc, count = self.select(self.nms(self.score_map(logits)))
-        desc = self.sample(dense, kpts, count)
+        tc = self.conv_impl == "tc"
+        logits, dense = self.dense_maps_tc(inp) if tc else self.dense_maps(inp)
+        kpts, sc, count = self.select(self.nms(self.score_map(logits, pixel_major=tc)))
+        desc = self.sample(dense, kpts, count, pixel_major=tc)
         return {"keypoints": kpts, "scores": sc, "descriptors_pm": desc, "count": count}
 
     @torch.no_grad()

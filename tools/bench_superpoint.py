@@ -45,11 +45,21 @@ def main():
     res = {"frames": B, "size": H}
     with torch.no_grad():
         t_net, (logits, dense) = timed(lambda: m.dense_maps(img), a.iters)
+        t_tc, (lg_tc, dn_tc) = timed(lambda: m.dense_maps_tc(img), a.iters)
+        res["conv_stack_tc_ms"] = round(t_tc, 3)
         t_sm, scores = timed(lambda: m.score_map(logits), a.iters)
         t_nms, nms = timed(lambda: m.nms(scores), a.iters)
         t_sel, (k, s, c) = timed(lambda: m.select(nms), a.iters)
         t_smp, d = timed(lambda: m.sample(dense, k, c), a.iters)
         t_all, _ = timed(lambda: m.forward_batched(img), a.iters)
+        from onepose_b200._lib import timeline
+        timeline.enabled = True; timeline.records = []
+        m.dense_maps_tc(img); torch.cuda.synchronize()
+        timeline.enabled = False
+        layers = {}
+        for name, tag, s0, e0, _ in timeline.records:
+            layers[tag or name] = round(layers.get(tag or name, 0.0) + s0.elapsed_time(e0), 4)
+        res["conv_tc_layers_ms"] = layers
     px = B * H * H
     stages = {
         "conv_stack(cuDNN)": (t_net, None),
