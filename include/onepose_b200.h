@@ -221,10 +221,11 @@ int op_sp_sample(const float *desc_pm, const float *kpts, const int32_t *count, 
  *   weight planes [ntaps, Cout_pad, Cin] = 64 * weight[co, ci, ky, kx] at tap ky*3+kx, rows >= Cout zero, Cout_pad = 64 or a multiple
  *   of 128 (<= 256); bias [Cout] fp32.  Outputs: planes yh/yl [B,H,W,Cout] (Cout % 32 == 0) and/or fp32 y32 [B,H,W,y32_stride]
  *   (columns >= Cout of a row receive zeros up to the stride).  Three fp16 MMAs per product, fp32 accumulation in TMEM.
+ *   pool = 1 (3x3, plane output, W % 8 == 0, even H): MaxPool2d(2,2) is applied in the epilogue, yh/yl are [B,H/2,W/2,Cout].
  * op_conv1a_planes: the first layer, image [B,1,H,W] fp32 -> planes [B,H,W,64], weights [64,1,3,3], ReLU (fp32 CUDA cores, K = 9).
  * op_pool2_planes: MaxPool2d(2,2) on planes [B,H,W,C] -> [B,H/2,W/2,C]. */
 int op_conv_tc(const void *xh, const void *xl, int B, int H, int W, int Cin, const void *wh, const void *wl, int Cout_pad,
-               const float *bias, int Cout, int ntaps, int relu, void *yh, void *yl, float *y32, int y32_stride, void *stream);
+               const float *bias, int Cout, int ntaps, int relu, int pool, void *yh, void *yl, float *y32, int y32_stride, void *stream);
 int op_conv1a_planes(const float *img, const float *w, const float *bias, int B, int H, int W, void *yh, void *yl, void *stream);
 int op_pool2_planes(const void *xh, const void *xl, int B, int H, int W, int C, void *yh, void *yl, void *stream);
 

@@ -42,7 +42,7 @@ _SIGS = {
     "op_segment_mean": (i32, [vp, vp, i64, i32, vp, vp]),
     "op_pose_errors": (i32, [vp, vp, i32, vp, vp, vp]),
     "op_sp_softmax_shuffle": (i32, [vp, i32, i32, i32, i32, vp, vp]),
-    "op_conv_tc": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp, i32, i32, i32, vp, vp, vp, i32, vp]),
+    "op_conv_tc": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp, vp, vp, i32, vp]),
     "op_conv1a_planes": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp]),
     "op_pool2_planes": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, vp]),
     "op_sp_nms_workspace_bytes": (sz, [i32, i32, i32]),

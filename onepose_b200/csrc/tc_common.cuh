@@ -76,6 +76,11 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap *m, const void *s
                  "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap *m, const void *smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
@@ -225,5 +230,7 @@ int make_tmap_f16_3d_store(CUtensorMap *map, const void *base, int batch, int ro
 // host: tensor map of an fp16 NHWC image batch [B, H, W, C], box = {64 channels, box_w pixels, box_h rows, 1}, 128-byte swizzle.
 // Coordinates may be negative or past the end: out-of-range pixels are zero-filled (the convolution's zero padding).
 int make_tmap_f16_nhwc(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h);
+// same array for TMA stores: box = {32 channels, box_w, box_h, 1} (64-byte rows), 64-byte swizzle; pixels past the end are clipped
+int make_tmap_f16_nhwc_store(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h);
 
 }  // namespace opb

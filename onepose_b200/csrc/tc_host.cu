@@ -54,21 +54,29 @@ int make_tmap_f16_3d_store(CUtensorMap *map, const void *base, int batch, int ro
     return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, batch, rows, cols, 32, box_rows, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
-int make_tmap_f16_nhwc(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h) {
+static int encode_nhwc(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_c, int box_w, int box_h, CUtensorMapSwizzle swz) {
     encode_fn encode = get_encoder();
     if (!encode) return OPB_ERR_CUDA;
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
     cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+    cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void *>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled (NHWC) failed: CUresult %d (B=%d H=%d W=%d C=%d box %dx%d)", (int)r, B, H, W, C, box_w, box_h);
         return OPB_ERR_CUDA;
     }
     return OPB_OK;
+}
+
+int make_tmap_f16_nhwc(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h) {
+    return encode_nhwc(map, base, B, H, W, C, 64, box_w, box_h, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int make_tmap_f16_nhwc_store(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h) {
+    return encode_nhwc(map, base, B, H, W, C, 32, box_w, box_h, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
 }  // namespace opb

@@ -139,16 +139,16 @@ class SuperPoint(nn.Module):
             pk = self._pack(dev)
             st = stream_ptr()
 
-            def conv(name, x, h, w, relu=True, f32_stride=0):
+            def conv(name, x, h, w, relu=True, f32_stride=0, pool=False):
                 hi, lo, bias, co, cp, ci, taps = pk[name]
                 if f32_stride:
                     y32 = torch.empty(B, h, w, f32_stride, dtype=torch.float32, device=dev)
-                    call("op_conv_tc", ptr(x[0]), ptr(x[1]), B, h, w, ci, ptr(hi), ptr(lo), cp, ptr(bias), co, taps, int(relu), None, None,
+                    call("op_conv_tc", ptr(x[0]), ptr(x[1]), B, h, w, ci, ptr(hi), ptr(lo), cp, ptr(bias), co, taps, int(relu), 0, None, None,
                          ptr(y32), f32_stride, st, tag=name)
                     return y32
-                y = planes(h, w, co)
-                call("op_conv_tc", ptr(x[0]), ptr(x[1]), B, h, w, ci, ptr(hi), ptr(lo), cp, ptr(bias), co, taps, int(relu), ptr(y[0]), ptr(y[1]),
-                     None, 0, st, tag=name)
+                y = planes(h // 2, w // 2, co) if pool else planes(h, w, co)
+                call("op_conv_tc", ptr(x[0]), ptr(x[1]), B, h, w, ci, ptr(hi), ptr(lo), cp, ptr(bias), co, taps, int(relu), int(pool), ptr(y[0]),
+                     ptr(y[1]), None, 0, st, tag=name)
                 return y
 
             def pool(x, h, w, c):
@@ -158,14 +158,16 @@ class SuperPoint(nn.Module):
 
             x = planes(H, W, 64)
             call("op_conv1a_planes", ptr(img), ptr(pk["conv1a"][0]), ptr(pk["conv1a"][1]), B, H, W, ptr(x[0]), ptr(x[1]), st, tag="conv1a")
-            x = conv("conv1b", x, H, W)
-            x = pool(x, H, W, 64); H, W = H // 2, W // 2
+            fused = os.environ.get("OPB_CONV_HALO", "1") != "0"        # MaxPool2d(2,2) inside the convolution's epilogue
+
+            def conv_pool(name, x, h, w, c):
+                return conv(name, x, h, w, pool=True) if fused else pool(conv(name, x, h, w), h, w, c)
+
+            x = conv_pool("conv1b", x, H, W, 64); H, W = H // 2, W // 2
             x = conv("conv2a", x, H, W)
-            x = conv("conv2b", x, H, W)
-            x = pool(x, H, W, 64); H, W = H // 2, W // 2
+            x = conv_pool("conv2b", x, H, W, 64); H, W = H // 2, W // 2
             x = conv("conv3a", x, H, W)
-            x = conv("conv3b", x, H, W)
-            x = pool(x, H, W, 128); H, W = H // 2, W // 2
+            x = conv_pool("conv3b", x, H, W, 128); H, W = H // 2, W // 2
             x = conv("conv4a", x, H, W)
             x = conv("conv4b", x, H, W)
             logits = conv("convPb", conv("convPa", x, H, W), H, W, relu=False, f32_stride=72)

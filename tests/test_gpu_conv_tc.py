@@ -23,7 +23,7 @@ def _unplanes(hi, lo):
     return ((hi.float() + lo.float()) / 64.0).permute(0, 3, 1, 2)
 
 
-def _conv_tc(x, w, bias, relu, f32_stride=0):
+def _conv_tc(x, w, bias, relu, f32_stride=0, pool=False):
     from onepose_b200._lib import call, ptr, stream_ptr
     B, ci, H, W = x.shape
     co, _, k, _ = w.shape
@@ -35,34 +35,48 @@ def _conv_tc(x, w, bias, relu, f32_stride=0):
     xh, xl = _planes(x)
     if f32_stride:
         y = torch.full((B, H, W, f32_stride), float("nan"), device="cuda")
-        call("op_conv_tc", ptr(xh), ptr(xl), B, H, W, ci, ptr(wh), ptr(wl), cp, ptr(bias), co, k * k, int(relu), None, None, ptr(y), f32_stride, stream_ptr())
+        call("op_conv_tc", ptr(xh), ptr(xl), B, H, W, ci, ptr(wh), ptr(wl), cp, ptr(bias), co, k * k, int(relu), 0, None, None, ptr(y), f32_stride, stream_ptr())
         return y.permute(0, 3, 1, 2)
-    yh = torch.full((B, H, W, co), float("nan"), dtype=torch.float16, device="cuda")
+    Ho, Wo = (H // 2, W // 2) if pool else (H, W)
+    yh = torch.full((B, Ho, Wo, co), float("nan"), dtype=torch.float16, device="cuda")
     yl = torch.full_like(yh, float("nan"))
-    call("op_conv_tc", ptr(xh), ptr(xl), B, H, W, ci, ptr(wh), ptr(wl), cp, ptr(bias), co, k * k, int(relu), ptr(yh), ptr(yl), None, 0, stream_ptr())
+    call("op_conv_tc", ptr(xh), ptr(xl), B, H, W, ci, ptr(wh), ptr(wl), cp, ptr(bias), co, k * k, int(relu), int(pool), ptr(yh), ptr(yl), None, 0,
+         stream_ptr())
     return _unplanes(yh, yl)
 
 
-@pytest.mark.parametrize("B,H,W,ci,co,k,relu,f32", [
-    (2, 16, 128, 64, 64, 3, True, 0),        # one 128-pixel row per tile
-    (1, 9, 256, 64, 64, 3, True, 0),
-    (2, 24, 80, 64, 128, 3, True, 0),        # 64 x 2 tiles, ragged in x
-    (1, 13, 64, 128, 128, 3, True, 0),       # ragged in y
-    (2, 8, 12, 128, 256, 3, True, 0),        # image narrower than a tile
-    (1, 40, 40, 128, 128, 3, False, 0),      # 32 x 4 tiles, no ReLU
-    (2, 16, 64, 256, 65, 1, False, 72),      # detector head's 1x1, fp32 out, padded channel count
-    (1, 8, 32, 256, 256, 1, False, 256),     # descriptor head's 1x1
-    (1, 64, 64, 128, 256, 3, True, 0),
+@pytest.mark.parametrize("B,H,W,ci,co,k,relu,f32,pool", [
+    # W % 8 == 0 and 3x3: the halo kernel (8 x 16 pixel tiles)
+    (2, 16, 128, 64, 64, 3, True, 0, False),
+    (1, 9, 256, 64, 64, 3, True, 0, False),       # ragged in y
+    (2, 24, 80, 64, 128, 3, True, 0, False),
+    (1, 13, 64, 128, 128, 3, True, 0, False),
+    (1, 40, 40, 128, 128, 3, False, 0, False),    # no ReLU
+    (1, 64, 64, 128, 256, 3, True, 0, False),     # two channel tiles
+    (2, 32, 64, 64, 64, 3, True, 0, True),        # fused 2x2 max-pool
+    (1, 22, 40, 64, 128, 3, True, 0, True),       # pooled, ragged in y
+    (1, 16, 16, 128, 128, 3, True, 0, True),
+    (3, 48, 8, 64, 64, 3, True, 0, False),        # a single tile column
+    # everything else: the tap-by-tap kernel (128-pixel row tiles)
+    (2, 8, 12, 128, 256, 3, True, 0, False),      # image narrower than a tile
+    (1, 20, 100, 64, 64, 3, True, 0, False),      # 64 x 2 tiles, ragged in x
+    (1, 5, 300, 64, 64, 3, False, 0, False),      # 128 x 1 tiles, ragged in x
+    (1, 12, 36, 128, 128, 3, True, 0, False),     # 32 x 4 tiles
+    (2, 16, 64, 256, 65, 1, False, 72, False),    # detector head's 1x1, fp32 out, padded channel count
+    (1, 8, 32, 256, 256, 1, False, 256, False),   # descriptor head's 1x1
+    (1, 7, 130, 64, 64, 1, True, 0, False),       # 1x1 with plane output
 ])
-def test_conv_tc_vs_fp64(B, H, W, ci, co, k, relu, f32):
+def test_conv_tc_vs_fp64(B, H, W, ci, co, k, relu, f32, pool):
     g = torch.Generator(device="cuda").manual_seed(H * 1000 + W + ci)
     x = torch.relu(torch.randn(B, ci, H, W, device="cuda", generator=g)) * 3.0
     w = torch.randn(co, ci, k, k, device="cuda", generator=g) / (ci * k * k) ** 0.5
     bias = torch.randn(co, device="cuda", generator=g)
-    got = _conv_tc(x, w, bias, relu, f32)
+    got = _conv_tc(x, w, bias, relu, f32, pool)
     xq = _unplanes(*_planes(x))                                      # the planes' value of x (2^-22 relative from x)
     ref = torch.nn.functional.conv2d(xq.double(), w.double(), bias.double(), padding=k // 2)
     ref = torch.relu(ref) if relu else ref
+    ref = torch.nn.functional.max_pool2d(ref, 2, 2) if pool else ref
+    assert got.shape[2:] == ref.shape[2:]
     assert torch.isfinite(got[:, :co]).all()
     err = (got[:, :co].double() - ref).abs().max().item()
     # fp32 TMEM accumulation over up to 9 * Cin / 16 * 3 chained MMAs (the tensor core truncates when it aligns addends): a few 1e-6 of

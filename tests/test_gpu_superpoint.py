@@ -161,13 +161,14 @@ def test_forward_batched_equals_per_image_and_properties():
     conf = {'nms_radius': 3, 'max_keypoints': 512, 'keypoint_threshold': 0.005, 'remove_borders': 4}
     m = _model(conf)
     imgs = torch.from_numpy(np.concatenate([spo.sp_image(s, 128, 160) for s in (1, 2, 3)])).cuda()
-    out = m.forward_batched(imgs)
-    assert out["keypoints"].shape == (3, 512, 2) and out["descriptors_pm"].shape == (3, 512, 256)
-    logits, dense = m.dense_maps(imgs)             # cuDNN may pick another algorithm for B=1: compare on the same maps
+    full = m.forward_batched(imgs)
+    assert full["keypoints"].shape == (3, 512, 2) and full["descriptors_pm"].shape == (3, 512, 256)
+    logits, dense = m.dense_maps(imgs)             # batch and single-image runs are compared on the same maps
 
     def post(lg, dn):
         k, s, c = m.select(m.nms(m.score_map(lg)))
         return {"keypoints": k, "scores": s, "count": c, "descriptors_pm": m.sample(dn, k, c)}
+    out = post(logits, dense)
     for b in range(3):
         one = post(logits[b:b + 1], dense[b:b + 1])
         n = int(out["count"][b])
