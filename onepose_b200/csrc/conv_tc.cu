@@ -41,6 +41,7 @@ struct Params {
     int y32_stride;
     const float *bias;
     int has_planes, has_f32;
+    int dbg;                       // experiment switches (env OPB_CONV_DBG; timing only, results are garbage): 1 = no loads, 2 = only the hi*hi MMA, 4 = no stores, 8 = no epilogue arithmetic or stores
 };
 
 struct Barriers {
@@ -243,7 +244,12 @@ struct HaloCfg {
     static constexpr int NA = BN == 64 ? 3 : 2;
     static constexpr int NW = BN == 64 ? 5 : 3;
     static constexpr int SMEM_BYTES = NA * A_BUF + NW * W_BUF + STG_BYTES + BIAS_FLOATS * 4 + 256;
-    static constexpr int TMEM_COLS = 2 * BN;
+    // BN = 64: an M128 x N64 x K16 MMA occupies the tensor pipe as long as an N128 one (measured ~65-90 clk: the 4 KB A operand is the
+    // cost), so Ah*Wh and Ah*Wl are issued as ONE N = 128 MMA against the adjacent [Wh; Wl] rows of the weight buffer: two MMAs per
+    // k-step instead of three, accumulator = 128 columns (hi*hi + lo*hi | hi*lo), added in the epilogue.
+    static constexpr bool WIDE = BN == 64;
+    static constexpr int ACC_COLS = WIDE ? 2 * BN : BN;
+    static constexpr int TMEM_COLS = 2 * ACC_COLS;
 };
 
 struct HaloBarriers {
@@ -291,7 +297,7 @@ k_conv_halo(const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ C
 
     if (warp == 8) {
         // ================= TMA producer: A(kx, kb) then its three weight taps, in the order the MMA warp consumes them =================
-        if (lane == 0) {
+        if (lane == 0 && !(p.dbg & 1)) {
             uint32_t ia = 0, iw = 0;
             for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
                 int b, y0, x0, ct; decode(t, b, y0, x0, ct);
@@ -321,7 +327,7 @@ k_conv_halo(const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ C
     } else if (warp == 9) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN);
+            constexpr uint32_t idesc = tc::umma_idesc_f16(BM, BN), idesc_wide = tc::umma_idesc_f16(BM, 2 * BN);
             const uint32_t a_base = tc::smem_u32(s_a), w_base = tc::smem_u32(s_w);
             uint32_t ia = 0, iw = 0;
             int j = 0;
@@ -329,23 +335,32 @@ k_conv_halo(const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ C
                 const uint32_t as = j & 1, aph = (j >> 1) & 1;
                 tc::mbar_wait(&bar->acc_empty[as], aph ^ 1);
                 tc::tcgen05_fence_after();
-                const uint32_t d = tmem_base + as * BN;
+                const uint32_t d = tmem_base + as * C::ACC_COLS;
                 uint32_t first = 0;                                      // 0 until the tile's first MMA has been issued
                 for (int kk = 0; kk < 3 * nkb; ++kk, ++ia) {
                     const uint32_t sa = ia % NA, pha = (ia / NA) & 1;
-                    tc::mbar_wait(&bar->a_full[sa], pha);
+                    if (!(p.dbg & 1)) tc::mbar_wait(&bar->a_full[sa], pha);
                     tc::tcgen05_fence_after();
                     for (int ky = 0; ky < 3; ++ky, ++iw) {
                         const uint32_t sw = iw % NW, phw = (iw / NW) & 1;
                         const uint32_t ab = a_base + sa * A_BUF + ky * 1024, wb = w_base + sw * W_BUF;
                         const uint64_t ah = tc::umma_desc_k128(ab), al = tc::umma_desc_k128(ab + A_HALF);
                         const uint64_t wh = tc::umma_desc_k128(wb), wl = tc::umma_desc_k128(wb + W_HALF);
-                        tc::mbar_wait(&bar->w_full[sw], phw);
+                        if (!(p.dbg & 1)) tc::mbar_wait(&bar->w_full[sw], phw);
                         tc::tcgen05_fence_after();
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
+                            if (p.dbg & 16) continue;
+                            if (C::WIDE) {
+                                tc::umma_f16(d, ah + 2 * k, wh + 2 * k, idesc_wide, first);     // Ah * [Wh; Wl] -> columns 0..63 | 64..127
+                                first = 1;
+                                if (p.dbg & 2) continue;
+                                tc::umma_f16(d, al + 2 * k, wh + 2 * k, idesc, 1);              // Al * Wh -> columns 0..63
+                                continue;
+                            }
                             tc::umma_f16(d, ah + 2 * k, wh + 2 * k, idesc, first);
                             first = 1;
+                            if (p.dbg & 2) continue;
                             tc::umma_f16(d, al + 2 * k, wh + 2 * k, idesc, 1);
                             tc::umma_f16(d, ah + 2 * k, wl + 2 * k, idesc, 1);
                         }
@@ -364,6 +379,7 @@ k_conv_halo(const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ C
         uint32_t nst = 0;
         // staging row r holds 64 bytes of one pixel; the TMA box is {32 channels, 8 px, 4 rows} (or {32, 4, 2} pooled)
         auto stage_store = [&](const CUtensorMap *tm, int col, const uint4 *data, bool writer, int r, int x, int y, int b) {
+            if (p.dbg & 4) return;
             uint8_t *buf = s_stg + (warp * 2 + (nst & 1)) * STG_BUF;
             if (lane == 0) tc::tma_store_wait_read1();
             __syncwarp();
@@ -388,14 +404,24 @@ k_conv_halo(const __grid_constant__ CUtensorMap tm_xh, const __grid_constant__ C
                 const int ccol = half * (BN / 2) + ch * 32;
                 const int c0 = ct * BN + ccol;
                 float v[32];
-                tc::tmem_ld_32x32(lane_base + as * BN + ccol, v);
-                tc::tmem_ld_wait();
+                if (!(p.dbg & 32)) {
+                    tc::tmem_ld_32x32(lane_base + as * C::ACC_COLS + ccol, v);
+                    if (C::WIDE) {
+                        float u[32];
+                        tc::tmem_ld_32x32(lane_base + as * C::ACC_COLS + BN + ccol, u);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] += u[i];
+                    } else {
+                        tc::tmem_ld_wait();
+                    }
+                }
                 if (ch == CHUNKS - 1) {
                     tc::tcgen05_fence_before();
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive(&bar->acc_empty[as]);
                 }
-                if (c0 >= p.Cout || y0 + 4 * quad >= p.H) continue;            // padding channels / rows below the image (warp-uniform)
+                if (c0 >= p.Cout || y0 + 4 * quad >= p.H || (p.dbg & 8)) continue;            // padding channels / rows below the image (warp-uniform)
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
                     const float4 bq = *reinterpret_cast<const float4 *>(s_bias + c0 + 4 * q);
@@ -569,6 +595,8 @@ extern "C" int op_conv_tc(const void *xh, const void *xl, int B, int H, int W, i
     p.B = B; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout; p.ntaps = ntaps; p.relu = relu;
     p.bias = bias;
     static const int use_halo = [] { const char *e = getenv("OPB_CONV_HALO"); return e ? atoi(e) : 1; }();
+    static const int dbg = [] { const char *e = getenv("OPB_CONV_DBG"); return e ? atoi(e) : 0; }();
+    p.dbg = dbg;
     const bool halo = use_halo && ntaps == 9 && yh && yl && !y32 && W % 8 == 0;
     OPB_CHECK_ARG(!pool || (halo && H % 2 == 0), "op_conv_tc: the fused 2x2 max-pool needs a 3x3 convolution with plane output, W %% 8 == 0 and even H");
     if (halo) {
