@@ -229,6 +229,30 @@ int op_conv_tc(const void *xh, const void *xl, int B, int H, int W, int Cin, con
 int op_conv1a_planes(const float *img, const float *w, const float *bias, int B, int H, int W, void *yh, void *yl, void *stream);
 int op_pool2_planes(const void *xh, const void *xl, int B, int H, int W, int C, void *yh, void *yl, void *stream);
 
+/* ---- (3e) SURVEY.md 8(f) row f4: tracker-side geometry (src/tracker/ba_tracker.py, tracking_utils.py), float64 ----------------
+ * op_snavely_residual: SnavelyReprojectionErrorV2 + AngleAxisRotatePoint (tracking_utils.py:91-169).  points [.,3], cams [.,6]
+ *   (angle-axis, translation), features [n,5] = (x, y, focal, l1, l2); observation i uses points[pt_idx[i]] / cams[cam_idx[i]]
+ *   (NULL index = i, the reference's already-gathered form); residual [n,2].
+ * op_project_points: `project` (tracking_utils.py:74-89): xy [n,2] (+ depth [n]); with ref2d [n,2], dist_sum receives the sum of
+ *   |xy - ref2d| (flow_track's kpt_dist is dist_sum / n, ba_tracker.py:318-319).  K [3,3], RT [3,4] row-major, device memory.
+ * op_triangulate_points: apply_triangulation (ba_tracker.py:267-273, cv2.triangulatePoints; DLT rows as :255-259): P1, P2 [3,4]
+ *   projection matrices, x1, x2 [n,2] -> X [n,3] de-homogenised.
+ * op_ba_lm: apply_ba (ba_tracker.py:358-441) -- windowed bundle adjustment on the Snavely residual.  The reference calls DeepLM's
+ *   Solve (third-party, absent); this is Levenberg-Marquardt with analytic Jacobians, Schur complement on the points, dense Cholesky
+ *   of the reduced camera system, accept / reject and damping (x0.1 / x10, Marquardt diagonal scaling) decided on the device.
+ *   cams [C,6] and points [P,3] are updated in place; cam_idx / pt_idx [O] int32; observations grouped by point: ids
+ *   pt_obs[pt_off[p] .. pt_off[p+1]).  Stops after num_iterations trials or num_success_iterations accepted steps.  state_out
+ *   (device, 8 doubles, may be NULL): lambda, cost, candidate cost, accepted steps, done, last accepted, iterations, initial cost. */
+int op_snavely_residual(const double *points, const double *cams, const double *features, const int64_t *pt_idx, const int64_t *cam_idx,
+                        long long n, double *residual, void *stream);
+int op_project_points(const double *xyz, const double *K, const double *RT, long long n, const double *ref2d, double *xy, double *depth,
+                      double *dist_sum, void *stream);
+int op_triangulate_points(const double *P1, const double *P2, const double *x1, const double *x2, long long n, double *X, void *stream);
+size_t op_ba_workspace_bytes(int C, int P, int O);
+int op_ba_lm(double *cams, double *points, const double *features, const int32_t *cam_idx, const int32_t *pt_idx, const int32_t *pt_off,
+             const int32_t *pt_obs, int C, int P, int O, int num_iterations, int num_success_iterations, double lambda0, void *workspace,
+             size_t workspace_bytes, double *state_out, void *stream);
+
 /* ---- (4) batched PnP-RANSAC: eval_utils.py:18-42 (cv2.solvePnPRansac, EPnP, 5 px, 10000 it) ---
  * Correspondences of frame f are rows [f*stride, f*stride + count[f]) of pts2d/pts3d (float64,
  * converted to float32 inside as cv2 does).  samples: [n_samples_sets, H, 5] int32 minimal-sample

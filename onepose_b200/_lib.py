@@ -44,6 +44,11 @@ _SIGS = {
     "op_sp_softmax_shuffle": (i32, [vp, i32, i32, i32, i32, vp, vp]),
     "op_conv_tc": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp, i32, i32, i32, i32, vp, vp, vp, i32, vp]),
     "op_conv1a_planes": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp]),
+    "op_snavely_residual": (i32, [vp, vp, vp, vp, vp, i64, vp, vp]),
+    "op_project_points": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, vp]),
+    "op_triangulate_points": (i32, [vp, vp, vp, vp, i64, vp, vp]),
+    "op_ba_workspace_bytes": (sz, [i32, i32, i32]),
+    "op_ba_lm": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f64, vp, sz, vp, vp]),
     "op_pool2_planes": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, vp]),
     "op_sp_nms_workspace_bytes": (sz, [i32, i32, i32]),
     "op_sp_nms": (i32, [vp, i32, i32, i32, i32, vp, vp, sz, vp]),
