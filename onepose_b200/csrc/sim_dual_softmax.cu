@@ -296,19 +296,20 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         OPB_CHECK_LAUNCH();
         CUtensorMap t2h, t2l, t3h, t3l, tconf;
         int rc;
-        // One CTA per row tile by default; OPB_SIM_CG=2 selects the CTA-pair (cta_group::2) form of the same kernel.  Measured at the
-        // headline shape (64 frames): pair 1.30 + 1.97 ms, single 1.26 + 1.87 ms -- the pair halves the L2 -> SM stream of B per CTA
-        // but its 8 KB ring units double the per-unit round trip, so it does not win here.
-        static const int cg = [] { const char *e = getenv("OPB_SIM_CG"); return (e && e[0] == '2') ? 2 : 1; }();
+        // CTA pairs (cta_group::2, M256 x N256 tiles) by default: each CTA keeps its 128 query rows resident and stages half of every
+        // B k-block, which halves the L2 -> SM stream that bounds the one-CTA form.  Measured at the headline shape (64 frames):
+        // pair 1.02 + 1.48 ms, single (OPB_SIM_CG=1, M128 x N128) 1.27 + 1.74 ms.
+        static const int cg = [] { const char *e = getenv("OPB_SIM_CG"); return (e && e[0] == '1') ? 1 : 2; }();
         if ((rc = make_tmap_f16_3d(&t2h, w.m2h, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) ||
-            (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, simtc::BN / cg)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, simtc::BN / cg)))
+            (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, 128)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, 128)))
             return rc;
+        const int tiles_n = ceil_div(N3, 128 * cg);          // column tiles of the tensor-core passes: 128 wide, 256 for a CTA pair
         // enough CTAs for ~2 waves over 148 SMs: split the column tiles when frames x row tiles is small
         int splits = ceil_div(2 * 148, (long long)B * p.tiles_m);
-        splits = splits < 1 ? 1 : (splits > p.tiles_n ? p.tiles_n : splits);
+        splits = splits < 1 ? 1 : (splits > tiles_n ? tiles_n : splits);
         simtc::Params q{};
-        q.N2 = N2; q.N3 = N3; q.tiles_n = p.tiles_n; q.tiles_m = p.tiles_m; q.tiles_per_split = ceil_div(p.tiles_n, splits);
-        splits = ceil_div(p.tiles_n, q.tiles_per_split);
+        q.N2 = N2; q.N3 = N3; q.tiles_n = tiles_n; q.tiles_m = p.tiles_m; q.tiles_per_split = ceil_div(tiles_n, splits);
+        splits = ceil_div(tiles_n, q.tiles_per_split);
         row_parts = splits * 2;
         const double log2e = 1.4426950408889634;
         q.c1 = (float)(log2e / ((double)scale_factor * simtc::kOperandScale * simtc::kOperandScale));
@@ -338,7 +339,7 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         cfg.attrs = attr; cfg.numAttrs = 1;
         if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 2>, t2h, t2l, t3h, t3l, tconf, q));
         else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 1>, t2h, t2l, t3h, t3l, tconf, q));
-        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, p.tiles_n * 2, N2, w.invR, 1);
+        k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, tiles_n * 2, N2, w.invR, 1);
         k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC, 1);
         OPB_CHECK_LAUNCH();
         if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 2>, t2h, t2l, t3h, t3l, tconf, q));

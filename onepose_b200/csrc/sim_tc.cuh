@@ -17,11 +17,11 @@
 namespace opb {
 namespace simtc {
 
-constexpr int BM = 128, BN = 128, NKB = 4;
+constexpr int BM = 128, NKB = 4;
 constexpr int TILE_BYTES = 128 * 128;                 // 128 rows x 64 fp16
 constexpr int A_BYTES = 2 * NKB * TILE_BYTES;         // 131072
 constexpr int RING_BYTES = 4 * TILE_BYTES;            // 65536
-constexpr int MAX_UNITS = 8;
+constexpr int MAX_UNITS = 4;
 // CG = 1: one CTA per 128 query rows; a ring unit is a whole 128-column k-block of B (16 KB, 4 units).
 // CG = 2: a CTA pair (cta_group::2) per 256 query rows: each CTA keeps its own 128 rows of A resident and stages HALF of every
 //         B k-block (64 columns, 8 KB, 8 units), the leader issues M256 N128 MMAs.  Every row tile re-streams all of the frame's
@@ -31,14 +31,18 @@ constexpr int MAX_UNITS = 8;
 //         time (the ring is round-trip bound), so CG = 1 stays the default.
 template <int CG>
 struct SimCfg {
-    static constexpr int UNITS = 4 * CG;
-    static constexpr int B_ROWS = BN / CG;            // columns of a B k-block held by one CTA
-    static constexpr int UNIT_BYTES = B_ROWS * 128;   // 16384 / 8192
+    static constexpr int BN = 128 * CG;               // columns of a tile: 128 (one CTA) / 256 (pair, M256 x N256 like the projections)
+    static constexpr int UNITS = 4;
+    static constexpr int B_ROWS = 128;                // columns of a B k-block held by one CTA
+    static constexpr int UNIT_BYTES = B_ROWS * 128;   // 16384
+    static constexpr int HALF = BN / 2;               // columns of a tile one epilogue warp owns: 64 / 128
+    static constexpr int GROUPS = HALF / 64;          // pairs of 32-column chunks per warp and tile
+    static constexpr int TMEM_COLS = 2 * BN;          // double-buffered accumulator: 256 / 512 columns
 };
 constexpr int STG_WARP_BYTES = 32 * 16 * 4;            // per epilogue warp: 32 rows x 16 fp32 columns, TMA-store staging
 constexpr int STG_BYTES = 8 * STG_WARP_BYTES;         // 16384
-constexpr int SCRATCH_BYTES = 2 * 4 * BN * 8;         // double-buffered [4 warps][128] u64
-constexpr int LGC_BYTES = 2 * BN * 4;                 // double-buffered column terms of the current tile
+constexpr int SCRATCH_BYTES = 2 * 4 * 256 * 4;        // double-buffered [4 quadrants][<= 256 columns] of 32-bit partials
+constexpr int LGC_BYTES = 2 * 256 * 4;                // double-buffered column terms of the current tile
 constexpr int SMEM_BYTES = A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES + LGC_BYTES + 256 + 1024;   // + barriers + alignment slack
 constexpr float kOperandScale = 64.f;                 // unit-vector components are scaled into fp16's normal range
 
@@ -52,7 +56,7 @@ struct Params {
     float *conf;
     int tiles_m;                                      // row tiles of a frame (the grid may carry one ghost row tile to fill a pair)
     int tma_store;                                    // conf rows are 16-byte aligned: write conf through TMA stores
-    int dbg;                                          // experiment switches (OPB_SIM_DBG), 0 in production
+    int dbg;                                          // experiment switches (OPB_SIM_DBG; timing only): 1 = no conf stores, 8 = no MMAs; 0 in production
 };
 
 struct Barriers {
@@ -101,11 +105,12 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t *sA = smem, *sB = smem + A_BYTES;
     uint8_t *s_stg = smem + A_BYTES + RING_BYTES;
-    unsigned long long *scratch = reinterpret_cast<unsigned long long *>(smem + A_BYTES + RING_BYTES + STG_BYTES);
+    uint32_t *scratch = reinterpret_cast<uint32_t *>(smem + A_BYTES + RING_BYTES + STG_BYTES);
     float *s_lgc = reinterpret_cast<float *>(smem + A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES);
     Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + STG_BYTES + SCRATCH_BYTES + LGC_BYTES);
 
-    constexpr int UNITS = SimCfg<CG>::UNITS, UNIT_BYTES = SimCfg<CG>::UNIT_BYTES;
+    using Cfg = SimCfg<CG>;
+    constexpr int BN = Cfg::BN, UNITS = Cfg::UNITS, UNIT_BYTES = Cfg::UNIT_BYTES, HALF = Cfg::HALF, GROUPS = Cfg::GROUPS;
     const uint32_t rank = CG == 2 ? tc::cluster_ctarank() : 0;            // 0 = leader of the pair (cluster dims (2, 1, 1): row tiles 2i, 2i+1)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int split = blockIdx.y, row_tile = blockIdx.x, b = blockIdx.z;
@@ -113,7 +118,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     const int m0 = row_tile * BM;
     const int t0 = split * p.tiles_per_split;
     const int t1 = min(p.tiles_n, t0 + p.tiles_per_split);
-    if (t0 >= t1) return;                                   // uniform for the whole CTA
+    if (t0 >= t1) return;                                   // uniform for the whole CTA (and its pair)
 
     if (threadIdx.x == 0) {
         tc::mbar_init(&bar->a_full, 1);
@@ -121,7 +126,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&bar->acc_full[i], 1); tc::mbar_init(&bar->acc_empty[i], 8 * CG); }
         tc::fence_barrier_init();
     }
-    if (warp == 9) { if (CG == 2) tc::tmem_alloc_cg2<256>(&bar->tmem_base); else tc::tmem_alloc<256>(&bar->tmem_base); }
+    if (warp == 9) { if (CG == 2) tc::tmem_alloc_cg2<Cfg::TMEM_COLS>(&bar->tmem_base); else tc::tmem_alloc<Cfg::TMEM_COLS>(&bar->tmem_base); }
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_m2h); tc::tma_prefetch_desc(&tm_m2l); tc::tma_prefetch_desc(&tm_m3h); tc::tma_prefetch_desc(&tm_m3l);
         if (PASS == 2 && p.tma_store) tc::tma_prefetch_desc(&tm_conf);
@@ -156,7 +161,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                         if (CG == 2) {
                             if (rank == 0) tc::mbar_arrive_expect_tx(&bar->b_full[stage], 2 * UNIT_BYTES);
                             tc::tma_load_3d_cg2(sB + stage * UNIT_BYTES, plane ? &tm_m3l : &tm_m3h, tc::mapa(tc::smem_u32(&bar->b_full[stage]), 0),
-                                                kb * 64, t * BN + (int)rank * SimCfg<CG>::B_ROWS, b);
+                                                kb * 64, t * BN + (int)rank * Cfg::B_ROWS, b);
                         } else {
                             tc::mbar_arrive_expect_tx(&bar->b_full[stage], UNIT_BYTES);
                             tc::tma_load_3d(sB + stage * UNIT_BYTES, plane ? &tm_m3l : &tm_m3h, &bar->b_full[stage], kb * 64, t * BN, b);
@@ -216,26 +221,25 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         if (PASS == 2) rowc = row_ok ? p.lgR[(long long)b * p.N2 + row] - 2.f * p.c0 : -INFINITY;
         float *crow = PASS == 2 ? p.conf + ((long long)b * p.N2 + (row_ok ? row : 0)) * p.N3 : nullptr;
         const bool vec_ok = (p.N3 & 3) == 0;
-        const uint32_t rinv = 127u - (uint32_t)(quad * 32 + lane);          // inverted row index inside the tile
+        const uint32_t rinv = 127u - (uint32_t)(quad * 32 + lane);          // inverted row index inside the CTA's 128 rows
         // fold of the four quadrants' column partials of tile (tt, buffer jj), thread = column, fixed order
         auto fold_columns = [&](int tt, int jj) {
-            const unsigned long long *scr = scratch + (jj & 1) * 4 * BN;
+            const uint32_t *scr = scratch + (jj & 1) * 4 * BN;
             const int tid = threadIdx.x, col = tt * BN + tid;
             if (tid < BN && col < p.N3 && tile_ok) {
                 if (PASS == 1) {
                     const float *sf = reinterpret_cast<const float *>(scr);
                     p.colsum_part[((long long)b * p.tiles_m + row_tile) * p.N3 + col] = ((sf[tid] + sf[BN + tid]) + sf[2 * BN + tid]) + sf[3 * BN + tid];
                 } else {
-                    const uint32_t *su = reinterpret_cast<const uint32_t *>(scr);
-                    uint32_t k = su[tid];
+                    uint32_t k = scr[tid];
 #pragma unroll
-                    for (int w = 1; w < 4; ++w) k = su[w * BN + tid] > k ? su[w * BN + tid] : k;
+                    for (int w = 1; w < 4; ++w) k = scr[w * BN + tid] > k ? scr[w * BN + tid] : k;
                     p.colmax_part[((long long)b * p.tiles_m + row_tile) * p.N3 + col] =
                         ((unsigned long long)(k & 0xFFFFFF80u) << 32) | (unsigned long long)(0xffffffffu - (unsigned)(m0 + 127 - (int)(k & 127u)));
                 }
             }
         };
-        auto load_lgc = [&](int tt) -> float {           // column term of tile tt for this thread (threads 0..127)
+        auto load_lgc = [&](int tt) -> float {           // column term of tile tt for this thread (threads 0..BN-1)
             const int col = tt * BN + (int)threadIdx.x;
             return (PASS == 2 && threadIdx.x < BN && tt < t1 && col < p.N3) ? p.lgC[(long long)b * p.N3 + col] : -INFINITY;
         };
@@ -243,7 +247,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         int j = 0;
         for (int t = t0; t < t1; ++t, ++j) {
             const uint32_t as = j & 1, aph = (j >> 1) & 1;
-            unsigned long long *scr = scratch + (j & 1) * 4 * BN;
+            uint32_t *scr = scratch + (j & 1) * 4 * BN;
             float *lgc = s_lgc + (j & 1) * BN;
             if (PASS == 2 && threadIdx.x < BN) lgc[threadIdx.x] = lg_next;
             epi_bar_sync();                       // one barrier per tile: lgc(j) is visible and the partials of tile j-1 are complete
@@ -251,91 +255,102 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
             lg_next = load_lgc(t + 1);            // in flight during this tile
             tc::mbar_wait(&bar->acc_full[as], aph);
             tc::tcgen05_fence_after();
-            // both 32-column chunks of this warp are fetched up front, then the accumulator is handed back to the MMA warp
-            float v[2][32];
-            tc::tmem_ld_32x32(lane_base + as * BN + half * 64, v[0]);
-            tc::tmem_ld_32x32(lane_base + as * BN + half * 64 + 32, v[1]);
-            tc::tmem_ld_wait();
-            tc::tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) { if (CG == 2) tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&bar->acc_empty[as]), 0)); else tc::mbar_arrive(&bar->acc_empty[as]); }
-            uint32_t tile_rk = 0u;
+            uint32_t tile_rk = 0u;                // row key of this warp's HALF columns: value bits | 7-bit inverted index inside the half
             float row_sum = 0.f;
+#pragma unroll 1
+            for (int g = 0; g < GROUPS; ++g) {
+                // two 32-column chunks are fetched up front; after the last pair the accumulator goes back to the MMA warp
+                float v[2][32];
+                tc::tmem_ld_32x32(lane_base + as * BN + half * HALF + g * 64, v[0]);
+                tc::tmem_ld_32x32(lane_base + as * BN + half * HALF + g * 64 + 32, v[1]);
+                tc::tmem_ld_wait();
+                if (g == GROUPS - 1) {
+                    tc::tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) { if (CG == 2) tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&bar->acc_empty[as]), 0)); else tc::mbar_arrive(&bar->acc_empty[as]); }
+                }
 #pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-                const int ccol = half * 64 + cc * 32;          // column inside the tile
-                const int col0 = t * BN + ccol;
-                float *vv = v[cc];
-                if (PASS == 1) {
+                for (int cc = 0; cc < 2; ++cc) {
+                    const int hcol = g * 64 + cc * 32;             // column inside this warp's half
+                    const int ccol = half * HALF + hcol;           // column inside the tile
+                    const int col0 = t * BN + ccol;
+                    float *vv = v[cc];
+                    if (PASS == 1) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float e = tc::ex2(fmaf(vv[i], p.c1, -p.c0));
-                        vv[i] = (row_ok && col0 + i < p.N3) ? e : 0.f;
-                    }
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) row_sum += vv[i];
-                    const float cs = transpose_reduce_sum(vv, lane);
-                    reinterpret_cast<float *>(scr)[quad * BN + ccol + lane] = cs;
-                } else {
-                    // 32-bit selection keys: conf bits with the low 7 mantissa bits replaced by the inverted in-tile index
-                    // (ties within 2^-16 relative resolve to the smaller index; the exact score is read back from conf).
-                    uint32_t ck = 0u;
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        if (p.dbg & 16) continue;
-                        const float4 l4 = *reinterpret_cast<const float4 *>(lgc + ccol + 4 * q);
-                        const float l[4] = {l4.x, l4.y, l4.z, l4.w};
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const int i = 4 * q + e;
-                            const float cf = tc::ex2(fmaf(vv[i], p.c2, rowc + l[e]));
-                            vv[i] = cf;
-                            const uint32_t bits = __float_as_uint(cf) & 0xFFFFFF80u;
-                            const uint32_t kr = bits | (uint32_t)(127 - (ccol + i));
-                            tile_rk = kr > tile_rk ? kr : tile_rk;
-                            if (!(p.dbg & 2)) {
-                                const uint32_t r = __reduce_max_sync(0xffffffffu, bits | rinv);
-                                ck = lane == i ? r : ck;
-                            } else ck |= bits;
+                        for (int i = 0; i < 32; ++i) {
+                            const float e = tc::ex2(fmaf(vv[i], p.c1, -p.c0));
+                            vv[i] = (row_ok && col0 + i < p.N3) ? e : 0.f;
                         }
-                    }
-                    if (p.tma_store) {
-                        // coalesced write: stage 32 rows x 16 columns in (64-byte swizzled) shared memory, one TMA store per half
-                        // chunk; rows / columns past the end of conf are clipped by the TMA unit
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) row_sum += vv[i];
+                        const float cs = transpose_reduce_sum(vv, lane);
+                        reinterpret_cast<float *>(scr)[quad * BN + ccol + lane] = cs;
+                    } else {
+                        // 32-bit selection keys: conf bits with the low 7 mantissa bits replaced by the inverted in-tile index
+                        // (ties within 2^-16 relative resolve to the smaller index; the exact score is read back from conf).
+                        uint32_t ck = 0u;
                         uint8_t *stg = s_stg + warp * STG_WARP_BYTES;
 #pragma unroll
                         for (int hc = 0; hc < 2; ++hc) {
-                            if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
-                            __syncwarp();
+                            // 16 columns of arithmetic, then their store: the TMA engine reads the staging buffer of the previous
+                            // 16 columns while these are computed
+                            // (no experiment switch inside this loop: a branch per score serialises FFMA -> MUFU -> REDUX -> SEL)
+                            float l[16];
 #pragma unroll
-                            for (int q = 0; q < 4; ++q)
-                                *reinterpret_cast<float4 *>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) =
-                                    make_float4(vv[hc * 16 + 4 * q], vv[hc * 16 + 4 * q + 1], vv[hc * 16 + 4 * q + 2], vv[hc * 16 + 4 * q + 3]);
-                            tc::fence_proxy_async();
-                            __syncwarp();
-                            if (lane == 0 && !(p.dbg & 1)) {
-                                tc::tma_store_3d(&tm_conf, stg, col0 + hc * 16, m0 + quad * 32, b);
-                                tc::tma_store_commit();
+                            for (int q = 0; q < 4; ++q) {
+                                const float4 l4 = *reinterpret_cast<const float4 *>(lgc + ccol + 16 * hc + 4 * q);
+                                l[4 * q] = l4.x; l[4 * q + 1] = l4.y; l[4 * q + 2] = l4.z; l[4 * q + 3] = l4.w;
+                            }
+#pragma unroll
+                            for (int e = 0; e < 16; ++e) {
+                                const int i = 16 * hc + e;
+                                vv[i] = tc::ex2(fmaf(vv[i], p.c2, rowc + l[e]));
+                            }
+#pragma unroll
+                            for (int e = 0; e < 16; ++e) {
+                                const int i = 16 * hc + e;
+                                const uint32_t bits = __float_as_uint(vv[i]) & 0xFFFFFF80u;
+                                const uint32_t kr = bits | (uint32_t)(127 - (hcol + i));
+                                tile_rk = kr > tile_rk ? kr : tile_rk;
+                                const uint32_t r = __reduce_max_sync(0xffffffffu, bits | rinv);
+                                ck = lane == i ? r : ck;
+                            }
+                            if (p.tma_store) {
+                                // coalesced write: stage 32 rows x 16 columns in (64-byte swizzled) shared memory, one TMA store per half
+                                // chunk; rows / columns past the end of conf are clipped by the TMA unit
+                                if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
+                                __syncwarp();
+#pragma unroll
+                                for (int q = 0; q < 4; ++q)
+                                    *reinterpret_cast<float4 *>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) =
+                                        make_float4(vv[hc * 16 + 4 * q], vv[hc * 16 + 4 * q + 1], vv[hc * 16 + 4 * q + 2], vv[hc * 16 + 4 * q + 3]);
+                                tc::fence_proxy_async();
+                                __syncwarp();
+                                if (lane == 0 && !(p.dbg & 1)) {
+                                    tc::tma_store_3d(&tm_conf, stg, col0 + hc * 16, m0 + quad * 32, b);
+                                    tc::tma_store_commit();
+                                }
                             }
                         }
-                    } else if (row_ok) {
-                        if (vec_ok && col0 + 31 < p.N3) {
+                        if (!p.tma_store && row_ok) {
+                            if (vec_ok && col0 + 31 < p.N3) {
 #pragma unroll
-                            for (int q = 0; q < 8; ++q)
-                                *reinterpret_cast<float4 *>(crow + col0 + 4 * q) = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
-                        } else {
-                            for (int i = 0; i < 32; ++i) if (col0 + i < p.N3) crow[col0 + i] = vv[i];
+                                for (int q = 0; q < 8; ++q)
+                                    *reinterpret_cast<float4 *>(crow + col0 + 4 * q) = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
+                            } else {
+                                for (int i = 0; i < 32; ++i) if (col0 + i < p.N3) crow[col0 + i] = vv[i];
+                            }
                         }
+                        scr[quad * BN + ccol + lane] = ck;
                     }
-                    reinterpret_cast<uint32_t *>(scr)[quad * BN + ccol + lane] = ck;
                 }
             }
             if (PASS == 1) {
                 // per-(tile, column half) partial: the fold over partials is split-invariant
                 if (row_ok) p.rowsum_part[((long long)b * (p.tiles_n * 2) + t * 2 + half) * p.N2 + row] = row_sum;
-            } else {   // tile key -> global 64-bit key (value bits high, inverted global column low)
+            } else {   // half-tile key -> global 64-bit key (value bits high, inverted global column low)
                 const unsigned long long k64 = ((unsigned long long)(tile_rk & 0xFFFFFF80u) << 32) |
-                                               (unsigned long long)(0xffffffffu - (unsigned)(t * BN + 127 - (int)(tile_rk & 127u)));
+                                               (unsigned long long)(0xffffffffu - (unsigned)(t * BN + half * HALF + 127 - (int)(tile_rk & 127u)));
                 row_key = k64 > row_key ? k64 : row_key;
             }
         }
@@ -346,7 +361,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     }
     tc::tcgen05_fence_before();
     if (CG == 2) tc::cluster_sync(); else __syncthreads();                // nothing is in flight to or from the peer any more
-    if (warp == 9) { if (CG == 2) tc::tmem_dealloc_cg2<256>(tmem_base); else tc::tmem_dealloc<256>(tmem_base); }
+    if (warp == 9) { if (CG == 2) tc::tmem_dealloc_cg2<Cfg::TMEM_COLS>(tmem_base); else tc::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
 }
 
 // fp32 rows -> scaled fp16 hi / lo planes

@@ -153,8 +153,11 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(out) : "r"(addr), "r"(rank));
     return out;
 }
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {       // arrive on a (possibly remote) CTA's barrier
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+// arrive on a (possibly remote) CTA's barrier.  Default semantics (.release.cta), as library kernels release an accumulator stage:
+// the .release.cluster form costs a MEMBAR.ALL + ERRBAR per arrive (6 % of the pair kernels' epilogue samples in ncu), and the
+// only data the consumer depends on are TMEM reads that tcgen05.wait::ld has already completed
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load of one CTA of a pair: data into this CTA's shared memory, bytes credited to the barrier at cluster address `bar`
 // (the leader CTA's: its single MMA thread consumes both CTAs' operands)
