@@ -292,7 +292,7 @@ def run_ours(args):
             # fp32-class accuracy from fp16 MMAs costs three MMAs per algorithmic product (hi*hi + lo*hi + hi*lo): the tensor pipe
             # executes 3x the algorithmic flops that `achieved` counts
             roofline.update(mma_passes=3, achieved_issued=3 * d["achieved"], frac_issued=3 * d["frac"])
-        sim = kernels.get("op_sim_dual_softmax")
+        sim = kernels.get("op_sim_dual_softmax_rows") or kernels.get("op_sim_dual_softmax")
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             n_cpu = 4

@@ -171,6 +171,12 @@ int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3,
                         float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                         float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
                         void *stream);
+/* Same contract for rows that are not yet unit length: F.normalize (:245-246) is fused into the operand split, so the
+ * normalised fp32 copy of the final projections is never written (bit-identical to op_l2_normalize_rows + op_sim_dual_softmax). */
+int op_sim_dual_softmax_rows(const float *x2, const float *x3, int B, int N2, int N3, float scale_factor,
+                             float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                             float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
+                             void *stream);
 /* Same contract on fp32 CUDA cores (exact fp32 dot products, no tensor cores): kept as the on-device
  * cross-check of the tcgen05 split-precision kernel, not used by the product path. */
 int op_sim_dual_softmax_simt(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,

@@ -187,14 +187,24 @@ __global__ void k_sim_finalize_sums(const float *__restrict__ part, int tiles, i
 }
 
 __global__ void k_sim_finalize_max(const unsigned long long *__restrict__ part, int tiles, int n, int n_other,
-                                   int *__restrict__ idx, float *__restrict__ val) {
+                                   int *__restrict__ idx, float *__restrict__ val, const float *__restrict__ conf_rows) {
     const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     unsigned long long k = 0ull;
     for (int t = 0; t < tiles; ++t) { const unsigned long long v = part[((long long)b * tiles + t) * n + i]; k = v > k ? v : k; }
     // an all-zero row / column of conf can select a padding slot of the last tile: every index is then a maximum, clamp it
-    const int id = (int)(0xffffffffu - (unsigned)(k & 0xffffffffull));
-    idx[(long long)b * n + i] = id < n_other ? id : n_other - 1;
+    int id = (int)(0xffffffffu - (unsigned)(k & 0xffffffffull));
+    id = id < n_other ? id : n_other - 1;
+    if (conf_rows) {
+        // tensor-core pass 2, rows: the key carries the exact maximum and the first column of the 16-column block that holds it;
+        // the column is the first of those 16 scores equal to it (conf_rows = conf, row i of frame b)
+        const float *r = conf_rows + ((long long)b * n + i) * n_other;
+        const unsigned want = (unsigned)(k >> 32);
+        int hit = id;
+        for (int c = 15; c >= 0; --c) if (id + c < n_other && __float_as_uint(r[id + c]) == want) hit = id + c;
+        id = hit;
+    }
+    idx[(long long)b * n + i] = id;
     val[(long long)b * n + i] = __uint_as_float((unsigned)(k >> 32));
 }
 
@@ -261,7 +271,7 @@ extern "C" size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3) {
     return opb::carve(nullptr, B > 0 ? B : 1, N2 > 0 ? N2 : 1, N3 > 0 ? N3 : 1).bytes;
 }
 
-static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
+static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
                     float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                     float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
                     void *stream) {
@@ -291,8 +301,13 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
     } else {
         // split fp32 unit rows into scaled fp16 hi/lo planes, describe them to TMA, run the two tcgen05 passes
         const long long n2e = (long long)B * N2 * kD, n3e = (long long)B * N3 * kD;
-        simtc::k_split_planes<<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, n2e, simtc::kOperandScale);
-        simtc::k_split_planes<<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, n3e, simtc::kOperandScale);
+        if (normalize) {
+            simtc::k_normalize_split_planes<<<ceil_div((long long)B * N2, 8), 256, 0, st>>>(m2, w.m2h, w.m2l, (long long)B * N2, simtc::kOperandScale);
+            simtc::k_normalize_split_planes<<<ceil_div((long long)B * N3, 8), 256, 0, st>>>(m3, w.m3h, w.m3l, (long long)B * N3, simtc::kOperandScale);
+        } else {
+            simtc::k_split_planes<<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, n2e, simtc::kOperandScale);
+            simtc::k_split_planes<<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, n3e, simtc::kOperandScale);
+        }
         OPB_CHECK_LAUNCH();
         CUtensorMap t2h, t2l, t3h, t3l, tconf;
         int rc;
@@ -345,8 +360,8 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
         if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 2>, t2h, t2l, t3h, t3l, tconf, q));
         else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 1>, t2h, t2l, t3h, t3l, tconf, q));
     }
-    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, N3, w.idx0, w.val0);
-    k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, N2, w.idx1, w.val1);
+    k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, N3, w.idx0, w.val0, tensor_cores ? conf : nullptr);
+    k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, N2, w.idx1, w.val1, nullptr);
     OPB_CHECK_LAUNCH();
     const int nmax = N2 > N3 ? N2 : N3;
     k_mutual_select<<<dim3(ceil_div(nmax, 256), B), 256, 0, st>>>(w.idx0, conf, w.idx1, N2, N3, match_threshold,
@@ -358,13 +373,20 @@ static int sim_impl(bool tensor_cores, const float *m2, const float *m3, int B, 
 extern "C" int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
                                    float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                                    float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
-    return sim_impl(true, m2, m3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
+    return sim_impl(true, false, m2, m3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
                     workspace, workspace_bytes, stream);
 }
 
 extern "C" int op_sim_dual_softmax_simt(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
                                         float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                                         float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
-    return sim_impl(false, m2, m3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
+    return sim_impl(false, false, m2, m3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
+                    workspace, workspace_bytes, stream);
+}
+
+extern "C" int op_sim_dual_softmax_rows(const float *x2, const float *x3, int B, int N2, int N3, float scale_factor,
+                                        float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                                        float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
+    return sim_impl(true, true, x2, x3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
                     workspace, workspace_bytes, stream);
 }

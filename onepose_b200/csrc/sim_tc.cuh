@@ -215,13 +215,23 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
         const int row = m0 + quad * 32 + lane;
         const bool row_ok = row < p.N2;
         const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
-        unsigned long long row_key = 0ull;
+        // PASS 2 row selection: running maximum of the raw conf bits (conf >= +0: unsigned order = float order) and the first column of
+        // the 16-column block that holds it (strictly greater: the earliest block wins ties); k_sim_finalize_max finds the exact column
+        // by re-reading those 16 scores from conf
+        uint32_t row_best = 0u, row_blk = 0u;
         // PASS 2: conf = exp2(2*c1*acc - 2*c0 + log2(1/R_n) + log2(1/C_m)); rows / columns past the end carry -inf => conf = +0
         float rowc = 0.f;
         if (PASS == 2) rowc = row_ok ? p.lgR[(long long)b * p.N2 + row] - 2.f * p.c0 : -INFINITY;
         float *crow = PASS == 2 ? p.conf + ((long long)b * p.N2 + (row_ok ? row : 0)) * p.N3 : nullptr;
         const bool vec_ok = (p.N3 & 3) == 0;
-        const uint32_t rinv = 127u - (uint32_t)(quad * 32 + lane);          // inverted row index inside the CTA's 128 rows
+        // PASS 2 column selection reads the staged 32 x 16 block back transposed: lane = (column c, row parity par), 16 rows each.
+        // Keys: conf bits with the 7 low mantissa bits replaced by the inverted row index inside the CTA's 128 rows (ties within
+        // 2^-16 relative resolve to the smaller row; the exact score is read back from conf by k_mutual_select)
+        const int tc_c = lane & 15, tc_par = lane >> 4;
+        const uint32_t rinv0 = 127u - (uint32_t)(quad * 32 + tc_par);       // row 2j + par of the warp's 32 rows: key index rinv0 - 2j
+        uint32_t tc_off[4];                                                 // byte offset of (row 2j + par, column c) for j & 3 = 0..3, minus 128 j
+#pragma unroll
+        for (int k = 0; k < 4; ++k) tc_off[k] = (uint32_t)(tc_par * 64 + (((tc_c >> 2) ^ k) << 4) + (tc_c & 3) * 4);
         // fold of the four quadrants' column partials of tile (tt, buffer jj), thread = column, fixed order
         auto fold_columns = [&](int tt, int jj) {
             const uint32_t *scr = scratch + (jj & 1) * 4 * BN;
@@ -255,7 +265,6 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
             lg_next = load_lgc(t + 1);            // in flight during this tile
             tc::mbar_wait(&bar->acc_full[as], aph);
             tc::tcgen05_fence_after();
-            uint32_t tile_rk = 0u;                // row key of this warp's HALF columns: value bits | 7-bit inverted index inside the half
             float row_sum = 0.f;
 #pragma unroll 1
             for (int g = 0; g < GROUPS; ++g) {
@@ -286,51 +295,49 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                         const float cs = transpose_reduce_sum(vv, lane);
                         reinterpret_cast<float *>(scr)[quad * BN + ccol + lane] = cs;
                     } else {
-                        // 32-bit selection keys: conf bits with the low 7 mantissa bits replaced by the inverted in-tile index
-                        // (ties within 2^-16 relative resolve to the smaller index; the exact score is read back from conf).
-                        uint32_t ck = 0u;
                         uint8_t *stg = s_stg + warp * STG_WARP_BYTES;
 #pragma unroll
                         for (int hc = 0; hc < 2; ++hc) {
                             // 16 columns of arithmetic, then their store: the TMA engine reads the staging buffer of the previous
                             // 16 columns while these are computed
-                            // (no experiment switch inside this loop: a branch per score serialises FFMA -> MUFU -> REDUX -> SEL)
+                            // (no experiment switch inside this loop: a branch per score serialises FFMA -> MUFU -> ...)
                             float l[16];
 #pragma unroll
                             for (int q = 0; q < 4; ++q) {
                                 const float4 l4 = *reinterpret_cast<const float4 *>(lgc + ccol + 16 * hc + 4 * q);
                                 l[4 * q] = l4.x; l[4 * q + 1] = l4.y; l[4 * q + 2] = l4.z; l[4 * q + 3] = l4.w;
                             }
+                            uint32_t bm = 0u;
 #pragma unroll
                             for (int e = 0; e < 16; ++e) {
                                 const int i = 16 * hc + e;
                                 vv[i] = tc::ex2(fmaf(vv[i], p.c2, rowc + l[e]));
+                                bm = max(bm, __float_as_uint(vv[i]));
                             }
+                            if (bm > row_best) { row_best = bm; row_blk = (uint32_t)(col0 + 16 * hc); }
+                            // stage 32 rows x 16 columns in (64-byte swizzled) shared memory: one coalesced TMA store per block (rows /
+                            // columns past the end of conf are clipped by the TMA unit), and the source of the transposed read below
+                            if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
+                            __syncwarp();
 #pragma unroll
-                            for (int e = 0; e < 16; ++e) {
-                                const int i = 16 * hc + e;
-                                const uint32_t bits = __float_as_uint(vv[i]) & 0xFFFFFF80u;
-                                const uint32_t kr = bits | (uint32_t)(127 - (hcol + i));
-                                tile_rk = kr > tile_rk ? kr : tile_rk;
-                                const uint32_t r = __reduce_max_sync(0xffffffffu, bits | rinv);
-                                ck = lane == i ? r : ck;
+                            for (int q = 0; q < 4; ++q)
+                                *reinterpret_cast<float4 *>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) =
+                                    make_float4(vv[hc * 16 + 4 * q], vv[hc * 16 + 4 * q + 1], vv[hc * 16 + 4 * q + 2], vv[hc * 16 + 4 * q + 3]);
+                            tc::fence_proxy_async();
+                            __syncwarp();
+                            if (p.tma_store && lane == 0 && !(p.dbg & 1)) {
+                                tc::tma_store_3d(&tm_conf, stg, col0 + hc * 16, m0 + quad * 32, b);
+                                tc::tma_store_commit();
                             }
-                            if (p.tma_store) {
-                                // coalesced write: stage 32 rows x 16 columns in (64-byte swizzled) shared memory, one TMA store per half
-                                // chunk; rows / columns past the end of conf are clipped by the TMA unit
-                                if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
-                                __syncwarp();
+                            // column keys: 16 rows of one parity per lane (even rows sit in banks 0-15, odd rows in 16-31: conflict-free)
+                            uint32_t ck = 0u;
 #pragma unroll
-                                for (int q = 0; q < 4; ++q)
-                                    *reinterpret_cast<float4 *>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) =
-                                        make_float4(vv[hc * 16 + 4 * q], vv[hc * 16 + 4 * q + 1], vv[hc * 16 + 4 * q + 2], vv[hc * 16 + 4 * q + 3]);
-                                tc::fence_proxy_async();
-                                __syncwarp();
-                                if (lane == 0 && !(p.dbg & 1)) {
-                                    tc::tma_store_3d(&tm_conf, stg, col0 + hc * 16, m0 + quad * 32, b);
-                                    tc::tma_store_commit();
-                                }
+                            for (int j = 0; j < 16; ++j) {
+                                const uint32_t w = *reinterpret_cast<const uint32_t *>(stg + tc_off[j & 3] + 128 * j);
+                                ck = max(ck, (w & 0xFFFFFF80u) | (rinv0 - 2u * j));
                             }
+                            ck = max(ck, __shfl_xor_sync(0xffffffffu, ck, 16));
+                            if (lane < 16) scr[quad * BN + ccol + 16 * hc + lane] = ck;
                         }
                         if (!p.tma_store && row_ok) {
                             if (vec_ok && col0 + 31 < p.N3) {
@@ -341,23 +348,20 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                                 for (int i = 0; i < 32; ++i) if (col0 + i < p.N3) crow[col0 + i] = vv[i];
                             }
                         }
-                        scr[quad * BN + ccol + lane] = ck;
                     }
                 }
             }
             if (PASS == 1) {
                 // per-(tile, column half) partial: the fold over partials is split-invariant
                 if (row_ok) p.rowsum_part[((long long)b * (p.tiles_n * 2) + t * 2 + half) * p.N2 + row] = row_sum;
-            } else {   // half-tile key -> global 64-bit key (value bits high, inverted global column low)
-                const unsigned long long k64 = ((unsigned long long)(tile_rk & 0xFFFFFF80u) << 32) |
-                                               (unsigned long long)(0xffffffffu - (unsigned)(t * BN + half * HALF + 127 - (int)(tile_rk & 127u)));
-                row_key = k64 > row_key ? k64 : row_key;
             }
         }
         epi_bar_sync();
         fold_columns(t1 - 1, j - 1);
         if (PASS == 2 && lane == 0) tc::tma_store_wait_all();
-        if (PASS == 2 && row_ok) p.rowmax_part[((long long)b * (gridDim.y * 2) + split * 2 + half) * p.N2 + row] = row_key;
+        if (PASS == 2 && row_ok)      // (value bits, inverted first column of the winning 16-column block)
+            p.rowmax_part[((long long)b * (gridDim.y * 2) + split * 2 + half) * p.N2 + row] =
+                ((unsigned long long)row_best << 32) | (unsigned long long)(0xffffffffu - row_blk);
     }
     tc::tcgen05_fence_before();
     if (CG == 2) tc::cluster_sync(); else __syncthreads();                // nothing is in flight to or from the peer any more
@@ -374,6 +378,28 @@ __global__ void k_split_planes(const float *__restrict__ x, __half *__restrict__
     tc::split_f16(v.z * scale, h[2], l[2]); tc::split_f16(v.w * scale, h[3], l[3]);
     *reinterpret_cast<uint2 *>(hi + i) = *reinterpret_cast<uint2 *>(h);
     *reinterpret_cast<uint2 *>(lo + i) = *reinterpret_cast<uint2 *>(l);
+}
+
+// F.normalize (x / max(|x|, 1e-12), GATs_SuperGlue.py:245-246) fused into the operand split: one warp per 256-wide row, the same
+// summation order and quotient as k_l2_normalize_rows, so the planes are bit-identical to normalising first and splitting after
+__global__ void k_normalize_split_planes(const float *__restrict__ x, __half *__restrict__ hi, __half *__restrict__ lo, long long rows, float scale) {
+    const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const float *src = x + row * 256;
+    float v[8], ss = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { v[k] = src[lane + 32 * k]; ss += v[k] * v[k]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float den = fmaxf(sqrtf(ss), 1e-12f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        __half h, l;
+        tc::split_f16((v[k] / den) * scale, h, l);
+        hi[row * 256 + lane + 32 * k] = h;
+        lo[row * 256 + lane + 32 * k] = l;
+    }
 }
 
 }  // namespace simtc

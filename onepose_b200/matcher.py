@@ -576,8 +576,9 @@ class GATsSuperGlue(nn.Module):
             self._encode_tc(x2, db, pk, B, N2, N3, L, m2, m3, dev)
         else:
             self._encode_simt(x2, db, pk, B, N2, N3, L, m2, m3, dev)
-        call("op_l2_normalize_rows", ptr(m2), ptr(m2), B * N2, _D, stream_ptr())
-        call("op_l2_normalize_rows", ptr(m3), ptr(m3), B * N3, _D, stream_ptr())
+        if not self.use_tensor_cores:                                 # the tensor-core op normalises while it splits the operands
+            call("op_l2_normalize_rows", ptr(m2), ptr(m2), B * N2, _D, stream_ptr())
+            call("op_l2_normalize_rows", ptr(m3), ptr(m3), B * N3, _D, stream_ptr())
 
         conf = torch.empty(B, N2, N3, dtype=torch.float32, device=dev)      # returned to the caller
         i0 = torch.empty(B, N2, dtype=torch.int64, device=dev)
@@ -587,7 +588,7 @@ class GATsSuperGlue(nn.Module):
         nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
         w = self._ws.get("simws", (nbytes,), torch.uint8, dev)
         timeline.work = B * (4.0 * _D * (N2 + N3) + 4.0 * N2 * N3 + 24.0 * (N2 + N3))   # bytes, SURVEY.md 8(d)
-        call("op_sim_dual_softmax", ptr(m2), ptr(m3), B, N2, N3, float(self.hparams["scale_factor"]),
+        call("op_sim_dual_softmax_rows" if self.use_tensor_cores else "op_sim_dual_softmax", ptr(m2), ptr(m3), B, N2, N3, float(self.hparams["scale_factor"]),
                                       float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
                                       ptr(s1), ptr(w), nbytes, stream_ptr())
         pred = {

@@ -168,3 +168,23 @@ def test_sim_tcgen05_vs_cuda_core_and_float64(shape):
     # deterministic
     tc2 = _run_sim("op_sim_dual_softmax", m2c, m3c)
     assert torch.equal(tc[0], tc2[0]) and torch.equal(tc[1], tc2[1])
+
+
+@pytest.mark.gpu
+def test_sim_rows_entry_equals_normalise_then_sim():
+    """op_sim_dual_softmax_rows (F.normalize fused into the operand split) is bit-identical to op_l2_normalize_rows + op_sim_dual_softmax."""
+    from onepose_b200._lib import call, ptr, stream_ptr
+    g = torch.Generator().manual_seed(5)
+    x2 = (torch.randn(2, 200, 256, generator=g) * 3.0).cuda()
+    x3 = (torch.randn(2, 333, 256, generator=g) * 0.2).cuda()
+    x3[:, :100] = x2[:, :100] * 0.1 + 0.01 * torch.randn(2, 100, 256, generator=g).cuda()
+    x3[0, 7] = 0.0                                            # a zero row: F.normalize leaves it zero (eps clamp)
+    fused = _run_sim("op_sim_dual_softmax_rows", x2, x3)
+    m2, m3 = torch.empty_like(x2), torch.empty_like(x3)
+    call("op_l2_normalize_rows", ptr(x2), ptr(m2), 2 * 200, 256, stream_ptr())
+    call("op_l2_normalize_rows", ptr(x3), ptr(m3), 2 * 333, 256, stream_ptr())
+    assert torch.allclose(m2.cpu(), torch.nn.functional.normalize(x2.cpu(), dim=2), atol=1e-7)
+    two = _run_sim("op_sim_dual_softmax", m2, m3)
+    for a, b in zip(fused, two):
+        assert torch.equal(a, b)
+    assert int((fused[1] > -1).sum()) > 50
