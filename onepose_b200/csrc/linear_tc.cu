@@ -323,12 +323,6 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     p.w2 = W2h ? ((flags & OPB_LIN_W2BATCHED) ? 2 : 1) : 0;
     static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
-    static bool configured = false;
-    if (!configured) {
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::Cfg<1>::SMEM_BYTES));
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(lintc::k_linear_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, lintc::Cfg<2>::SMEM_BYTES));
-        configured = true;
-    }
     const int groups = sm_count() / cg;                                   // persistent CTAs (or CTA pairs), one per SM
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
@@ -339,8 +333,35 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cg; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lintc::k_linear_tc<2>, ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p));
-    else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lintc::k_linear_tc<1>, ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p));
+    // one specialised instantiation per layer kind of the matcher (epilogue flags and output kinds as compile-time constants), the
+    // generic kernel for everything else, for the one-CTA form and whenever experiment switches are set
+    const int key = (flags & lintc::kEpiMask) | (C ? lintc::kHasC : 0) | (Ch ? lintc::kHasP : 0);
+    auto launch = [&](auto kern, int smem_bytes) -> cudaError_t {
+        static const void *configured[16];       // kernels whose dynamic shared memory limit has been raised (all share one pointer type)
+        static int n_configured = 0;
+        bool seen = false;
+        for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void *)kern;
+        if (!seen) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+            if (e != cudaSuccess) return e;
+            if (n_configured < 16) configured[n_configured++] = (const void *)kern;
+        }
+        return cudaLaunchKernelEx(&cfg, kern, ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p);
+    };
+    constexpr int kK = OPB_LIN_ELU1 | OPB_LIN_COLSUM | lintc::kHasP;                          // K' projection
+    constexpr int kQ = OPB_LIN_ELU1 | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | lintc::kHasP;         // Q projection
+    constexpr int kM0 = OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU | lintc::kHasP;                   // MLP layer 0
+    constexpr int kM1 = OPB_LIN_COLSUM | lintc::kHasP;                                        // MLP layer 1 (residual inside the GEMM)
+    constexpr int kF = lintc::kHasC;                                                          // final projection
+    const int smem2 = lintc::Cfg<2>::SMEM_BYTES;
+    if (cg == 1) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<1, -1>, lintc::Cfg<1>::SMEM_BYTES));
+    else if (dbg) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, -1>, smem2));
+    else if (key == kK) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kK>, smem2));
+    else if (key == kQ) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kQ>, smem2));
+    else if (key == kM0) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kM0>, smem2));
+    else if (key == kM1) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kM1>, smem2));
+    else if (key == kF) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kF>, smem2));
+    else OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, -1>, smem2));
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }

@@ -93,7 +93,14 @@ __device__ __forceinline__ void split_planes32(const float *vs, uint32_t *h, uin
     }
 }
 
-template <int CG>
+// FL >= 0: the epilogue flags (kEpiMask bits of Params::flags) and the kinds of output (kHasC, kHasP) are compile-time constants --
+// one instantiation per layer kind of the matcher.  The generic kernel (FL = -1) carries every epilogue variant behind run-time
+// branches: 8400 SASS instructions (134 KB) of which a layer executes a fraction, 10 % of its warp samples waiting for instruction
+// fetch (ncu: stall_no_inst) and 8 % resolving branches; the specialised ones are a third of that size.
+constexpr int kEpiMask = OPB_LIN_ELU1 | OPB_LIN_RESIDUAL | OPB_LIN_STATS | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU;
+constexpr int kHasC = 1 << 20, kHasP = 1 << 21;
+
+template <int CG, int FL>
 __global__ void __launch_bounds__(THREADS, 1)
 k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ CUtensorMap tm_a1l,
             const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
@@ -218,15 +225,19 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
         __syncwarp();
     } else {
         // ================= epilogue (warps 0-7) =================
+        const int flags = FL >= 0 ? (FL & kEpiMask) : p.flags;
+        const bool has_c = FL >= 0 ? (FL & kHasC) != 0 : p.C != nullptr;
+        const bool has_p = FL >= 0 ? (FL & kHasP) != 0 : p.Ch != nullptr;
+        const int dbg = FL >= 0 ? 0 : p.dbg;                   // the experiment switches live in the generic kernel only
         const int quad = warp & 3, half = warp >> 2;
         const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
         // Coalesced output: 32 rows x 64 bytes are staged in (64-byte swizzled) shared memory and leave through one TMA store;
         // rows past the end are clipped by the TMA unit.  Two staging buffers per warp, at most one store still reading.
         uint32_t nst = 0;
         auto stage_store = [&](const CUtensorMap *tm, int col, const uint4 *data, int bb, int r0) {
-            if (p.dbg & 1) return;
+            if (dbg & 1) return;
             uint8_t *buf = s_stg + (warp * 2 + (nst & 1)) * STG_BUF;
-            if (lane == 0 && !(p.dbg & 8)) tc::tma_store_wait_read1();
+            if (lane == 0 && !(dbg & 8)) tc::tma_store_wait_read1();
             __syncwarp();
 #pragma unroll
             for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4 *>(buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) = data[q];
@@ -240,15 +251,15 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             int b, rt, ct; decode(t, b, rt, ct);
             const bool tile_ok = rt < p.row_tiles;                // false: ghost row tile of an odd pair
             const uint32_t as = j & 1, aph = (j >> 1) & 1;
-            if ((p.flags & (OPB_LIN_BIASB | OPB_LIN_ZSCALE)) && b != cur_b) {
+            if ((flags & (OPB_LIN_BIASB | OPB_LIN_ZSCALE)) && b != cur_b) {
                 // per-frame vectors (bias [B, Cout], Ksum [B, 256]) are staged in shared memory when the tile sequence enters a
                 // new frame -- every epilogue warp walks the same sequence, so they all meet here -- instead of being fetched
                 // from global memory inside each tile's critical path
                 asm volatile("bar.sync 1, 256;" ::: "memory");             // nobody still reads the previous frame's copy
                 const int tt = threadIdx.x;                               // 0..255: the epilogue warps
-                if (p.flags & OPB_LIN_BIASB)
+                if (flags & OPB_LIN_BIASB)
                     for (int i = tt; i < p.Cout; i += EPI_WARPS * 32) s_bias[i] = kScale * __ldg(p.bias + (long long)b * p.Cout + i);
-                if (p.flags & OPB_LIN_ZSCALE) s_bias[256 + tt] = __ldg(p.ksum + (long long)b * p.Cout + tt);   // Cout == 256: upper half is free
+                if (flags & OPB_LIN_ZSCALE) s_bias[256 + tt] = __ldg(p.ksum + (long long)b * p.Cout + tt);   // Cout == 256: upper half is free
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 cur_b = b;
             }
@@ -277,7 +288,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 for (int cc = 0; cc < 2; ++cc) {
                     float *vv = v[cc];
                     const int c0 = col0 + cc * 32;
-                    if ((p.flags & OPB_LIN_STATS) && tile_ok) {
+                    if ((flags & OPB_LIN_STATS) && tile_ok) {
                         float s[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = vv[i] * kInvScale2;     // rows past the end are exact zeros (TMA zero fill, no bias yet)
@@ -293,7 +304,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         vv[4 * q] = fmaf(vv[4 * q], 1.f / kScale, bq.x); vv[4 * q + 1] = fmaf(vv[4 * q + 1], 1.f / kScale, bq.y);
                         vv[4 * q + 2] = fmaf(vv[4 * q + 2], 1.f / kScale, bq.z); vv[4 * q + 3] = fmaf(vv[4 * q + 3], 1.f / kScale, bq.w);
                     }
-                    if ((p.flags & OPB_LIN_ELU1) && c0 < p.elu_cols) {
+                    if ((flags & OPB_LIN_ELU1) && c0 < p.elu_cols) {
                         // 64 * (elu(x) + 1) = x > 0 ? vs + 64 : 64 exp(vs / 64) = ex2(vs * log2(e) / 64 + 6)
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
@@ -301,7 +312,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                             vv[i] = vv[i] > 0.f ? vv[i] + kScale : e;
                         }
                     }
-                    if (p.flags & OPB_LIN_CSTATS_RELU) {
+                    if (flags & OPB_LIN_CSTATS_RELU) {
                         // InstanceNorm1d on a value the caller has already centred through the bias (bias = b - analytic mean):
                         // (sum, sum of squares) of d over the valid rows, then ReLU -- the 1/std factor commutes with ReLU and is
                         // folded into the next layer's weights (op_scale_weight_planes), GATs_SuperGlue.py:144-146
@@ -316,7 +327,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
 #pragma unroll
                         for (int i = 0; i < 32; ++i) vv[i] = fmaxf(vv[i], 0.f);
                     }
-                    if (p.flags & OPB_LIN_ZSCALE) {                // Q'_h . Ksum_h of this row (linear attention normaliser, :97)
+                    if (flags & OPB_LIN_ZSCALE) {                // Q'_h . Ksum_h of this row (linear attention normaliser, :97)
                         const float4 *ks = reinterpret_cast<const float4 *>(s_bias + 256 + c0);
 #pragma unroll
                         for (int q = 0; q < 8; ++q) {
@@ -326,7 +337,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         }
                     }
                 }
-                if (p.flags & OPB_LIN_ZSCALE) {
+                if (flags & OPB_LIN_ZSCALE) {
                     const float z = p.zscale_num / (den * (1.f / kScale) + 1e-6f);
 #pragma unroll
                     for (int i = 0; i < 32; ++i) { v[0][i] *= z; v[1][i] *= z; }
@@ -335,8 +346,8 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 for (int cc = 0; cc < 2; ++cc) {
                     float *vv = v[cc];
                     const int c0 = col0 + cc * 32;
-                    if ((p.flags & OPB_LIN_RESIDUAL) && row_ok && !(p.dbg & 2)) {
-                        if (p.C) {                                   // x64 domain: vs += 64 * old
+                    if ((flags & OPB_LIN_RESIDUAL) && row_ok && !(dbg & 2)) {
+                        if (has_c) {                                   // x64 domain: vs += 64 * old
                             const float4 *src = reinterpret_cast<const float4 *>(p.C + grow * p.Cout + c0);
 #pragma unroll
                             for (int q = 0; q < 8; ++q) {
@@ -359,20 +370,20 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                             }
                         }
                     }
-                    if (p.flags & OPB_LIN_COLSUM) {                // column sums of the stored value over the valid rows (Ksum :97; means)
+                    if (flags & OPB_LIN_COLSUM) {                // column sums of the stored value over the valid rows (Ksum :97; means)
                         float s[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
                         const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
                         if (tile_ok) p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
                     }
-                    if (p.Ch) {
+                    if (has_p) {
                         uint32_t h[16], l[16];
                         split_planes32(vv, h, l);
                         stage_store(&tm_ch, c0, reinterpret_cast<const uint4 *>(h), b, row0);
                         stage_store(&tm_cl, c0, reinterpret_cast<const uint4 *>(l), b, row0);
                     }
-                    if (p.C) {
+                    if (has_c) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) vv[i] *= 1.f / kScale;
                         stage_store(&tm_c, c0, reinterpret_cast<const uint4 *>(vv), b, row0);
