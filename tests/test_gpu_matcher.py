@@ -103,6 +103,33 @@ def test_headline_shape_properties():
     assert torch.equal(pred["matches0"], pred["matches0_batched"][0])
 
 
+def test_config3_large_object_properties():
+    """BASELINE.json configs[2]: large object model, N2d=4096 vs N3d=32768 x 16 leaves (score-matrix-bound dual-softmax), 2 frames."""
+    hp = dict(synth.DEFAULT_HPARAMS)
+    w = synth.make_weights(0, damped=True)
+    obj = synth.make_object(1, 32768, 16)
+    frames = [synth.make_frame(obj, f, 4096) for f in range(2)]
+    m = _model(hp, w)
+    data = _cuda(synth.pack_batch(obj, frames))
+    pred, conf = m(data)
+    assert conf.shape == (2, 4096, 32768)
+    assert float(conf.min()) >= 0 and float(conf.max()) <= 1
+    assert float(conf.sum(2).max()) <= 1 + 1e-4 and float(conf.sum(1).max()) <= 1 + 1e-4
+    for b in range(2):
+        i0 = pred["matches0_batched"][b]; rows = torch.nonzero(i0 > -1)[:, 0]
+        assert len(rows) > 30, len(rows)
+        assert torch.equal(conf[b, rows].argmax(1), i0[rows])
+        assert torch.equal(conf[b][:, i0[rows]].argmax(0), rows)
+        i1 = pred["matches1_batched"][b]; cols = torch.nonzero(i1 > -1)[:, 0]
+        assert torch.equal(i0[i1[cols]], cols)                              # matches1 is the inverse map of matches0
+        planted = torch.from_numpy(frames[b].planted).cuda()
+        assert float((i0[rows] == planted[rows]).float().mean()) > 0.9
+    # a frame gives the same bits alone or inside the batch
+    m0 = pred["matches0_batched"][1].clone(); c1 = conf[1, :64].clone()
+    p1, cs = m(_cuda(synth.pack_batch(obj, frames[1:2])))
+    assert torch.equal(cs[0, :64], c1) and torch.equal(p1["matches0"], m0)
+
+
 def test_unshared_db_and_dtype_cast():
     """Per-frame DB copies (reference pack_data style) and non-fp32 inputs give the shared-DB result."""
     hp = dict(synth.DEFAULT_HPARAMS)
