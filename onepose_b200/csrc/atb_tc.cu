@@ -140,19 +140,22 @@ namespace atb {
 // per (head h, frame b): G_h = sum of chunk partials; Ksum_h = sum of column-sum partials;
 // KV_h[d,:] = (G_h[d,:] Wv_h^T + Ksum_h[d] bv_h^T) / M;  P_b[o, h*64+d] = sum_q KV_h[d,q] Wm[o, h*64+q], o < n_out, written as
 // split-precision planes (x64).  All folds in a fixed order.  One CTA owns a whole head, so the head's slices of WvT / WmT
-// (64 KB + 64..128 KB) cross L2 -> SM once per frame-head; 512 threads, G (64 KB) and KV' (17 KB) in shared memory.
+// (64 KB + 64..128 KB) cross L2 -> SM once per frame-head.  Both small GEMMs are register-blocked (4 x 4 and 4 x 8 outputs per
+// thread, operands as 128-bit loads: one shared-memory load per 8-11 FMAs, where the first version of this kernel needed one per 4
+// and was shared-memory bound at 100-120 us per call); 512 threads at <= 64 registers, two CTAs per SM (G^T 68 KB, KV'^T 17 KB).
 constexpr int kPostThreads = 512;
-constexpr int kPostSmem = (64 * 256 + 64 * 68 + 64) * 4 + 8 * 64 * 8;
-__global__ void __launch_bounds__(kPostThreads)
+constexpr int kGTStride = 68;                                 // floats per row of G^T / KV'^T: 16-byte aligned rows, conflict-free 128-bit column writes
+constexpr int kPostSmem = (256 * kGTStride + 64 * kGTStride + 64) * 4 + 8 * 64 * 8;
+__global__ void __launch_bounds__(kPostThreads, 2)
 k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
           const float *__restrict__ WvT /* [4][256 c][64 q] = Wv[h*64+q][c] */, const float *__restrict__ bv,
           const float *__restrict__ WmT /* [4][64 q][n_out o] = Wm[o][h*64+q] */, int n_out, float inv_m, float *__restrict__ ksum /* [B][256] */,
           float *__restrict__ kv_out /* [B][4][64][64] or null */, __half *__restrict__ Ph, __half *__restrict__ Pl) {
     extern __shared__ __align__(16) float post_smem[];
-    float (*G)[256] = reinterpret_cast<float (*)[256]>(post_smem);                        // [64 d][256 c]
-    float (*KV)[68] = reinterpret_cast<float (*)[68]>(post_smem + 64 * 256);              // [64 d][64 q] (+4 pad)
-    float *Ks = post_smem + 64 * 256 + 64 * 68;                                           // [64 d]
-    double (*Kslice)[64] = reinterpret_cast<double (*)[64]>(post_smem + 64 * 256 + 64 * 68 + 64);   // [8 slices][64 d]
+    float *GT = post_smem;                                                                // [256 c][68]: G^T, d contiguous
+    float *KVT = post_smem + 256 * kGTStride;                                             // [64 q][68]: KV'^T, d contiguous
+    float *Ks = KVT + 64 * kGTStride;                                                     // [64 d]
+    double (*Kslice)[64] = reinterpret_cast<double (*)[64]>(Ks + 64);                     // [8 slices][64 d]
     const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int ch0 = h * 64;                                     // first K' channel of this head
     {   // G fold: thread = (column c, half of the head's 64 rows), 32 independent loads in flight per chunk; chunks summed in order
@@ -166,12 +169,13 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
             for (int d = 0; d < 32; ++d) acc[d] += __ldg(src + d * 256);
         }
 #pragma unroll
-        for (int d = 0; d < 32; ++d) G[d0 + d][c] = acc[d];
+        for (int d = 0; d < 32; d += 4) *reinterpret_cast<float4 *>(&GT[c * kGTStride + d0 + d]) = make_float4(acc[d], acc[d + 1], acc[d + 2], acc[d + 3]);
     }
     {   // Ksum fold: 8 slices of the partial list per channel in float64, then the slices in order
         const int d = tid & 63, slice = tid >> 6;
         const int per = (nparts + 7) / 8, k0 = slice * per, k1 = min(nparts, k0 + per);
         double s = 0;
+#pragma unroll 8
         for (int k = k0; k < k1; ++k) s += (double)__ldg(&ksum_part[((long long)b * nparts + k) * 256 + ch0 + d].x);
         Kslice[slice][d] = s;
     }
@@ -183,57 +187,85 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
         Ks[tid] = (float)s;
         ksum[(long long)b * 256 + ch0 + tid] = (float)s;
     }
-    __syncthreads();
-    {   // KV[d][q]: thread = (q, group of 8 d); G rows are read four channels at a time (broadcast LDS.128)
-        const int q = tid & 63, d0 = (tid >> 6) * 8;
-        float acc[8];
+    {   // KV'[d][q] = sum_c G[d][c] Wv[q][c]: thread = (half of the c range, 4 d, 4 q); the two halves are added in order below
+        const int kh = tid >> 8, t = tid & 255, dg = t >> 4, qg = t & 15;
+        float acc[4][4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-        const float *w = WvT + (long long)h * 256 * 64 + q;          // coalesced over q
-#pragma unroll 2
-        for (int c = 0; c < 256; c += 4) {
-            const float w0 = __ldg(w + c * 64), w1 = __ldg(w + (c + 1) * 64), w2 = __ldg(w + (c + 2) * 64), w3 = __ldg(w + (c + 3) * 64);
+        for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float4 g4 = *reinterpret_cast<const float4 *>(&G[d0 + i][c]);
-                acc[i] = fmaf(g4.x, w0, acc[i]); acc[i] = fmaf(g4.y, w1, acc[i]); acc[i] = fmaf(g4.z, w2, acc[i]); acc[i] = fmaf(g4.w, w3, acc[i]);
-            }
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        const float4 *w = reinterpret_cast<const float4 *>(WvT + ((long long)h * 256 + kh * 128) * 64) + qg;      // 256 contiguous bytes per c over the q groups
+        const float *g = GT + (kh * 128) * kGTStride + 4 * dg;
+#pragma unroll 8
+        for (int c = 0; c < 128; ++c) {
+            const float4 w4 = __ldg(w + c * 16);
+            const float4 g4 = *reinterpret_cast<const float4 *>(g + c * kGTStride);
+            const float gv[4] = {g4.x, g4.y, g4.z, g4.w}, wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(gv[i], wv[j], acc[i][j]);
         }
-        const float bq = bv[h * 64 + q];
+        __syncthreads();                                        // every read of G^T is done (and Ks is visible): its first 16 KB become scratch
+        float *scr = GT + (dg * 16 + qg) * 16;                  // 16 floats per (dg, qg)
+        if (kh == 1) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float v = fmaf(Ks[d0 + i], bq, acc[i]) * inv_m;        // value / v_length, :93-94
-            KV[d0 + i][q] = v;
-            if (kv_out) kv_out[(((long long)b * 4 + h) * 64 + d0 + i) * 64 + q] = v;
+            for (int i = 0; i < 4; ++i) *reinterpret_cast<float4 *>(scr + 4 * i) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        }
+        __syncthreads();
+        if (kh == 0) {
+            const float4 bq4 = *reinterpret_cast<const float4 *>(bv + h * 64 + 4 * qg);
+            const float bq[4] = {bq4.x, bq4.y, bq4.z, bq4.w};
+            float v[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 o4 = *reinterpret_cast<const float4 *>(scr + 4 * i);
+                const float ov[4] = {o4.x, o4.y, o4.z, o4.w};
+                const float ks = Ks[4 * dg + i];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[i][j] = fmaf(ks, bq[j], acc[i][j] + ov[j]) * inv_m;        // value / v_length, :93-94
+                if (kv_out) *reinterpret_cast<float4 *>(kv_out + (((long long)b * 4 + h) * 64 + 4 * dg + i) * 64 + 4 * qg) = make_float4(v[i][0], v[i][1], v[i][2], v[i][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) *reinterpret_cast<float4 *>(&KVT[(4 * qg + j) * kGTStride + 4 * dg]) = make_float4(v[0][j], v[1][j], v[2][j], v[3][j]);
         }
     }
     __syncthreads();
-    for (int o = tid; o < n_out; o += kPostThreads) {   // P[o][ch0 + d], thread = o, 16 d at a time
-        float wm[64];
+    {   // P[o][ch0 + d] = sum_q Wm[o][h*64+q] KV'[d][q]: thread = (4 o, 8 d), 256 o per pass
+        const int og = tid >> 3, dg = tid & 7;
+        for (int ob = 0; ob < n_out; ob += 256) {
+            const int o0 = ob + 4 * og;
+            float acc[4][8];
 #pragma unroll
-        for (int q = 0; q < 64; ++q) wm[q] = __ldg(WmT + ((long long)h * 64 + q) * n_out + o);     // coalesced over o
-#pragma unroll 1
-        for (int dg = 0; dg < 4; ++dg) {
-            uint32_t hh[8], ll[8];
+            for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int d = 0; d < 16; d += 2) {
-                const float *k0p = KV[dg * 16 + d], *k1p = KV[dg * 16 + d + 1];
-                float a0 = 0.f, a1 = 0.f;
+                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+            const float *wm = WmT + (long long)h * 64 * n_out + o0;                    // + q * n_out; 16 contiguous bytes, 128 per 8 threads' worth of o
+            const float *kv = KVT + 8 * dg;
+#pragma unroll 4
+            for (int q = 0; q < 64; ++q) {
+                const float4 w4 = __ldg(reinterpret_cast<const float4 *>(wm + (long long)q * n_out));
+                const float4 ka = *reinterpret_cast<const float4 *>(kv + q * kGTStride), kb = *reinterpret_cast<const float4 *>(kv + q * kGTStride + 4);
+                const float wv[4] = {w4.x, w4.y, w4.z, w4.w}, kk[8] = {ka.x, ka.y, ka.z, ka.w, kb.x, kb.y, kb.z, kb.w};
 #pragma unroll
-                for (int q = 0; q < 64; q += 4) {
-                    const float4 k0 = *reinterpret_cast<const float4 *>(k0p + q), k1 = *reinterpret_cast<const float4 *>(k1p + q);
-                    a0 = fmaf(k0.x, wm[q], a0); a0 = fmaf(k0.y, wm[q + 1], a0); a0 = fmaf(k0.z, wm[q + 2], a0); a0 = fmaf(k0.w, wm[q + 3], a0);
-                    a1 = fmaf(k1.x, wm[q], a1); a1 = fmaf(k1.y, wm[q + 1], a1); a1 = fmaf(k1.z, wm[q + 2], a1); a1 = fmaf(k1.w, wm[q + 3], a1);
-                }
-                __half h0, l0, h1, l1;
-                tc::split_f16(a0 * 64.f, h0, l0); tc::split_f16(a1 * 64.f, h1, l1);
-                hh[d / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
-                ll[d / 2] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(wv[i], kk[j], acc[i][j]);
             }
-            uint4 *ph = reinterpret_cast<uint4 *>(Ph + ((long long)b * n_out + o) * 256 + ch0 + dg * 16);
-            uint4 *pl = reinterpret_cast<uint4 *>(Pl + ((long long)b * n_out + o) * 256 + ch0 + dg * 16);
-            ph[0] = make_uint4(hh[0], hh[1], hh[2], hh[3]); ph[1] = make_uint4(hh[4], hh[5], hh[6], hh[7]);
-            pl[0] = make_uint4(ll[0], ll[1], ll[2], ll[3]); pl[1] = make_uint4(ll[4], ll[5], ll[6], ll[7]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                uint32_t hh[4], ll[4];
+#pragma unroll
+                for (int j = 0; j < 8; j += 2) {
+                    __half h0, l0, h1, l1;
+                    tc::split_f16(acc[i][j] * 64.f, h0, l0); tc::split_f16(acc[i][j + 1] * 64.f, h1, l1);
+                    hh[j / 2] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+                    ll[j / 2] = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+                }
+                const long long e = ((long long)b * n_out + o0 + i) * 256 + ch0 + 8 * dg;
+                *reinterpret_cast<uint4 *>(Ph + e) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+                *reinterpret_cast<uint4 *>(Pl + e) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+            }
         }
     }
 }
