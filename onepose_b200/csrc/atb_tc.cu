@@ -145,7 +145,14 @@ namespace atb {
 // and was shared-memory bound at 100-120 us per call); 512 threads at <= 64 registers, two CTAs per SM (G^T 68 KB, KV'^T 17 KB).
 constexpr int kPostThreads = 512;
 constexpr int kGTStride = 68;                                 // floats per row of G^T / KV'^T: 16-byte aligned rows, conflict-free 128-bit column writes
-constexpr int kPostSmem = (256 * kGTStride + 64 * kGTStride + 64) * 4 + 8 * 64 * 8;
+constexpr int kWRing = 2 * 2 * 16 * 64;                        // floats: 2 stages x 2 halves of the c range x 16 c x 64 q of Wv^T
+constexpr int kPostSmem = (256 * kGTStride + 64 * kGTStride + 64 + kWRing) * 4 + 8 * 64 * 8;
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tc::smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __global__ void __launch_bounds__(kPostThreads, 2)
 k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restrict__ ksum_part, int nparts,
           const float *__restrict__ WvT /* [4][256 c][64 q] = Wv[h*64+q][c] */, const float *__restrict__ bv,
@@ -156,6 +163,7 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
     float *KVT = post_smem + 256 * kGTStride;                                             // [64 q][68]: KV'^T, d contiguous
     float *Ks = KVT + 64 * kGTStride;                                                     // [64 d]
     double (*Kslice)[64] = reinterpret_cast<double (*)[64]>(Ks + 64);                     // [8 slices][64 d]
+    float *Wring = Ks + 64 + 8 * 64 * 2;                                                  // [2 stages][2 halves][16 c][64 q]
     const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int ch0 = h * 64;                                     // first K' channel of this head
     {   // G fold: thread = (column c, half of the head's 64 rows), 32 independent loads in flight per chunk; chunks summed in order
@@ -194,17 +202,29 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-        const float4 *w = reinterpret_cast<const float4 *>(WvT + ((long long)h * 256 + kh * 128) * 64) + qg;      // 256 contiguous bytes per c over the q groups
+        // Wv^T streams through a two-stage cp.async ring, 16 c per half and stage (every thread copies 16 bytes per stage): the weights
+        // come from L2, and loading them straight into registers left their latency exposed (ncu: 45 % of the samples on long_sb)
+        const float *wsrc = WvT + ((long long)h * 256 + kh * 128) * 64 + 4 * t;         // + 1024 floats per stage
+        float *wdst = Wring + kh * 1024 + 4 * t;                                         // + 2048 floats per stage parity
         const float *g = GT + (kh * 128) * kGTStride + 4 * dg;
-#pragma unroll 8
-        for (int c = 0; c < 128; ++c) {
-            const float4 w4 = __ldg(w + c * 16);
-            const float4 g4 = *reinterpret_cast<const float4 *>(g + c * kGTStride);
-            const float gv[4] = {g4.x, g4.y, g4.z, g4.w}, wv[4] = {w4.x, w4.y, w4.z, w4.w};
+        cp_async16(wdst, wsrc); cp_async_commit();
+        for (int st = 0; st < 8; ++st) {
+            if (st + 1 < 8) cp_async16(wdst + ((st + 1) & 1) * 2048, wsrc + (st + 1) * 1024);
+            cp_async_commit();
+            cp_async_wait<1>();
+            __syncthreads();                                    // stage st has landed for every thread
+            const float *wr = Wring + (st & 1) * 2048 + kh * 1024 + 4 * qg;
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int cc = 0; cc < 16; ++cc) {
+                const float4 w4 = *reinterpret_cast<const float4 *>(wr + cc * 64);
+                const float4 g4 = *reinterpret_cast<const float4 *>(g + (st * 16 + cc) * kGTStride);
+                const float gv[4] = {g4.x, g4.y, g4.z, g4.w}, wv[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(gv[i], wv[j], acc[i][j]);
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(gv[i], wv[j], acc[i][j]);
+            }
+            __syncthreads();                                    // stage st may be overwritten by the copy issued in the next iteration
         }
         __syncthreads();                                        // every read of G^T is done (and Ks is visible): its first 16 KB become scratch
         float *scr = GT + (dg * 16 + qg) * 16;                  // 16 floats per (dg, qg)
@@ -240,11 +260,24 @@ k_kv_post(const float *__restrict__ partial, int nchunks, const float2 *__restri
             for (int i = 0; i < 4; ++i)
 #pragma unroll
                 for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-            const float *wm = WmT + (long long)h * 64 * n_out + o0;                    // + q * n_out; 16 contiguous bytes, 128 per 8 threads' worth of o
+            // this pass's slice of Wm^T (64 q x 256 o, 64 KB) is copied into the G^T area, which is dead by now
+            __syncthreads();                                    // the previous pass (or the scratch of the KV' stage) is done with it
+            {
+                const float *src = WmT + (long long)h * 64 * n_out + ob;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int e = (i * kPostThreads + tid) * 4, q = e >> 8, o = e & 255;
+                    cp_async16(GT + e, src + (long long)q * n_out + o);
+                }
+                cp_async_commit();
+                cp_async_wait<0>();
+            }
+            __syncthreads();
+            const float *wm = GT + 4 * og;                                             // + 256 q
             const float *kv = KVT + 8 * dg;
 #pragma unroll 4
             for (int q = 0; q < 64; ++q) {
-                const float4 w4 = __ldg(reinterpret_cast<const float4 *>(wm + (long long)q * n_out));
+                const float4 w4 = *reinterpret_cast<const float4 *>(wm + q * 256);
                 const float4 ka = *reinterpret_cast<const float4 *>(kv + q * kGTStride), kb = *reinterpret_cast<const float4 *>(kv + q * kGTStride + 4);
                 const float wv[4] = {w4.x, w4.y, w4.z, w4.w}, kk[8] = {ka.x, ka.y, ka.z, ka.w, kb.x, kb.y, kb.z, kb.w};
 #pragma unroll
