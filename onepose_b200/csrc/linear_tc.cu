@@ -290,12 +290,13 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     // CTA pairs (cta_group::2) by default; OPB_LINEAR_CG=1 selects the one-CTA-per-tile form of the same kernel (A/B runs)
     static const int cg = [] { const char *e = getenv("OPB_LINEAR_CG"); return (e && e[0] == '1') ? 1 : 2; }();
     const int wbox = lintc::BN / cg;                  // rows of a W block one CTA loads
-    if ((rc = make_tmap_f16_3d(&ta1h, A1h, B, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, B, rows_per_batch, K1, lintc::BM)) ||
+    const int a1b = (flags & OPB_LIN_A1_BCAST) ? 1 : B, a2b = (flags & OPB_LIN_A2_BCAST) ? 1 : B;
+    if ((rc = make_tmap_f16_3d(&ta1h, A1h, a1b, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, a1b, rows_per_batch, K1, lintc::BM)) ||
         (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)) ||
         (rc = make_tmap_f16_3d(&twl, Wl, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)))
         return rc;
     if (K2) {
-        if ((rc = make_tmap_f16_3d(&ta2h, A2h, B, rows_per_batch, K2, lintc::BM)) || (rc = make_tmap_f16_3d(&ta2l, A2l, B, rows_per_batch, K2, lintc::BM)))
+        if ((rc = make_tmap_f16_3d(&ta2h, A2h, a2b, rows_per_batch, K2, lintc::BM)) || (rc = make_tmap_f16_3d(&ta2l, A2l, a2b, rows_per_batch, K2, lintc::BM)))
             return rc;
     } else {
         ta2h = ta1h; ta2l = ta1l;
@@ -321,6 +322,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     p.bias = bias; p.C = C; p.Ch = (__half *)Ch; p.Cl = (__half *)Cl; p.stats = (float2 *)stats_partial;
     p.ksum = ksum; p.zscale_num = zscale_num; p.w_batched = (flags & OPB_LIN_WBATCHED) ? 1 : 0;
     p.w2 = W2h ? ((flags & OPB_LIN_W2BATCHED) ? 2 : 1) : 0;
+    p.a_bcast = ((flags & OPB_LIN_A1_BCAST) ? 1 : 0) | ((flags & OPB_LIN_A2_BCAST) ? 2 : 0);
     static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
     const int groups = sm_count() / cg;                                   // persistent CTAs (or CTA pairs), one per SM

@@ -54,6 +54,7 @@ struct Params {
     const float *ksum;             // ZSCALE: [B][Cout] per-frame Ksum; every 64-column head of a row is divided by (row_head . ksum_head + 1e-6)
     float zscale_num;              // ZSCALE numerator: the source length M of :94,98 (z = M / (q.ksum + 1e-6))
     int w_batched;                 // W planes are [B][Cout][K] (one matrix per frame)
+    int a_bcast;                   // bit 0: A1 is one [1, rows, K1] tensor read by every frame; bit 1: the same for A2
     int w2;                        // 0: W spans K1+K2 columns; 1: the A2 part has its own weight W2 [Cout][K2]; 2: W2 is [B][Cout][K2]
 };
 
@@ -160,6 +161,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     uint8_t *st = smem + stage * STAGE_BYTES;
                     const bool second = kb >= nkb1;
                     const int ka = (second ? kb - nkb1 : kb) * BK;
+                    const int ab = (p.a_bcast >> (second ? 1 : 0)) & 1 ? 0 : b;   // an operand shared by all frames ([1, rows, K])
                     const bool own_w2 = second && p.w2;                    // the A2 part multiplies its own (per-frame) weight
                     const int kw = own_w2 ? ka : kb * BK;
                     const int wb = own_w2 ? (p.w2 == 2 ? b : 0) : (p.w_batched ? b : 0);
@@ -168,17 +170,17 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         // both CTAs load into their own shared memory; the bytes of both are credited to the leader's barriers
                         const uint32_t fh = tc::mapa(tc::smem_u32(&bar->full_hi[stage]), 0), fl = tc::mapa(tc::smem_u32(&bar->full_lo[stage]), 0);
                         if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_hi[stage], 2 * HALF_BYTES);
-                        tc::tma_load_3d_cg2(st, second ? &tm_a2h : &tm_a1h, fh, ka, rt * BM, b);
+                        tc::tma_load_3d_cg2(st, second ? &tm_a2h : &tm_a1h, fh, ka, rt * BM, ab);
                         tc::tma_load_3d_cg2(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, fh, kw, wrow, wb);
                         if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_lo[stage], 2 * HALF_BYTES);
-                        tc::tma_load_3d_cg2(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, fl, ka, rt * BM, b);
+                        tc::tma_load_3d_cg2(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, fl, ka, rt * BM, ab);
                         tc::tma_load_3d_cg2(st + HALF_BYTES + A_PLANE, own_w2 ? &tm_w2l : &tm_wl, fl, kw, wrow, wb);
                     } else {
                         tc::mbar_arrive_expect_tx(&bar->full_hi[stage], HALF_BYTES);
-                        tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, b);
+                        tc::tma_load_3d(st, second ? &tm_a2h : &tm_a1h, &bar->full_hi[stage], ka, rt * BM, ab);
                         tc::tma_load_3d(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, &bar->full_hi[stage], kw, wrow, wb);
                         tc::mbar_arrive_expect_tx(&bar->full_lo[stage], HALF_BYTES);
-                        tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, b);
+                        tc::tma_load_3d(st + HALF_BYTES, second ? &tm_a2l : &tm_a1l, &bar->full_lo[stage], ka, rt * BM, ab);
                         tc::tma_load_3d(st + HALF_BYTES + A_PLANE, own_w2 ? &tm_w2l : &tm_wl, &bar->full_lo[stage], kw, wrow, wb);
                     }
                 }

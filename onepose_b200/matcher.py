@@ -315,15 +315,19 @@ class GATsSuperGlue(nn.Module):
              ptr(P[0]), ptr(P[1]), stream_ptr())
         return ksum, P
 
-    def _propagate_tc(self, st, M, ksum, P, lw, shared_src=False):
+    def _propagate_tc(self, st, M, ksum, P, lw, shared_src=False, x_in=None):
         """x-side of AttentionPropagation on the tensor cores; the stream state st (planes st.p, column sums st.xs, and the
         fp32 copy st.x when one is kept) is updated in place.
         With Q'' = Q' M / (Q'_h . Ksum_h + 1e-6)  (:97-98):  message = Q'' P_b^T + bm  (:119), and the MLP's first
         layer sees it only through W0b, so  h = W0a x + P'_b Q'' + const  -- the merge projection is never run.
         InstanceNorm + ReLU (:144-146) without a normalisation pass: the mean is analytic (column sums of x and Q'' through
         W0a / P'_b), layer 0 writes relu(h - mean) as planes, 1/std is folded into per-frame layer-1 weights.
-        st.ch names the stream ("2" / "3"): its scratch buffers are its own, the two may run concurrently."""
-        B, N, ch, x_p = st.B, st.N, st.ch, st.p
+        st.ch names the stream ("2" / "3"): its scratch buffers are its own, the two may run concurrently.
+        x_in: planes [1, N, 256] of a stream that is still the same for every frame (the shared 3D prefix at its first per-frame
+        layer): the GEMMs read it as a broadcast operand (OPB_LIN_A1_BCAST / A2_BCAST) and write the per-frame result to st.p, so
+        the B-fold copy of the prefix is never made."""
+        B, N, ch, x_p = st.B, st.N, st.ch, (x_in if x_in is not None else st.p)
+        b1, b2 = (2048, 4096) if x_in is not None else (0, 0)
         dev = x_p[0].device
         parts = lib.op_linear_tc_stat_parts(N)
         if shared_src:          # one source (ksum [1,256], P'_b [1,512,256]) for all B frames: P' is an ordinary weight
@@ -333,14 +337,14 @@ class GATsSuperGlue(nn.Module):
             pflag = 512                                                                                           # W2BATCHED
         q_p = self._planes("q" + ch, (B, N, _D), dev)
         qs = self._ws.get("qpart" + ch, (B, parts, _D, 2), torch.float32, dev)
-        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 16 | 32, elu_cols=_D, stats=qs, ksum=ksum, zscale_num=M,
+        self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 16 | 32 | b1, elu_cols=_D, stats=qs, ksum=ksum, zscale_num=M,
                         tag="q")                                                                                  # ELU1 | COLSUM | ZSCALE
         cb = self._ws.get("cbias" + ch, (B, 2 * _D), torch.float32, dev)
         call("op_mlp_center_bias", ptr(st.xs), st.parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cb),
              stream_ptr())
         hn_p = self._planes("hn" + ch, (B, N, 2 * _D), dev)
         stats = self._ws.get("tcstats" + ch, (B, parts, 2 * _D, 2), torch.float32, dev)
-        self._linear_tc(x_p, lw["W0a_p"], cb, B, N, A2=q_p, W2=P, Cp=hn_p, flags=128 | 256 | pflag, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
+        self._linear_tc(x_p, lw["W0a_p"], cb, B, N, A2=q_p, W2=P, Cp=hn_p, flags=128 | 256 | pflag | b1, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
         W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
         call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
              stream_ptr())
@@ -349,7 +353,7 @@ class GATsSuperGlue(nn.Module):
             # prefetched TMA pipeline as a second operand instead of being fetched by the epilogue (exposed latency); the
             # identity's planes are exact (64, 0), so the tensor core reproduces hi + lo of x to fp32 rounding.  In place: a
             # row tile is read completely (all MMAs retired) before its epilogue stores, and Cout = 256 is one column tile.
-            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._identity_planes(dev), Cp=x_p, flags=16 | 64 | 1024, stats=st.xs,
+            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._identity_planes(dev), Cp=st.p, flags=16 | 64 | 1024 | b2, stats=st.xs,
                             tag="mlp1", work_k=2 * _D)                                                                      # COLSUM | WBATCHED | W2_EXACT_HI
         else:   # an fp32 copy is kept (with_linear_transform): residual add onto it in the epilogue
             self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
@@ -477,8 +481,9 @@ class GATsSuperGlue(nn.Module):
         side.wait_stream(main)
         ev2 = ev3 = None                 # end of the last cross-layer update of the 2D / 3D stream
 
-        def broadcast3():
-            s3.p[0].copy_(s3s.p[0].expand(B, N3, _D)); s3.p[1].copy_(s3s.p[1].expand(B, N3, _D))
+        def broadcast3(planes=True):
+            if planes:
+                s3.p[0].copy_(s3s.p[0].expand(B, N3, _D)); s3.p[1].copy_(s3s.p[1].expand(B, N3, _D))
             s3.xs.copy_(s3s.xs.expand_as(s3.xs))
             s3.parts = s3s.parts
             if s3.x is not None:
@@ -510,9 +515,12 @@ class GATsSuperGlue(nn.Module):
                         ev2 = side.record_event()
                     main.wait_event(e2)
                     if single3:                                   # from here on the 3D stream is per frame
-                        broadcast3()
+                        lazy = s3.x is None                       # planes-only stream: the prefix is read as a broadcast operand
+                        broadcast3(planes=not lazy)
                         single3 = False
-                    self._propagate_tc(s3, N2, *k2, lw)
+                        self._propagate_tc(s3, N2, *k2, lw, x_in=s3s.p if lazy else None)
+                    else:
+                        self._propagate_tc(s3, N2, *k2, lw)
                     ev3 = main.record_event()
                 else:
                     with torch.cuda.stream(side):
