@@ -155,6 +155,8 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":      # its banner goes to stdout, in front of the JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
 
@@ -318,7 +320,7 @@ def run_ours(args):
             "roofline": roofline,
             "roofline_sim_dual_softmax": None if sim is None else dict(
                 {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
-                traffic=(traffic.get("op_sim_dual_softmax") or {}).get("traffic_bytes"),
+                traffic=(traffic.get("op_sim_dual_softmax_rows") or traffic.get("op_sim_dual_softmax") or {}).get("traffic_bytes"),
                 # the similarity is computed twice (statistics pass, write pass), three fp16 MMAs per product each time
                 tensor_issued_tflops=2 * 3 * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12,
                 tensor_frac_issued=2 * 3 * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12 / peaks["tensor"]),

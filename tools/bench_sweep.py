@@ -31,7 +31,9 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
     side = None
     if world > 1:
-        dist.init_process_group("nccl")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":      # its banner goes to stdout, in front of the JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
         side = dist.new_group(backend="gloo")
     model = GATsSuperGlue(dict(synth.DEFAULT_HPARAMS)).cuda().eval()
     model.load_state_dict(synth.make_weights(0, damped=True), strict=True)
