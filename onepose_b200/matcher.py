@@ -125,6 +125,12 @@ class GATsSuperGlue(nn.Module):
         self.use_tensor_cores = True
         self.two_streams = True      # 2D / 3D streams of a layer on two CUDA streams (tensor-core path)
         self._side = {}
+        # Pipelines only (off by default: the drop-in contract returns a pose that is ready on the caller's stream).  True: gather +
+        # PnP of a call run on the module's pose stream, so that the (latency-bound, few-CTA) RANSAC of one block of frames overlaps
+        # the matcher of the next; ``pred["pose_event"]`` is recorded behind them and ``wait_pose(pred)`` makes the current stream
+        # wait for it.  Work that consumes the pose can also be enqueued on ``pose_stream(device)`` directly.
+        self.pnp_overlap = False
+        self._pose_streams = {}
 
     # ------------------------------------------------------------------ weights in kernel layout
     def _weights_key(self):
@@ -208,6 +214,25 @@ class GATsSuperGlue(nn.Module):
         if s is None:
             s = self._side[dev.index] = torch.cuda.Stream(device=dev)
         return s
+
+    def pose_stream(self, dev):
+        dev = torch.device(dev)
+        s = self._pose_streams.get(dev.index)
+        if s is None:
+            s = self._pose_streams[dev.index] = torch.cuda.Stream(device=dev)
+        return s
+
+    @staticmethod
+    def wait_pose(pred):
+        """With ``pnp_overlap``: makes the current stream wait for the pose of this ``pred`` (no host synchronisation)."""
+        ev = pred.get("pose_event")
+        if ev is not None:
+            cur = torch.cuda.current_stream(pred["pose"].device)
+            cur.wait_event(ev)
+            for k in _POSE_KEYS:
+                if k in pred:
+                    pred[k].record_stream(cur)
+        return pred
 
     def _planes(self, name, shape, dev):
         return (self._ws.get(name + ".hi", shape, torch.float16, dev), self._ws.get(name + ".lo", shape, torch.float16, dev))
@@ -608,8 +633,20 @@ class GATsSuperGlue(nn.Module):
         K = data.get("query_intrinsic", data.get("K"))
         if K is not None:
             from . import pnp
-            pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
+            if self.pnp_overlap:
+                main, ps = torch.cuda.current_stream(dev), self.pose_stream(dev)
+                ps.wait_stream(main)                                  # the matches are complete
+                with torch.cuda.stream(ps):
+                    pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
+                    for t in (i0, s0, kpts2d, kpts3d):                # read on the pose stream after the caller may have dropped them
+                        t.record_stream(ps)
+                    pred["pose_event"] = ps.record_event()
+            else:
+                pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
         return pred, conf
+
+
+_POSE_KEYS = ("mkpts2d", "mkpts3d", "mconf", "n_matches", "match_query_idx", "pose", "inliers", "n_inliers", "ransac_iters")
 
 
 class _StreamState:

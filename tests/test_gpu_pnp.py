@@ -134,3 +134,32 @@ def test_end_to_end_pose_vs_oracle_pipeline():
         assert r_err < R_TOL_DEG and t_err < T_TOL_CM
         r_gt, t_gt = po.pose_error(pred["pose"][b].cpu().numpy(), fr.pose_gt)
         assert r_gt < 1.0 and t_gt < 1.0
+
+
+@pytest.mark.gpu
+def test_pose_stream_overlap_gives_the_same_poses():
+    """GATsSuperGlue.pnp_overlap: gather + PnP on the module's pose stream (pipelined with the next call's matcher) -- same bits."""
+    import torch
+    from onepose_b200 import synth
+    from onepose_b200.matcher import GATsSuperGlue
+    m = GATsSuperGlue(dict(synth.DEFAULT_HPARAMS)).cuda().eval()
+    m.load_state_dict(synth.make_weights(0, damped=True), strict=True)
+    obj = synth.make_object(4, 1024, 4)
+    batches = []
+    for k in range(3):
+        frames = [synth.make_frame(obj, 10 * k + f, 512) for f in range(4)]
+        d = {a: (torch.as_tensor(b).cuda() if not isinstance(b, torch.Tensor) else b.cuda()) for a, b in synth.pack_batch(obj, frames).items()}
+        d["query_intrinsic"] = torch.as_tensor(frames[0].K).cuda()
+        batches.append(d)
+    ref = []
+    for d in batches:
+        pred, _ = m(d)
+        ref.append({k: pred[k].clone() for k in ("pose", "n_inliers", "n_matches", "inliers")})
+    assert int(ref[0]["n_inliers"].min()) > 10
+    m.pnp_overlap = True
+    preds = [m(d)[0] for d in batches]              # three calls in flight, no synchronisation in between
+    for pred, r in zip(preds, ref):
+        assert "pose_event" in pred
+        GATsSuperGlue.wait_pose(pred)
+        for k, v in r.items():
+            assert torch.equal(pred[k], v), k
