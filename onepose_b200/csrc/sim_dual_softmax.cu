@@ -7,6 +7,7 @@
 // conf = (e/R_n)*(e/C_m) to HBM exactly once and keeps per-row / per-column (max, argmax) as packed
 // 64-bit keys (value bits high, inverted index low => ties resolve to the smallest index).  All
 // cross-tile reductions go through per-tile partials folded in a fixed order (deterministic).
+#include <cstring>
 #include <stdlib.h>
 #include "common.cuh"
 #include "sim_tc.cuh"
@@ -301,23 +302,39 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
     } else {
         // split fp32 unit rows into scaled fp16 hi/lo planes, describe them to TMA, run the two tcgen05 passes
         const long long n2e = (long long)B * N2 * kD, n3e = (long long)B * N3 * kD;
-        if (normalize) {
-            simtc::k_normalize_split_planes<<<ceil_div((long long)B * N2, 8), 256, 0, st>>>(m2, w.m2h, w.m2l, (long long)B * N2, simtc::kOperandScale);
-            simtc::k_normalize_split_planes<<<ceil_div((long long)B * N3, 8), 256, 0, st>>>(m3, w.m3h, w.m3l, (long long)B * N3, simtc::kOperandScale);
+        // One CTA per row tile pair by default (cta_group::2, M256 x N256 tiles): each CTA keeps its 128 query rows resident and stages half
+        // of every B k-block, which halves the L2 -> SM stream that bounds the one-CTA form (OPB_SIM_CG=1, M128 x N128).  In the pair form
+        // the two cross terms of the split-precision product run as fp8 MMAs (OPB_SIM_MMA=f16 keeps three fp16 MMAs per product).
+        static const int cg = [] { const char *e = getenv("OPB_SIM_CG"); return (e && e[0] == '1') ? 1 : 2; }();
+        static const int f8 = [] { const char *e = getenv("OPB_SIM_MMA"); return (e && !strcmp(e, "f16")) ? 0 : 1; }() && cg == 2;
+        // fp8 mode: the 2-byte lo area holds the e5m2 lo plane (first half) and the e4m3 hi plane (second half)
+        uint8_t *m2x = (uint8_t *)w.m2l + (size_t)B * N2 * kD, *m3x = (uint8_t *)w.m3l + (size_t)B * N3 * kD;
+        const long long r2 = (long long)B * N2, r3 = (long long)B * N3;
+        if (normalize && f8) {
+            simtc::k_normalize_split_planes<1><<<ceil_div(r2, 8), 256, 0, st>>>(m2, w.m2h, w.m2l, m2x, r2, simtc::kOperandScale);
+            simtc::k_normalize_split_planes<1><<<ceil_div(r3, 8), 256, 0, st>>>(m3, w.m3h, w.m3l, m3x, r3, simtc::kOperandScale);
+        } else if (normalize) {
+            simtc::k_normalize_split_planes<0><<<ceil_div(r2, 8), 256, 0, st>>>(m2, w.m2h, w.m2l, m2x, r2, simtc::kOperandScale);
+            simtc::k_normalize_split_planes<0><<<ceil_div(r3, 8), 256, 0, st>>>(m3, w.m3h, w.m3l, m3x, r3, simtc::kOperandScale);
+        } else if (f8) {
+            simtc::k_split_planes<1><<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, m2x, n2e, simtc::kOperandScale);
+            simtc::k_split_planes<1><<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, m3x, n3e, simtc::kOperandScale);
         } else {
-            simtc::k_split_planes<<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, n2e, simtc::kOperandScale);
-            simtc::k_split_planes<<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, n3e, simtc::kOperandScale);
+            simtc::k_split_planes<0><<<ceil_div(n2e / 4, 256), 256, 0, st>>>(m2, w.m2h, w.m2l, m2x, n2e, simtc::kOperandScale);
+            simtc::k_split_planes<0><<<ceil_div(n3e / 4, 256), 256, 0, st>>>(m3, w.m3h, w.m3l, m3x, n3e, simtc::kOperandScale);
         }
         OPB_CHECK_LAUNCH();
-        CUtensorMap t2h, t2l, t3h, t3l, tconf;
+        CUtensorMap t2h, t2l, t2x, t3h, t3l, t3x, tconf;
         int rc;
-        // CTA pairs (cta_group::2, M256 x N256 tiles) by default: each CTA keeps its 128 query rows resident and stages half of every
-        // B k-block, which halves the L2 -> SM stream that bounds the one-CTA form.  Measured at the headline shape (64 frames):
-        // pair 1.02 + 1.48 ms, single (OPB_SIM_CG=1, M128 x N128) 1.27 + 1.74 ms.
-        static const int cg = [] { const char *e = getenv("OPB_SIM_CG"); return (e && e[0] == '1') ? 1 : 2; }();
-        if ((rc = make_tmap_f16_3d(&t2h, w.m2h, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) ||
-            (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, 128)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, 128)))
-            return rc;
+        if ((rc = make_tmap_f16_3d(&t2h, w.m2h, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t3h, w.m3h, B, N3, kD, 128))) return rc;
+        if (f8) {
+            if ((rc = make_tmap_u8_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) || (rc = make_tmap_u8_3d(&t2x, m2x, B, N2, kD, simtc::BM)) ||
+                (rc = make_tmap_u8_3d(&t3l, w.m3l, B, N3, kD, 128)) || (rc = make_tmap_u8_3d(&t3x, m3x, B, N3, kD, 128)))
+                return rc;
+        } else {
+            if ((rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, 128))) return rc;
+            t2x = t2l; t3x = t3l;
+        }
         const int tiles_n = ceil_div(N3, 128 * cg);          // column tiles of the tensor-core passes: 128 wide, 256 for a CTA pair
         // enough CTAs for ~2 waves over 148 SMs: split the column tiles when frames x row tiles is small
         int splits = ceil_div(2 * 148, (long long)B * p.tiles_m);
@@ -337,10 +354,12 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
         q.rowmax_part = w.rowmax_part; q.colmax_part = w.colmax_part; q.conf = conf;
         static bool configured = false;
         if (!configured) {
-            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
-            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
-            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
-            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<1, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
+            OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc::k_sim_tc<2, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc::SMEM_BYTES));
             configured = true;
         }
         cudaLaunchConfig_t cfg = {};
@@ -352,13 +371,15 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = cg; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
-        if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 2>, t2h, t2l, t3h, t3l, tconf, q));
-        else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 1>, t2h, t2l, t3h, t3l, tconf, q));
+        if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+        else if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+        else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<1, 1, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
         k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, tiles_n * 2, N2, w.invR, 1);
         k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum_part, p.tiles_m, N3, w.invC, 1);
         OPB_CHECK_LAUNCH();
-        if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 2>, t2h, t2l, t3h, t3l, tconf, q));
-        else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 1>, t2h, t2l, t3h, t3l, tconf, q));
+        if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+        else if (cg == 2) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+        else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc::k_sim_tc<2, 1, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
     }
     k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, row_parts, N2, N3, w.idx0, w.val0, tensor_cores ? conf : nullptr);
     k_sim_finalize_max<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colmax_part, p.tiles_m, N3, N2, w.idx1, w.val1, nullptr);

@@ -1,17 +1,18 @@
 // tcgen05 / TMA version of the similarity + dual-softmax passes (included by sim_dual_softmax.cu).
 //
-// One CTA owns 128 query rows of one frame and walks a range of 128-column tiles of the 3D points.
-//   warp 4   : TMA producer.  The CTA's A operand (128 rows x K=256, fp16 hi and lo planes, 128 KB) is loaded once
-//              and stays resident; B (3D descriptors) streams through a ring of five 16 KB units, one unit =
-//              one 64-wide k-block of one plane (hi or lo) of a 128-column tile.
-//   warp 5   : TMEM allocation + single-thread tcgen05.mma issue.  Per k-block: Ah*Bh, Al*Bh on the hi unit,
-//              Ah*Bl on the lo unit (split precision, see tc_common.cuh); fp32 accumulators are double-buffered
-//              in TMEM (2 x 128 columns) so the epilogue of tile j overlaps the MMAs of tile j+1.
-//   warps 0-3: epilogue.  Thread = one query row (TMEM lane).  e = exp2(acc*c1 - c0) with the fixed shift
-//              1/scale (|cos| <= 1).  PASS 1 keeps the row sum in a register and reduces column sums across the
-//              128 rows with a shuffle transpose-reduce; PASS 2 writes conf = (e/R)(e/C) once, 512 contiguous
-//              bytes per thread, and tracks row / column maxima as packed (value, inverted index) keys.
+// A CTA owns 128 query rows of one frame; by default two CTAs form a pair (cta_group::2) that walks 256-column tiles of the 3D
+// points with M256 x N256 MMAs (CG = 2); CG = 1 is the one-CTA form on 128-column tiles.
+//   warp 8   : TMA producer.  The CTA's A operand (128 rows x K=256, 128 KB of planes) is loaded once and stays resident; B (3D
+//              descriptors) streams through a ring of four 16 KB units (a unit = 128 columns x 128 bytes of one plane; in a pair
+//              each CTA stages its half of the tile's columns and both CTAs' bytes are credited to the leader's barrier).
+//   warp 9   : TMEM allocation + single-thread tcgen05.mma issue (the pair's leader only).  fp32 accumulators are double-buffered in
+//              TMEM (2 x 128 / 2 x 256 columns) so the epilogue of tile j overlaps the MMAs of tile j+1.
+//   warps 0-7: epilogue.  Thread = one query row (TMEM lane), warp = (lane quadrant, column half).  e = exp2(acc*c1 - c0) with the
+//              fixed shift 1/scale (|cos| <= 1).  PASS 1 keeps the row sum in a register and reduces column sums across the 128
+//              rows with a shuffle transpose-reduce; PASS 2 writes conf = (e/R)(e/C) once through swizzled staging + TMA stores and
+//              tracks row maxima (16-column blocks) and column maxima (transposed read of the staged block).
 #pragma once
+#include <cuda_fp8.h>
 #include "tc_common.cuh"
 
 namespace opb {
@@ -95,11 +96,17 @@ __device__ __forceinline__ unsigned long long transpose_reduce_max(unsigned long
     return v[0];
 }
 
-template <int PASS, int CG>
+// F8 = 0: a product is three kind::f16 MMAs, hi*hi + lo*hi + hi*lo on fp16 planes (tm_*l = the lo planes, tm_*x unused).
+// F8 = 1 (pair form only): hi*hi on the fp16 hi planes plus the two cross terms as kind::f8f6f4 MMAs at twice the rate,
+//         lo(e5m2) * hi(e4m3) + hi(e4m3) * lo(e5m2) on byte planes (tm_*l = lo as e5m2, tm_*x = hi as e4m3, [B, N, 256] bytes).  The cross
+//         terms are 2^-11 of the product, so 3 mantissa bits keep the cosine to 5.4e-6 (1.6e-4 on conf; CPU emulation and
+//         tests/test_gpu_matcher.py) at two thirds of the tensor work and the same operand bytes.
+template <int PASS, int CG, int F8>
 __global__ void __launch_bounds__(320, 1)
-k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l,
-         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l,
+k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l, const __grid_constant__ CUtensorMap tm_m2x,
+         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l, const __grid_constant__ CUtensorMap tm_m3x,
          const __grid_constant__ CUtensorMap tm_conf, const Params p) {
+    static_assert(!F8 || CG == 2, "the fp8 cross terms are implemented for the pair form");
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment (SWIZZLE_128B) by an offset on the shared array, so accesses stay in the shared address space (LDS/STS)
     uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -129,6 +136,7 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     if (warp == 9) { if (CG == 2) tc::tmem_alloc_cg2<Cfg::TMEM_COLS>(&bar->tmem_base); else tc::tmem_alloc<Cfg::TMEM_COLS>(&bar->tmem_base); }
     if (warp == 8 && lane == 0) {
         tc::tma_prefetch_desc(&tm_m2h); tc::tma_prefetch_desc(&tm_m2l); tc::tma_prefetch_desc(&tm_m3h); tc::tma_prefetch_desc(&tm_m3l);
+        if (F8) { tc::tma_prefetch_desc(&tm_m2x); tc::tma_prefetch_desc(&tm_m3x); }
         if (PASS == 2 && p.tma_store) tc::tma_prefetch_desc(&tm_conf);
     }
     tc::tcgen05_fence_before();
@@ -138,7 +146,27 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
 
     if (warp == 8) {
         // ================= TMA producer =================
-        if (lane == 0) {
+        if (lane == 0 && F8) {
+            // A resident: hi fp16 (4 k-blocks of 64, 64 KB), then lo e5m2 and hi e4m3 (2 k-blocks of 128 bytes each, 32 + 32 KB).
+            // B ring, 8 units of 16 KB per tile: 4 x hi fp16, 2 x hi e4m3, 2 x lo e5m2
+            const uint32_t af = tc::mapa(tc::smem_u32(&bar->a_full), 0);
+            if (rank == 0) tc::mbar_arrive_expect_tx(&bar->a_full, 2 * A_BYTES);
+            for (int kb = 0; kb < NKB; ++kb) tc::tma_load_3d_cg2(sA + kb * TILE_BYTES, &tm_m2h, af, kb * 64, m0, b);
+            for (int j = 0; j < 2; ++j) tc::tma_load_3d_cg2(sA + (4 + j) * TILE_BYTES, &tm_m2l, af, j * 128, m0, b);
+            for (int j = 0; j < 2; ++j) tc::tma_load_3d_cg2(sA + (6 + j) * TILE_BYTES, &tm_m2x, af, j * 128, m0, b);
+            uint32_t u = 0;
+            for (int t = t0; t < t1; ++t)
+                for (int q = 0; q < 8; ++q, ++u) {
+                    const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
+                    tc::mbar_wait(&bar->b_empty[stage], ph ^ 1);
+                    if (rank == 0) tc::mbar_arrive_expect_tx(&bar->b_full[stage], 2 * UNIT_BYTES);
+                    const CUtensorMap *tm = q < 4 ? &tm_m3h : (q < 6 ? &tm_m3x : &tm_m3l);
+                    const int c0 = q < 4 ? q * 64 : (q & 1) * 128;
+                    tc::tma_load_3d_cg2(sB + stage * UNIT_BYTES, tm, tc::mapa(tc::smem_u32(&bar->b_full[stage]), 0), c0,
+                                        t * BN + (int)rank * Cfg::B_ROWS, b);
+                }
+        }
+        if (lane == 0 && !F8) {
             if (CG == 2) {
                 // both CTAs load into their own shared memory; the bytes of both are credited to the leader's barriers
                 const uint32_t af = tc::mapa(tc::smem_u32(&bar->a_full), 0);
@@ -185,7 +213,26 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
                 tc::mbar_wait(&bar->acc_empty[as], aph ^ 1);
                 tc::tcgen05_fence_after();
                 const uint32_t d = tmem_base + as * BN;
-                for (int kb = 0; kb < NKB; ++kb)
+                if (F8) {
+                    constexpr uint32_t id_lh = tc::umma_idesc_f8(BM * CG, BN, tc::kF8E5M2, tc::kF8E4M3);     // A lo (e5m2) x B hi (e4m3)
+                    constexpr uint32_t id_hl = tc::umma_idesc_f8(BM * CG, BN, tc::kF8E4M3, tc::kF8E5M2);     // A hi (e4m3) x B lo (e5m2)
+                    for (int q = 0; q < 8; ++q, ++u) {
+                        const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
+                        tc::mbar_wait(&bar->b_full[stage], ph);
+                        tc::tcgen05_fence_after();
+                        const uint64_t bd = tc::umma_desc_k128(b_base + stage * UNIT_BYTES);
+                        // A block q: hi fp16 k-block q (q < 4); lo e5m2 half q - 4 against B hi e4m3; hi e4m3 half q - 6 against B lo e5m2
+                        const uint64_t ad = tc::umma_desc_k128(a_base + q * TILE_BYTES);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {            // 32 bytes per k-step: 16 fp16 or 32 bytes of fp8
+                            if (p.dbg & 8) continue;
+                            if (q < 4) tc::umma_f16_cg2(d, ad + 2 * k, bd + 2 * k, idesc, (q | k) != 0);
+                            else tc::umma_f8_cg2(d, ad + 2 * k, bd + 2 * k, q < 6 ? id_lh : id_hl, 1);
+                        }
+                        commit(&bar->b_empty[stage]);
+                    }
+                }
+                for (int kb = 0; kb < (F8 ? 0 : NKB); ++kb)
                     for (int plane = 0; plane < 2; ++plane, ++u) {
                         const uint32_t stage = u % UNITS, ph = (u / UNITS) & 1;
                         tc::mbar_wait(&bar->b_full[stage], ph);
@@ -368,21 +415,35 @@ k_sim_tc(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUt
     if (warp == 9) { if (CG == 2) tc::tmem_dealloc_cg2<Cfg::TMEM_COLS>(tmem_base); else tc::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
 }
 
-// fp32 rows -> scaled fp16 hi / lo planes
-__global__ void k_split_planes(const float *__restrict__ x, __half *__restrict__ hi, __half *__restrict__ lo, long long n, float scale) {
+// Operand planes of a row-major fp32 tensor, x scaled by `scale`: hi = fp16(x), lo = fp16(x - hi).
+// F8 = 0: hi and lo as fp16 arrays.  F8 = 1: hi as fp16, lo as e5m2 bytes (`lo`), hi as e4m3 bytes (`hx`) for the fp8 cross terms.
+template <int F8>
+__device__ __forceinline__ void store_planes(float xs, long long i, __half *hi, void *lo, uint8_t *hx) {
+    __half h, l;
+    tc::split_f16(xs, h, l);
+    hi[i] = h;
+    if (F8) {
+        reinterpret_cast<uint8_t *>(lo)[i] = (uint8_t)__nv_cvt_float_to_fp8(__half2float(l), __NV_SATFINITE, __NV_E5M2);
+        hx[i] = (uint8_t)__nv_cvt_float_to_fp8(__half2float(h), __NV_SATFINITE, __NV_E4M3);
+    } else {
+        reinterpret_cast<__half *>(lo)[i] = l;
+    }
+}
+
+template <int F8>
+__global__ void k_split_planes(const float *__restrict__ x, __half *__restrict__ hi, void *__restrict__ lo, uint8_t *__restrict__ hx, long long n, float scale) {
     const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (i >= n) return;
     const float4 v = *reinterpret_cast<const float4 *>(x + i);
-    __half h[4], l[4];
-    tc::split_f16(v.x * scale, h[0], l[0]); tc::split_f16(v.y * scale, h[1], l[1]);
-    tc::split_f16(v.z * scale, h[2], l[2]); tc::split_f16(v.w * scale, h[3], l[3]);
-    *reinterpret_cast<uint2 *>(hi + i) = *reinterpret_cast<uint2 *>(h);
-    *reinterpret_cast<uint2 *>(lo + i) = *reinterpret_cast<uint2 *>(l);
+    store_planes<F8>(v.x * scale, i, hi, lo, hx); store_planes<F8>(v.y * scale, i + 1, hi, lo, hx);
+    store_planes<F8>(v.z * scale, i + 2, hi, lo, hx); store_planes<F8>(v.w * scale, i + 3, hi, lo, hx);
 }
 
 // F.normalize (x / max(|x|, 1e-12), GATs_SuperGlue.py:245-246) fused into the operand split: one warp per 256-wide row, the same
 // summation order and quotient as k_l2_normalize_rows, so the planes are bit-identical to normalising first and splitting after
-__global__ void k_normalize_split_planes(const float *__restrict__ x, __half *__restrict__ hi, __half *__restrict__ lo, long long rows, float scale) {
+template <int F8>
+__global__ void k_normalize_split_planes(const float *__restrict__ x, __half *__restrict__ hi, void *__restrict__ lo, uint8_t *__restrict__ hx,
+                                         long long rows, float scale) {
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
     const int lane = threadIdx.x & 31;
@@ -394,12 +455,7 @@ __global__ void k_normalize_split_planes(const float *__restrict__ x, __half *__
     for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     const float den = fmaxf(sqrtf(ss), 1e-12f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        __half h, l;
-        tc::split_f16((v[k] / den) * scale, h, l);
-        hi[row * 256 + lane + 32 * k] = h;
-        lo[row * 256 + lane + 32 * k] = l;
-    }
+    for (int k = 0; k < 8; ++k) store_planes<F8>((v[k] / den) * scale, row * 256 + lane + 32 * k, hi, lo, hx);
 }
 
 }  // namespace simtc

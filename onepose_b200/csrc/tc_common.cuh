@@ -196,6 +196,24 @@ __device__ __forceinline__ void umma_commit_cg2(uint64_t *bar) {
                  : "memory");
 }
 
+// kind::f8f6f4: 8-bit operands (K = 32 per instruction, the same 32 bytes per k-step as 16 fp16), fp32 accumulation at twice the
+// kind::f16 rate.  Operand formats of the instruction descriptor: 0 = e4m3, 1 = e5m2.  Used for the two cross terms of a
+// split-precision product, which only need 3-4 significant bits (sim_tc.cuh).
+constexpr uint32_t kF8E4M3 = 0, kF8E5M2 = 1;
+__host__ __device__ constexpr uint32_t umma_idesc_f8(int M, int N, uint32_t a_fmt, uint32_t b_fmt) {
+    return (1u << 4) | (a_fmt << 7) | (b_fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_f8_cg2(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile(
@@ -225,6 +243,8 @@ __device__ __forceinline__ void split_f16(float x, __half &hi, __half &lo) {
 // host: tensor map of an fp16 [batch, rows, cols] row-major array, box = {64 cols, box_rows, 1}, 128-byte swizzle.
 // Out-of-range rows are zero-filled, so ragged row counts need no special casing in the kernels.
 int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// host: tensor map of a byte [batch, rows, cols] row-major array (fp8 planes), box = {128 bytes, box_rows, 1}, 128-byte swizzle
+int make_tmap_u8_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // host: tensor map of an fp32 [batch, rows, cols] row-major array for TMA stores, box = {16 cols, box_rows, 1}, 64-byte swizzle
 // (cols must be a multiple of 4: global strides are multiples of 16 bytes).
 int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
