@@ -329,13 +329,18 @@ def run_ours(args):
             "roofline_sim_dual_softmax": None if sim is None else dict(
                 {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
                 traffic=(traffic.get("op_sim_dual_softmax_rows") or traffic.get("op_sim_dual_softmax") or {}).get("traffic_bytes"),
-                # the similarity is computed twice (statistics pass, write pass), three fp16 MMAs per product each time
-                tensor_issued_tflops=2 * 3 * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12,
-                tensor_frac_issued=2 * 3 * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12 / peaks["tensor"]),
+                # the similarity is computed twice (statistics pass, write pass); a product is one fp16 MMA plus two fp8 MMAs at twice
+                # the rate (= 2 fp16-equivalent passes; 3 with OPB_SIM_MMA=f16 / OPB_SIM_CG=1)
+                mma_passes_fp16_equivalent=SIM_MMA_UNITS,
+                tensor_issued_tflops=2 * SIM_MMA_UNITS * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12,
+                tensor_frac_issued=2 * SIM_MMA_UNITS * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12 / peaks["tensor"]),
             "cpu_baseline": cpu, "clocks": clk, "kernels": kernels, "sanity": sanity,
         }))
     if world > 1:
         dist.destroy_process_group()
+
+
+SIM_MMA_UNITS = 3 if (os.environ.get("OPB_SIM_MMA") == "f16" or os.environ.get("OPB_SIM_CG") == "1") else 2
 
 
 def main():
