@@ -31,9 +31,17 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
     side = None
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":      # its banner goes to stdout, in front of the JSON line
-            os.environ["NCCL_DEBUG"] = "WARN"
-        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
+        sys.stdout.flush()                 # the "NCCL version ..." banner of communicator creation goes to stdout: send it to stderr
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
         side = dist.new_group(backend="gloo")
     model = GATsSuperGlue(dict(synth.DEFAULT_HPARAMS)).cuda().eval()
     model.load_state_dict(synth.make_weights(0, damped=True), strict=True)
