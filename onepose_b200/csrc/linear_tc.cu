@@ -88,7 +88,8 @@ k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__
         const int parts = r < 4 ? xparts : qparts;
         const int kk = (r & 3) * 64 + j;
         double s = 0;
-        for (int t = sl; t < parts; t += 4) s += (double)src[((long long)b * parts + t) * 256 + kk].x;
+#pragma unroll 8
+        for (int t = sl; t < parts; t += 4) s += (double)__ldg(&src[((long long)b * parts + t) * 256 + kk].x);
         red[sl][j] = (float)s;
     }
     __syncthreads();
@@ -98,14 +99,15 @@ k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__
     cluster.sync();                                       // nobody leaves (or reuses red) while its means are still being read
     const int c = r * 64 + j;
     float acc = 0.f;
-#pragma unroll 8
+#pragma unroll 16
     for (int k = sl * 64; k < sl * 64 + 64; ++k) acc = fmaf(__ldg(W0aT + (long long)k * 512 + c), mean_in[k], acc);
     red[sl][j] = acc;
     {   // P' rows of this CTA: warp w takes rows 8w .. 8w+7, lane l the 8 columns 8l .. 8l+7 of both planes
         const int warp = tid >> 5, lane = tid & 31;
         const float4 m0 = *reinterpret_cast<const float4 *>(mean_in + 256 + lane * 8), m1 = *reinterpret_cast<const float4 *>(mean_in + 260 + lane * 8);
         const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-        for (int i = 0; i < 8; ++i) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {                         // unrolled: the 16 loads of a warp's rows are in flight together
             const long long off = (((long long)(p_batched ? b : 0) * 512) + r * 64 + warp * 8 + i) * 256 + lane * 8;
             const uint4 h4 = __ldg(reinterpret_cast<const uint4 *>(Ph + off)), l4 = __ldg(reinterpret_cast<const uint4 *>(Pl + off));
             const __half2 *hh = reinterpret_cast<const __half2 *>(&h4), *ll = reinterpret_cast<const __half2 *>(&l4);
@@ -130,21 +132,29 @@ k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__
 __global__ void __launch_bounds__(256)
 k_instnorm_scale_weight_planes(const float2 *__restrict__ part, int parts, int rows, float eps, const float *__restrict__ W,
                                int Cout, int K, __half *__restrict__ hi, __half *__restrict__ lo, float *__restrict__ rstd_out) {
-    __shared__ double red_s[4][64], red_q[4][64];
+    __shared__ double red_s[16][64], red_q[16][64];
     __shared__ float rs[64];
-    const int b = blockIdx.x, g = blockIdx.y, tid = threadIdx.x, j = tid & 63, sl = tid >> 6;
-    {
-        double s = 0, q = 0;
-        for (int t = sl; t < parts; t += 4) {
-            const float2 v = part[((long long)b * parts + t) * K + g * 64 + j];
-            s += (double)v.x; q += (double)v.y;
+    const int b = blockIdx.x, g = blockIdx.y, tid = threadIdx.x;
+    {   // thread = (slice of 16, 4 channels): 32-byte loads, many in flight (four slices of scalar loads were a chain of L2 round trips)
+        const int fs = tid >> 4, f4 = (tid & 15) * 4;
+        double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+        const float4 *p4 = reinterpret_cast<const float4 *>(part + (long long)b * parts * K + g * 64 + f4);
+#pragma unroll 4
+        for (int t = fs; t < parts; t += 16) {
+            const float4 a = __ldg(p4 + (long long)t * (K / 2)), c = __ldg(p4 + (long long)t * (K / 2) + 1);
+            s[0] += (double)a.x; q[0] += (double)a.y; s[1] += (double)a.z; q[1] += (double)a.w;
+            s[2] += (double)c.x; q[2] += (double)c.y; s[3] += (double)c.z; q[3] += (double)c.w;
         }
-        red_s[sl][j] = s; red_q[sl][j] = q;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { red_s[fs][f4 + i] = s[i]; red_q[fs][f4 + i] = q[i]; }
     }
     __syncthreads();
     if (tid < 64) {
-        const double mu = (red_s[0][tid] + red_s[1][tid] + red_s[2][tid] + red_s[3][tid]) / rows;
-        double var = (red_q[0][tid] + red_q[1][tid] + red_q[2][tid] + red_q[3][tid]) / rows - mu * mu;
+        double ss = 0, qq = 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { ss += red_s[k][tid]; qq += red_q[k][tid]; }
+        const double mu = ss / rows;
+        double var = qq / rows - mu * mu;
         if (var < 0) var = 0;
         rs[tid] = (float)(1.0 / sqrt(var + (double)eps));
         if (rstd_out) rstd_out[(long long)b * K + g * 64 + tid] = rs[tid];
