@@ -167,7 +167,10 @@ int op_l2_normalize_rows(const float *x, float *out, long long rows, int C, void
  * m2 [B,N2,256], m3 [B,N3,256] unit rows.  conf[b,n,m] = softmax_n(s)*softmax_m(s), s = m2.m3/scale.
  * Pass 1 accumulates the row/column exp sums, pass 2 recomputes the tile and writes conf exactly
  * once, tracking row/column maxima; the selection kernel applies the mutual / threshold logic.
- * Outputs are batched: matches0 [B,N2] int64, matches1 [B,N3] int64, scores0 [B,N2], scores1 [B,N3]. */
+ * Outputs are batched: matches0 [B,N2] int64, matches1 [B,N3] int64, scores0 [B,N2], scores1 [B,N3].
+ * Tensor-core form: CTA pairs (cta_group::2) on 256 x 256 tiles; a product is one fp16 MMA (hi*hi) plus the two cross terms as fp8
+ * MMAs (lo e5m2 x hi e4m3): conf within 3e-4 of float64 (bound 1e-3).  Environment switches for A/B runs only: OPB_SIM_MMA=f16
+ * (three fp16 MMAs per product, conf within 6e-5), OPB_SIM_CG=1 (one CTA per 128 x 128 tile). */
 size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3);
 int op_sim_dual_softmax(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
                         float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
