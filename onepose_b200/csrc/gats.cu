@@ -109,10 +109,15 @@ __device__ __forceinline__ void f4_to_planes(const float4 &v, uint2 &h, uint2 &l
 // ELU through MUFU.EX2 (absolute error ~2e-7, below the 22-bit planes the result is stored in)
 __device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : tc::ex2(x * 1.4426950408889634f) - 1.f; }
 
+// LT > 0: the number of leaves is a compile-time constant (8 and 16, the shipped object models), so the loops over the leaves are
+// unrolled four at a time without a remainder loop (the 64-register budget of two 512-thread blocks per SM does not allow more);
+// LT = 0 takes L at run time.
+template <int LT>
 __global__ void __launch_bounds__(kGatsPW * kGatsFW * 32, 2)
 k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh, __half *xl, const float *__restrict__ v1,
-              const float *__restrict__ v2, float2 *__restrict__ colsum, int B, int N3, int L, float alpha, int include_self,
+              const float *__restrict__ v2, float2 *__restrict__ colsum, int B, int N3, int Lrt, float alpha, int include_self,
               int add_self) {
+    const int L = LT > 0 ? LT : Lrt;
     extern __shared__ float4 smem4[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pt = warp % kGatsPW, fw = warp / kGatsPW;       // point of the block, frame way
@@ -174,6 +179,7 @@ k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh
             const float w_self = p_self / denom;
             o0 = make_float4(w_self * h0.x, w_self * h0.y, w_self * h0.z, w_self * h0.w);
             o1 = make_float4(w_self * h1.x, w_self * h1.y, w_self * h1.z, w_self * h1.w);
+#pragma unroll 4
             for (int j = 0; j < L; ++j) {
                 const float a = __shfl_sync(0xffffffffu, pr, j);
                 const float4 x0 = sl[j * 64 + lane], x1 = sl[j * 64 + 32 + lane];
@@ -256,14 +262,19 @@ extern "C" int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_b
     OPB_CHECK_ARG(L >= 1 && L <= 24, "op_gats_leaf_aggregate_planes: num_leaf=%d not in [1,24]", L);   // leaves + fold buffers within 227 KB
     if (B == 0 || N3 == 0) return OPB_OK;
     const size_t smem = ((size_t)opb::kGatsPW * L + 2 * opb::kGatsFW * opb::kGatsPW) * opb::kD * sizeof(float);
-    static thread_local size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(opb::k_gats_planes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
-    const int grid = opb::ceil_div(N3, opb::kGatsPW);
-    opb::k_gats_planes<<<grid, opb::kGatsPW * opb::kGatsFW * 32, smem, (cudaStream_t)stream>>>(leaf, leaf_bstride, (__half *)xh, (__half *)xl, v1, v2,
-                                                                               (float2 *)colsum_partial, B, N3, L, alpha, include_self, add_self);
+    auto launch = [&](auto kern) -> cudaError_t {
+        if (smem > 48 * 1024) {                       // cheap; the limit is per kernel instantiation
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        const int grid = opb::ceil_div(N3, opb::kGatsPW);
+        kern<<<grid, opb::kGatsPW * opb::kGatsFW * 32, smem, (cudaStream_t)stream>>>(leaf, leaf_bstride, (__half *)xh, (__half *)xl, v1, v2,
+                                                                                 (float2 *)colsum_partial, B, N3, L, alpha, include_self, add_self);
+        return cudaSuccess;
+    };
+    if (L == 8) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8>));
+    else if (L == 16) OPB_CHECK_CUDA(launch(opb::k_gats_planes<16>));
+    else OPB_CHECK_CUDA(launch(opb::k_gats_planes<0>));
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }
