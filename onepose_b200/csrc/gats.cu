@@ -172,11 +172,12 @@ k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh
             if (lane >= L) e = -INFINITY;
             float m = warp_max(e);
             if (include_self) m = fmaxf(m, e_self);
-            float pr = lane < L ? expf(e - m) : 0.f;
-            const float p_self = include_self ? expf(e_self - m) : 0.f;
-            const float denom = warp_sum(pr) + p_self;
-            pr = pr / denom;
-            const float w_self = p_self / denom;
+            // softmax weights through MUFU.EX2 and one reciprocal (2 ulp; the result is stored in 22-bit planes)
+            float pr = lane < L ? tc::ex2((e - m) * 1.4426950408889634f) : 0.f;
+            const float p_self = include_self ? tc::ex2((e_self - m) * 1.4426950408889634f) : 0.f;
+            const float inv = 1.f / (warp_sum(pr) + p_self);
+            pr = pr * inv;
+            const float w_self = p_self * inv;
             o0 = make_float4(w_self * h0.x, w_self * h0.y, w_self * h0.z, w_self * h0.w);
             o1 = make_float4(w_self * h1.x, w_self * h1.y, w_self * h1.z, w_self * h1.w);
 #pragma unroll 4
