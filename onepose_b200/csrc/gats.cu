@@ -100,11 +100,14 @@ __device__ __forceinline__ void planes_to_f4(const uint2 &h, const uint2 &l, flo
     const float2 l0 = __half22float2(*reinterpret_cast<const __half2 *>(&l.x)), l1 = __half22float2(*reinterpret_cast<const __half2 *>(&l.y));
     o = make_float4((h0.x + l0.x) * (1.f / 64.f), (h0.y + l0.y) * (1.f / 64.f), (h1.x + l1.x) * (1.f / 64.f), (h1.y + l1.y) * (1.f / 64.f));
 }
+// packed conversions (cvt.rn.f16x2.f32): the same values as tc::split_f16 element by element, three fifths of the instructions
 __device__ __forceinline__ void f4_to_planes(const float4 &v, uint2 &h, uint2 &l) {
-    __half a[4], b[4];
-    tc::split_f16(v.x * 64.f, a[0], b[0]); tc::split_f16(v.y * 64.f, a[1], b[1]);
-    tc::split_f16(v.z * 64.f, a[2], b[2]); tc::split_f16(v.w * 64.f, a[3], b[3]);
-    h = *reinterpret_cast<const uint2 *>(a); l = *reinterpret_cast<const uint2 *>(b);
+    const float s0 = v.x * 64.f, s1 = v.y * 64.f, s2 = v.z * 64.f, s3 = v.w * 64.f;
+    const __half2 h01 = __floats2half2_rn(s0, s1), h23 = __floats2half2_rn(s2, s3);
+    const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
+    const __half2 l01 = __floats2half2_rn(s0 - f01.x, s1 - f01.y), l23 = __floats2half2_rn(s2 - f23.x, s3 - f23.y);
+    h = make_uint2(*reinterpret_cast<const uint32_t *>(&h01), *reinterpret_cast<const uint32_t *>(&h23));
+    l = make_uint2(*reinterpret_cast<const uint32_t *>(&l01), *reinterpret_cast<const uint32_t *>(&l23));
 }
 // ELU through MUFU.EX2 (absolute error ~2e-7, below the 22-bit planes the result is stored in)
 __device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : tc::ex2(x * 1.4426950408889634f) - 1.f; }
