@@ -115,12 +115,15 @@ __device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : tc::ex
 // LT > 0: the number of leaves is a compile-time constant (8 and 16, the shipped object models), so the loops over the leaves are
 // unrolled four at a time without a remainder loop (the 64-register budget of two 512-thread blocks per SM does not allow more);
 // LT = 0 takes L at run time.
-template <int LT>
+// FL >= 0: include_self (bit 0) and add_self (bit 1) are compile-time constants too (FL = 1 is the shipped layer).
+template <int LT, int FL>
 __global__ void __launch_bounds__(kGatsPW * kGatsFW * 32, 2)
 k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh, __half *xl, const float *__restrict__ v1,
-              const float *__restrict__ v2, float2 *__restrict__ colsum, int B, int N3, int Lrt, float alpha, int include_self,
-              int add_self) {
+              const float *__restrict__ v2, float2 *__restrict__ colsum, int B, int N3, int Lrt, float alpha, int include_self_rt,
+              int add_self_rt) {
     const int L = LT > 0 ? LT : Lrt;
+    const bool include_self = FL >= 0 ? (FL & 1) != 0 : include_self_rt != 0;
+    const bool add_self = FL >= 0 ? (FL & 2) != 0 : add_self_rt != 0;
     extern __shared__ float4 smem4[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pt = warp % kGatsPW, fw = warp / kGatsPW;       // point of the block, frame way
@@ -276,9 +279,11 @@ extern "C" int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_b
                                                                                  (float2 *)colsum_partial, B, N3, L, alpha, include_self, add_self);
         return cudaSuccess;
     };
-    if (L == 8) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8>));
-    else if (L == 16) OPB_CHECK_CUDA(launch(opb::k_gats_planes<16>));
-    else OPB_CHECK_CUDA(launch(opb::k_gats_planes<0>));
+    const bool shipped = include_self && !add_self;
+    if (L == 8 && shipped) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8, 1>));
+    else if (L == 16 && shipped) OPB_CHECK_CUDA(launch(opb::k_gats_planes<16, 1>));
+    else if (L == 8) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8, -1>));
+    else OPB_CHECK_CUDA(launch(opb::k_gats_planes<0, -1>));
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }
