@@ -84,6 +84,7 @@ int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_bstride, voi
 #define OPB_LIN_W2BATCHED 512 /* op_linear_tc: the second weight W2 is [B, Cout, K2], one matrix per frame */
 #define OPB_LIN_A1_BCAST 2048 /* op_linear_tc: A1 is [1, rows, K1], the same rows for every frame (e.g. the shared 3D stream at its first per-frame layer) */
 #define OPB_LIN_A2_BCAST 4096 /* op_linear_tc: the same for A2 */
+#define OPB_LIN_W2_IDENTITY 8192 /* op_linear_tc: W2 is the 256 x 256 identity (planes (64, 0); K2 = Cout = 256): C = epi(A1 . W^T + A2).  The pair form then issues the A2 part as N = 64 MMAs on the diagonal blocks only (a quarter of the tensor work of the residual) */
 #define OPB_LIN_W2_EXACT_HI 1024 /* op_linear_tc: W2's lo plane is all zeros (e.g. the identity of the in-GEMM residual add): its MMA pass is skipped */
 int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
               float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,

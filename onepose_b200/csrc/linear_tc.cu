@@ -311,9 +311,12 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     } else {
         ta2h = ta1h; ta2l = ta1l;
     }
+    const bool w2_ident = (flags & OPB_LIN_W2_IDENTITY) && cg == 2;
+    OPB_CHECK_ARG(!(flags & OPB_LIN_W2_IDENTITY) || (W2h && K2 == 256 && Cout == 256 && !(flags & OPB_LIN_W2BATCHED)),
+                  "op_linear_tc: W2_IDENTITY needs unbatched W2 planes with K2 = Cout = 256");
     if (W2h) {
         const int wb = (flags & OPB_LIN_W2BATCHED) ? B : 1;
-        if ((rc = make_tmap_f16_3d(&tw2h, W2h, wb, Cout, K2, wbox)) || (rc = make_tmap_f16_3d(&tw2l, W2l, wb, Cout, K2, wbox))) return rc;
+        if ((rc = make_tmap_f16_3d(&tw2h, W2h, wb, Cout, K2, w2_ident ? 32 : wbox)) || (rc = make_tmap_f16_3d(&tw2l, W2l, wb, Cout, K2, wbox))) return rc;
     } else {
         tw2h = twh; tw2l = twl;
     }
@@ -332,6 +335,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     p.bias = bias; p.C = C; p.Ch = (__half *)Ch; p.Cl = (__half *)Cl; p.stats = (float2 *)stats_partial;
     p.ksum = ksum; p.zscale_num = zscale_num; p.w_batched = (flags & OPB_LIN_WBATCHED) ? 1 : 0;
     p.w2 = W2h ? ((flags & OPB_LIN_W2BATCHED) ? 2 : 1) : 0;
+    p.w2_ident = w2_ident ? 1 : 0;
     p.a_bcast = ((flags & OPB_LIN_A1_BCAST) ? 1 : 0) | ((flags & OPB_LIN_A2_BCAST) ? 2 : 0);
     static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;

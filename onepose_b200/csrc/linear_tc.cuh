@@ -54,6 +54,7 @@ struct Params {
     const float *ksum;             // ZSCALE: [B][Cout] per-frame Ksum; every 64-column head of a row is divided by (row_head . ksum_head + 1e-6)
     float zscale_num;              // ZSCALE numerator: the source length M of :94,98 (z = M / (q.ksum + 1e-6))
     int w_batched;                 // W planes are [B][Cout][K] (one matrix per frame)
+    int w2_ident;                  // pair form: W2 is the 256 x 256 identity (planes (64, 0)); the A2 part is issued as N = 64 MMAs on its diagonal blocks
     int a_bcast;                   // bit 0: A1 is one [1, rows, K1] tensor read by every frame; bit 1: the same for A2
     int w2;                        // 0: W spans K1+K2 columns; 1: the A2 part has its own weight W2 [Cout][K2]; 2: W2 is [B][Cout][K2]
 };
@@ -169,6 +170,16 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     if (CG == 2) {
                         // both CTAs load into their own shared memory; the bytes of both are credited to the leader's barriers
                         const uint32_t fh = tc::mapa(tc::smem_u32(&bar->full_hi[stage]), 0), fl = tc::mapa(tc::smem_u32(&bar->full_lo[stage]), 0);
+                        if (second && p.w2_ident) {
+                            // residual through the identity: only the diagonal 64 x 64 block of this k-block multiplies anything.  Each CTA
+                            // stages 32 of its rows (4 KB, tm_w2h has a 32-row box), the lo plane of the identity is never loaded
+                            if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_hi[stage], 2 * (A_PLANE + 32 * 128));
+                            tc::tma_load_3d_cg2(st, &tm_a2h, fh, ka, rt * BM, ab);
+                            tc::tma_load_3d_cg2(st + A_PLANE, &tm_w2h, fh, ka, ka + 32 * (int)rank, 0);
+                            if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_lo[stage], 2 * A_PLANE);
+                            tc::tma_load_3d_cg2(st + HALF_BYTES, &tm_a2l, fl, ka, rt * BM, ab);
+                            continue;
+                        }
                         if (rank == 0) tc::mbar_arrive_expect_tx(&bar->full_hi[stage], 2 * HALF_BYTES);
                         tc::tma_load_3d_cg2(st, second ? &tm_a2h : &tm_a1h, fh, ka, rt * BM, ab);
                         tc::tma_load_3d_cg2(st + A_PLANE, own_w2 ? &tm_w2h : &tm_wh, fh, kw, wrow, wb);
@@ -210,6 +221,19 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     tc::mbar_wait(&bar->full_hi[stage], ph);
                     tc::tcgen05_fence_after();
                     if (p.dbg & 4) { tc::mbar_wait(&bar->full_lo[stage], ph); commit(&bar->empty[stage]); continue; }
+                    if (CG == 2 && p.w2_ident && kb >= nkb1) {
+                        // x_new[:, 64 j .. 64 j + 63] += (hi + lo) of x's k-block j: two N = 64 MMAs per k-step instead of two N = 256 ones
+                        constexpr uint32_t idesc64 = tc::umma_idesc_f16(BM * CG, 64);
+                        const uint32_t d64 = d + (uint32_t)(kb - nkb1) * 64;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) tc::umma_f16_cg2(d64, ah + 2 * k, wh + 2 * k, idesc64, 1);
+                        tc::mbar_wait(&bar->full_lo[stage], ph);
+                        tc::tcgen05_fence_after();
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) tc::umma_f16_cg2(d64, al + 2 * k, wh + 2 * k, idesc64, 1);
+                        commit(&bar->empty[stage]);
+                        continue;
+                    }
 #pragma unroll
                     for (int k = 0; k < 4; ++k) mma(d, ah + 2 * k, wh + 2 * k, (kb | k) != 0);   // UMMA_K = 16 fp16 = 32 B
                     tc::mbar_wait(&bar->full_lo[stage], ph);

@@ -378,7 +378,7 @@ class GATsSuperGlue(nn.Module):
             # prefetched TMA pipeline as a second operand instead of being fetched by the epilogue (exposed latency); the
             # identity's planes are exact (64, 0), so the tensor core reproduces hi + lo of x to fp32 rounding.  In place: a
             # row tile is read completely (all MMAs retired) before its epilogue stores, and Cout = 256 is one column tile.
-            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._identity_planes(dev), Cp=st.p, flags=16 | 64 | 1024 | b2, stats=st.xs,
+            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._identity_planes(dev), Cp=st.p, flags=16 | 64 | 1024 | 8192 | b2, stats=st.xs,
                             tag="mlp1", work_k=2 * _D)                                                                      # COLSUM | WBATCHED | W2_EXACT_HI
         else:   # an fp32 copy is kept (with_linear_transform): residual add onto it in the epilogue
             self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
