@@ -291,6 +291,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             }
             const int row = rt * BM + quad * 32 + lane;
             const bool row_ok = row < p.rows;
+            const bool rows_full = rt * BM + BM <= p.rows;         // warp-uniform: no row of this tile needs masking out of the column sums
             const long long grow = (long long)b * p.rows + (row_ok ? row : 0);
             const int row0 = rt * BM + quad * 32;
             tc::mbar_wait(&bar->acc_full[as], aph);
@@ -344,10 +345,18 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         // folded into the next layer's weights (op_scale_weight_planes), GATs_SuperGlue.py:144-146
                         float s[32];
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
+                        for (int i = 0; i < 32; ++i) s[i] = vv[i];
+                        if (!rows_full) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = row_ok ? s[i] : 0.f;
+                        }
                         const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) { const float t = row_ok ? vv[i] : 0.f; s[i] = t * t; }
+                        for (int i = 0; i < 32; ++i) s[i] = vv[i] * vv[i];
+                        if (!rows_full) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = row_ok ? s[i] : 0.f;
+                        }
                         const float cq = transpose_reduce_sum(s, lane) * kInvScale2;
                         if (tile_ok) p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, cq);
 #pragma unroll
@@ -399,7 +408,11 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     if (flags & OPB_LIN_COLSUM) {                // column sums of the stored value over the valid rows (Ksum :97; means)
                         float s[32];
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) s[i] = row_ok ? vv[i] : 0.f;
+                        for (int i = 0; i < 32; ++i) s[i] = vv[i];
+                        if (!rows_full) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = row_ok ? s[i] : 0.f;
+                        }
                         const float cs = transpose_reduce_sum(s, lane) * (1.f / kScale);
                         if (tile_ok) p.stats[((long long)b * (p.row_tiles * 4) + rt * 4 + quad) * p.Cout + c0 + lane] = make_float2(cs, 0.f);
                     }
