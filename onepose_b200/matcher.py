@@ -13,6 +13,8 @@ from __future__ import annotations
 
 import copy
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -219,7 +221,9 @@ class GATsSuperGlue(nn.Module):
         dev = torch.device(dev)
         s = self._pose_streams.get(dev.index)
         if s is None:
-            s = self._pose_streams[dev.index] = torch.cuda.Stream(device=dev)
+            # high priority: the few, long-running PnP blocks take the first SM resources that come free between the matcher's kernels
+            # (OPB_POSE_PRIORITY=0 for A/B runs)
+            s = self._pose_streams[dev.index] = torch.cuda.Stream(device=dev, priority=int(os.environ.get("OPB_POSE_PRIORITY", "-1")))
         return s
 
     @staticmethod
