@@ -39,6 +39,11 @@ int op_abi_version(void);
  * point-major [B, N, C].  bstride_in (in elements) may be 0 for an expand()-ed static DB. */
 int op_channel_major_to_point_major(const float *in, float *out, int B, int C, int N,
                                     long long bstride_in, void *stream);
+/* The same transposition straight into split-precision planes (64 x, [B, N, 256] fp16 hi / lo) plus the per-32-row column sums
+ * [B][op_linear_tc_stat_parts(N)][256][2] of the tensor-core path: op_channel_major_to_point_major + op_split_planes + op_colsum_partial
+ * in one pass, bit-identical, C = 256. */
+int op_channel_major_to_planes(const float *in, long long bstride_in, void *hi, void *lo, float *colsum_partial, int B, int N,
+                               void *stream);
 
 /* ---- (1) GATs leaf aggregation: GATs.py:62-123 ------------------------------------------------
  * For every 3D point n (and frame b): logits over its (include_self ? 1 : 0) + L entries,

@@ -27,6 +27,7 @@ _SIGS = {
     "op_last_error": (C.c_char_p, []),
     "op_abi_version": (i32, []),
     "op_channel_major_to_point_major": (i32, [vp, vp, i32, i32, i32, i64, vp]),
+    "op_channel_major_to_planes": (i32, [vp, i64, vp, vp, vp, i32, i32, vp]),
     "op_gats_leaf_aggregate": (i32, [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp]),
     "op_linear": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
     "op_linear_row_tiles": (i32, [i32]),
@@ -106,7 +107,7 @@ def stream_ptr():
 # kernels launched by each entry point (for the bench's gpu_launches claim)
 LAUNCHES = {
     "op_atb_tc": 1, "op_kv_post": 1, "op_split_planes": 1, "op_norm_relu_split": 1, "op_linear_tc": 1, "op_instnorm_finalize_tc": 1, "op_attn_apply_planes": 1,
-    "op_channel_major_to_point_major": 1, "op_gats_leaf_aggregate": 1, "op_linear": 1, "op_instnorm_finalize": 1,
+    "op_channel_major_to_point_major": 1, "op_channel_major_to_planes": 1, "op_gats_leaf_aggregate": 1, "op_linear": 1, "op_instnorm_finalize": 1,
     "op_kv_reduce": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 9, "op_sim_dual_softmax_rows": 9, "op_sim_dual_softmax_simt": 7,
     "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 5,
 }

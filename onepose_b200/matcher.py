@@ -489,12 +489,19 @@ class GATsSuperGlue(nn.Module):
         self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")
         self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
 
-    def _encode_tc(self, x2, db, pk, B, N2, N3, L, m2, m3, dev):
+    def _encode_tc(self, x2, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=None):
         """Tensor-core path.  The streams live as split-precision planes + per-frame column sums; an fp32 copy is kept
         only when the GATs layers need one (with_linear_transform)."""
         keep = bool(self.hparams["with_linear_transform"])
         s2 = self._new_stream("2", B, N2, dev, keep)
-        self._load_stream(s2, x2)
+        if x2 is None:
+            x = x2_cm
+            if x.dtype != torch.float32 or x.stride(2) != 1 or x.stride(1) != N2:
+                x = (x[:1] if x.stride(0) == 0 else x).float().contiguous()
+            call("op_channel_major_to_planes", ptr(x), x.stride(0) if x.shape[0] > 1 else 0, ptr(s2.p[0]), ptr(s2.p[1]), ptr(s2.xs), B, N2, stream_ptr())
+            s2.parts = lib.op_linear_tc_stat_parts(N2)
+        else:
+            self._load_stream(s2, x2)
         s3 = self._new_stream("3", B, N3, dev, keep)
         # With one object DB shared by the whole batch the 3D stream does not depend on the query frame until it first
         # receives a message from the 2D stream (the x-side update of the first 'cross' layer): up to there it is
@@ -606,13 +613,17 @@ class GATsSuperGlue(nn.Module):
             raise ValueError(f"bad descriptor shapes {tuple(desc2d.shape)} {tuple(desc3d.shape)} {tuple(leaves.shape)}")
         pk = self._pack_weights(dev)
         db = self._static_db(desc3d, leaves[:, :, :N3 * L], L)
-        x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
         m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
         m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
-        if self.use_tensor_cores:
-            self._encode_tc(x2, db, pk, B, N2, N3, L, m2, m3, dev)
+        if self.use_tensor_cores and not self.hparams["with_linear_transform"]:
+            # planes-only streams: the query descriptors go from the public channel-major layout straight into planes + column sums
+            self._encode_tc(None, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=desc2d)
         else:
-            self._encode_simt(x2, db, pk, B, N2, N3, L, m2, m3, dev)
+            x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
+            if self.use_tensor_cores:
+                self._encode_tc(x2, db, pk, B, N2, N3, L, m2, m3, dev)
+            else:
+                self._encode_simt(x2, db, pk, B, N2, N3, L, m2, m3, dev)
         if not self.use_tensor_cores:                                 # the tensor-core op normalises while it splits the operands
             call("op_l2_normalize_rows", ptr(m2), ptr(m2), B * N2, _D, stream_ptr())
             call("op_l2_normalize_rows", ptr(m3), ptr(m3), B * N3, _D, stream_ptr())

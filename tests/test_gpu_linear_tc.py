@@ -339,3 +339,25 @@ def test_matcher_gats_variants_tensor_core_vs_cuda_core(flags):
     assert helpers.conf_rel_err(conf_tc.cpu(), conf_cc.cpu()) < helpers.CONF_RTOL
     for b in range(2):
         helpers.assert_matches_equal_off_ties(m0_tc[b].cpu(), pred_cc["matches0_batched"][b].cpu(), conf_cc[b].cpu(), axis=2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(2, 200), (3, 2048), (1, 33)])
+def test_channel_major_to_planes_equals_the_three_kernel_path(shape):
+    """op_channel_major_to_planes = op_channel_major_to_point_major + op_split_planes + op_colsum_partial, bit for bit."""
+    from onepose_b200._lib import call, lib, ptr, stream_ptr
+    B, N = shape
+    g = torch.Generator().manual_seed(N)
+    x = torch.randn(B, 256, N, generator=g).cuda()
+    parts = lib.op_linear_tc_stat_parts(N)
+    pm = torch.empty(B, N, 256, device="cuda")
+    call("op_channel_major_to_point_major", ptr(x), ptr(pm), B, 256, N, x.stride(0), stream_ptr())
+    h0 = torch.empty(B, N, 256, dtype=torch.float16, device="cuda"); l0 = torch.empty_like(h0)
+    call("op_split_planes", ptr(pm), ptr(h0), ptr(l0), pm.numel(), stream_ptr())
+    cs0 = torch.full((B, parts, 256, 2), float("nan"), device="cuda")
+    call("op_colsum_partial", ptr(pm), B, N, 256, ptr(cs0), stream_ptr())
+    h1 = torch.empty_like(h0); l1 = torch.empty_like(h0)
+    cs1 = torch.full((B, parts, 256, 2), float("nan"), device="cuda")
+    call("op_channel_major_to_planes", ptr(x), x.stride(0), ptr(h1), ptr(l1), ptr(cs1), B, N, stream_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(h0, h1) and torch.equal(l0, l1) and torch.equal(cs0, cs1)
