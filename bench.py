@@ -44,7 +44,8 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 25 ms from the last warm-up steps to the end of the timed region (the sampler
+    process needs ~0.1 s to come up, as long as a default timed region)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -54,7 +55,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "25"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True).start()
         except OSError:
             self.proc = None
@@ -247,10 +248,10 @@ def run_ours(args):
     # Steps are pipelined as a frame server would run them: gather + PnP of step i go to the module's pose stream and overlap the
     # matcher of step i+1 (GATsSuperGlue.pnp_overlap); every step's work is complete at the barrier that ends the timed region.
     model.pnp_overlap = not args.no_pnp_overlap
-    for _ in range(max(args.warmup, 3)):
-        step_resident()
     clocks = ClockSampler(local_rank)
     clocks.start()
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
     ms, pred = timed(step_resident, args.steps)
     clk = clocks.stop()
     # per-kernel durations (roofline, shares, launch count): the same K steps once more with CUDA events around every
