@@ -83,6 +83,17 @@ class Evaluator:
         return {"cmd1": cmd1, "cmd3": cmd3, "cmd5": cmd5}
 
 
+_COPY_STREAMS = {}
+
+
+def _copy_stream(dev):
+    dev = torch.device(dev)
+    st = _COPY_STREAMS.get(dev.index)
+    if st is None:
+        st = _COPY_STREAMS[dev.index] = torch.cuda.Stream(device=dev)
+    return st
+
+
 @torch.no_grad()
 def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=64, scale=1000.0, evaluator=None):
     """The loop of inference_core (inference.py:132-160) for one object and F query frames, in blocks of ``batch`` frames.
@@ -98,18 +109,53 @@ def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=
     K = (K[None].expand(F, 3, 3) if K.dim() == 2 else K).to(dev)
     evaluator = evaluator if evaluator is not None else Evaluator()
     out = {k: [] for k in ("pose", "n_matches", "n_inliers")}
-    for f0 in range(0, F, batch):
+    # A three-stage pipeline over the blocks: block i+1 is uploaded on a copy stream while block i is matched on the caller's stream,
+    # and gather + PnP + pose errors of block i run on the matcher's pose stream (GATsSuperGlue.pnp_overlap) next to the matcher of
+    # block i+1.  Host buffers should be pinned for the upload to be asynchronous.
+    main = torch.cuda.current_stream(dev)
+    copy = _copy_stream(dev)
+    overlap_was = getattr(matcher, "pnp_overlap", None)
+    if overlap_was is not None:
+        matcher.pnp_overlap = True
+
+    def upload(f0):
         f1 = min(F, f0 + batch)
-        data = db.inputs(f1 - f0)
-        data["keypoints2d"] = torch.as_tensor(keypoints2d[f0:f1]).to(dev, non_blocking=True)
-        data["descriptors2d_query"] = torch.as_tensor(descriptors2d[f0:f1]).to(dev, non_blocking=True)
-        data["query_intrinsic"] = K[f0:f1]
-        data["pnp_scale"] = scale
-        pred, _ = matcher(data)
+        with torch.cuda.stream(copy):
+            kp = torch.as_tensor(keypoints2d[f0:f1]).to(dev, non_blocking=True)
+            ds = torch.as_tensor(descriptors2d[f0:f1]).to(dev, non_blocking=True)
+            gt = None if poses_gt is None else torch.as_tensor(poses_gt[f0:f1]).to(dev, non_blocking=True)
+            return f0, f1, kp, ds, gt, copy.record_event()
+
+    copy.wait_stream(main)
+    nxt = upload(0) if F > 0 else None
+    preds = []
+    try:
+        while nxt is not None:
+            f0, f1, kp, ds, gt, ready = nxt
+            main.wait_event(ready)
+            for t in (kp, ds):
+                t.record_stream(main)
+            nxt = upload(f1) if f1 < F else None
+            data = db.inputs(f1 - f0)
+            data["keypoints2d"], data["descriptors2d_query"] = kp, ds
+            data["query_intrinsic"] = K[f0:f1]
+            data["pnp_scale"] = scale
+            pred, _ = matcher(data)
+            preds.append(pred)
+            if gt is not None:
+                ev = pred.get("pose_event")
+                side = matcher.pose_stream(dev) if ev is not None else main
+                with torch.cuda.stream(side):                           # behind this block's PnP
+                    gt.record_stream(side)
+                    evaluator.evaluate_batch(pred["pose"], gt)
+    finally:
+        if overlap_was is not None:
+            matcher.pnp_overlap = overlap_was
+    if preds and preds[-1].get("pose_event") is not None:               # everything on the pose stream is ordered before what follows
+        main.wait_stream(matcher.pose_stream(dev))
+    for pred in preds:
         for k in out:
             out[k].append(pred[k])
-        if poses_gt is not None:
-            evaluator.evaluate_batch(pred["pose"], torch.as_tensor(poses_gt[f0:f1]).to(dev))
     res = {k: torch.cat(v) for k, v in out.items()}
     homo = torch.zeros(F, 4, 4, dtype=torch.float64, device=dev)
     homo[:, :3] = res["pose"]; homo[:, 3, 3] = 1.0                        # eval_utils.py:35-36
