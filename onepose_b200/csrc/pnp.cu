@@ -200,4 +200,5 @@ __device__ void block_reduce(double *v, double *scratch /* [8][K] */, double *ou
 }  // namespace pnp
 }  // namespace opb
 
+#include "pnp_p3p.cuh"
 #include "pnp_refit.cuh"

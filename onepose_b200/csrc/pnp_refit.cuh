@@ -39,9 +39,27 @@ k_pnp_select_refit(const float *__restrict__ X32, const float *__restrict__ uv32
             n_inliers[f] = 0; iters_run[f] = 0;
         }
     };
-    // cv2 raises for n < 4 (-> identity pose, no inliers, eval_utils.py:40-42).  n == 4 would take cv2's
-    // P3P branch, which is not implemented here: reported as a failure as well (documented deviation).
-    if (n < 5) { write_identity(); return; }
+    // cv2 raises for n < 4 (-> identity pose, no inliers, eval_utils.py:40-42)
+    if (n < 4) { write_identity(); return; }
+    if (n == 4) {
+        // cv2's npoints == 4 branch: no RANSAC, P3P on points 0-2 disambiguated by point 3, all four points reported as inliers
+        // (pnp_p3p.cuh); no admissible solution = cv2 failure = the wrapper's identity fallback
+        __syncthreads();                              // the mask is cleared
+        if (tid == 0) {
+            double R4[9], t4[3], rv[3];
+            if (solve_p3p4(X, uv, cam, R4, t4)) {
+                rodrigues_to_vec(R4, rv);
+                rodrigues_to_mat(rv, R4);             // the wrapper's cv2.Rodrigues(rvec), eval_utils.py:31
+                for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) out[r * 4 + c] = R4[3 * r + c]; out[r * 4 + 3] = t4[r] / scale; }
+                n_inliers[f] = 4; iters_run[f] = 0;
+                for (int i = 0; i < 4; ++i) mask[i] = 1;
+            } else {
+                for (int i = 0; i < 12; ++i) out[i] = (i % 5 == 0) ? 1.0 : 0.0;
+                n_inliers[f] = 0; iters_run[f] = 0;
+            }
+        }
+        return;
+    }
 
     // ---- 1. winner ---------------------------------------------------------------------------
     if (tid == 0) {

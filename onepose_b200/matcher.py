@@ -184,8 +184,15 @@ class GATsSuperGlue(nn.Module):
                     if k in lw:
                         lw[k + "_p"] = self._split_new(lw[k])
             self._packed["Wf_p"] = self._split_new(self._packed["Wf"])
+            # identity block of the in-GEMM residual add (_propagate_tc): built here, on the caller's stream, BEFORE forward forks
+            # the side stream -- both streams' mlp1 launches read these planes, and a lazily built copy would be written on
+            # whichever stream got there first with nothing ordering the other stream behind it
+            self._packed["eye_p"] = self._split_new(torch.eye(_D, dtype=torch.float32, device=device))
         self._packed_key = key
-        self._db_cache.clear()       # cached W-transformed leaves depend on the weights
+        # cached W-transformed leaves depend on the weights; the point-major DB copies themselves (incl. a DB registered by
+        # ObjectDB.register before the first forward) do not
+        for _, entry in self._db_cache.values():
+            entry["wh_leaf"] = {}
         return self._packed
 
     # ------------------------------------------------------------------ layout helpers
@@ -250,14 +257,20 @@ class GATsSuperGlue(nn.Module):
             raise ValueError("register_static_db: inconsistent DB shapes")
         entry = dict(d3=avg_pm[None].float().contiguous(), leaves=leaves_pm[None].float().contiguous(), shared=True, wh_leaf={},
                      _src=(descriptors3d_db, descriptors2d_db))
-        self._db_cache["registered"] = ((descriptors3d_db.data_ptr(), descriptors2d_db.data_ptr(), N3, N3 * num_leaf), entry)
+        self._db_cache["registered"] = (self._registered_key(descriptors3d_db, descriptors2d_db, N3, N3 * num_leaf) +
+                                        (avg_pm._version, leaves_pm._version), entry)
+        entry["_pm_src"] = (avg_pm, leaves_pm)
+
+    @staticmethod
+    def _registered_key(d3, lv, n3, nl):
+        return (d3.data_ptr(), lv.data_ptr(), n3, nl, d3._version, lv._version)
 
     def _static_db(self, d3, lv, L):
         """Point-major copy of the object DB, cached while the caller keeps handing the same tensors."""
         shared = d3.shape[0] == 1 or (d3.stride(0) == 0 and lv.stride(0) == 0)
         reg = self._db_cache.get("registered")
-        if reg is not None and shared and reg[0] == (d3.data_ptr(), lv.data_ptr(), d3.shape[2], lv.shape[2]) \
-                and d3.stride(1) == 1 and lv.stride(1) == 1:
+        if reg is not None and shared and d3.stride(1) == 1 and lv.stride(1) == 1 and \
+                reg[0] == self._registered_key(d3, lv, d3.shape[2], lv.shape[2]) + tuple(t._version for t in reg[1]["_pm_src"]):
             return reg[1]
         Bd = 1 if shared else d3.shape[0]
         key = (d3.data_ptr(), lv.data_ptr(), tuple(d3.shape), tuple(lv.shape), d3._version, lv._version, Bd)
@@ -382,17 +395,11 @@ class GATsSuperGlue(nn.Module):
             # prefetched TMA pipeline as a second operand instead of being fetched by the epilogue (exposed latency); the
             # identity's planes are exact (64, 0), so the tensor core reproduces hi + lo of x to fp32 rounding.  In place: a
             # row tile is read completely (all MMAs retired) before its epilogue stores, and Cout = 256 is one column tile.
-            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._identity_planes(dev), Cp=st.p, flags=16 | 64 | 1024 | 8192 | b2, stats=st.xs,
+            self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._packed["eye_p"], Cp=st.p, flags=16 | 64 | 1024 | 8192 | b2, stats=st.xs,
                             tag="mlp1", work_k=2 * _D)                                                                      # COLSUM | WBATCHED | W2_EXACT_HI
         else:   # an fp32 copy is kept (with_linear_transform): residual add onto it in the epilogue
             self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
         st.parts = parts
-
-    def _identity_planes(self, dev):
-        eye = self._db_cache.get("eye")
-        if eye is None or eye[0].device != dev:
-            eye = self._db_cache["eye"] = self._split_new(torch.eye(_D, dtype=torch.float32, device=dev))
-        return eye
 
     def _new_stream(self, ch, B, N, dev, keep_fp32, name=None):
         """Buffers of one descriptor stream of the tensor-core path: planes, column-sum partials (sized for either

@@ -21,7 +21,10 @@ from ._lib import call, lib, ptr, stream_ptr
 REPROJ_ERROR = 5.0          # eval_utils.py:28
 MAX_ITERS = 10000           # eval_utils.py:29
 CONFIDENCE = 0.99           # cv2 default
-DEFAULT_HYPOTHESES = 4096   # hypotheses evaluated per frame in one launch (BASELINE.json config 4)
+# Upper bound of hypotheses per frame = cv2's iterationsCount: the sequential rule may run that far when the best inlier ratio stays
+# below ~26 % (adaptive niters > 4096).  They are evaluated in adaptive rounds [0,32), [32,256), [256,1024), [1024,4096), [4096,8192),
+# [8192,10000): a frame whose replayed bound is reached costs nothing in later rounds, so only hard frames pay for the tail.
+DEFAULT_HYPOTHESES = MAX_ITERS
 
 _M32 = 0xFFFFFFFF
 

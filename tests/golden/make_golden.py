@@ -62,6 +62,49 @@ def matcher_inputs(case):
     return hp, w, obj, fr, synth.pack_batch(obj, fr)
 
 
+def all_outlier_problem(n, seed=0):
+    """Random 2D points against random 3D points: no pose explains them."""
+    rng = np.random.default_rng(seed)
+    return rng.uniform(0, 512, (n, 2)), rng.uniform(-0.1, 0.1, (n, 3))
+
+
+def make_pnp_edge(ransac_PnP):
+    """Edge cases of the wrapper (SURVEY.md appendix B caveats), all through the unmodified reference ``ransac_PnP``:
+    n = 0, 3 (cv2.error -> identity), n = 4 (cv2's P3P branch; eight more seeded problems in ``p3p_*``), n = 5 (direct EPnP),
+    all-outlier inputs of 6 and 50 points (cv2 reports failure: ``inliers == []``; the pose the wrapper then builds comes from
+    the rvec/tvec Mats that cv2 allocated but never wrote: three calls on the same input return different poses, so only the
+    inlier list is stored), and a
+    low-inlier problem on which the adaptive iteration bound stays above 4096 (cv2 runs to iteration 10000)."""
+    edge = {}
+    for n in (0, 3, 4, 5):
+        pr = synth.make_pnp_problem(10 + n, max(n, 1), 1.0)
+        with contextlib.redirect_stdout(io.StringIO()):
+            pose, _, inl = ransac_PnP(pr["K"], pr["pts2d"][:n], pr["pts3d"][:n], scale=1000)
+        edge[f"pose_{n}"] = pose; edge[f"inl_{n}"] = np.asarray(inl).ravel()
+        print("edge n=%d inliers=%d" % (n, len(inl)))
+    p3p = []
+    for seed in range(8):
+        pr = synth.make_pnp_problem(900 + seed, 4, 1.0, px_noise=0.5 if seed % 2 else 0.0)
+        pose, _, inl = ransac_PnP(pr["K"], pr["pts2d"], pr["pts3d"], scale=1000)
+        assert list(np.asarray(inl).ravel()) == [0, 1, 2, 3]
+        p3p.append(pose)
+    edge["p3p_poses"] = np.stack(p3p)
+    for n in (6, 50):
+        p2, p3 = all_outlier_problem(n)
+        poses = []
+        for _ in range(3):
+            pose, _, inl = ransac_PnP(synth.INTRINSIC, p2, p3, scale=1000)
+            poses.append(pose)
+        edge[f"inl_out{n}"] = np.asarray(inl).ravel()          # the pose is not stored: it is not a function of the inputs
+        varies = not all(np.array_equal(poses[0], q, equal_nan=True) for q in poses[1:])
+        print("all-outlier n=%d inliers=%d identity=%s pose varies between calls=%s" % (n, len(inl), np.array_equal(poses[0], np.eye(4)[:3]), varies))
+    pr = synth.make_pnp_problem(4, 400, 0.2)
+    pose, _, inl = ransac_PnP(pr["K"], pr["pts2d"], pr["pts3d"], scale=1000)
+    edge["pose_lowinl"] = pose; edge["inl_lowinl"] = np.asarray(inl).ravel()
+    print("low-inlier 400 x 0.2: inliers", len(inl))
+    np.savez_compressed(os.path.join(HERE, "pnp_edge.npz"), **edge)
+
+
 def main():
     from src.models.GATsSPG_architectures.GATs_SuperGlue import GATsSuperGlue, AttentionPropagation
     from src.models.GATsSPG_architectures.GATs import GraphAttentionLayer
@@ -111,16 +154,7 @@ def main():
                             samples=samples, sample_rt=np.stack(rts))
         print(case, "inliers", len(inl))
 
-    # edge cases of the wrapper (SURVEY.md appendix B caveats): n = 0, 3, 4, 5, 6(all outliers)
-    edge = {}
-    rng = np.random.default_rng(5)
-    for n in (0, 3, 4, 5):
-        pr = synth.make_pnp_problem(10 + n, max(n, 1), 1.0)
-        with contextlib.redirect_stdout(io.StringIO()):
-            pose, _, inl = ransac_PnP(pr["K"], pr["pts2d"][:n], pr["pts3d"][:n], scale=1000)
-        edge[f"pose_{n}"] = pose; edge[f"inl_{n}"] = np.asarray(inl).ravel()
-        print("edge n=%d inliers=%d" % (n, len(inl)))
-    np.savez_compressed(os.path.join(HERE, "pnp_edge.npz"), **edge)
+    make_pnp_edge(ransac_PnP)
 
     # DB builder + evaluator
     import ast
@@ -158,4 +192,8 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "pnp_edge" in sys.argv[1:]:
+        from src.utils.eval_utils import ransac_PnP as _ref_ransac_PnP
+        make_pnp_edge(_ref_ransac_PnP)
+    else:
+        main()

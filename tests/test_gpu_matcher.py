@@ -70,6 +70,51 @@ def test_config1_shape_vs_oracle(damped):
     assert int((pred["matches0"] > -1).sum()) > 0
 
 
+def _check_vs_oracle(hp, w, obj, frames, oracle_dtype=torch.float32):
+    """Full forward against oracle.matcher_forward (GATs_SuperGlue.py:203-278) on every frame of the batch."""
+    from oracle import gats_spg_oracle as orc
+    data = synth.pack_batch(obj, frames)
+    po, co = orc.matcher_forward(data, w, hp, dtype=oracle_dtype, return_batched=True)
+    pred, conf = _model(hp, w)(_cuda(data))
+    err = helpers.conf_rel_err(conf.cpu(), co)
+    assert err < helpers.CONF_RTOL, err
+    for b in range(len(frames)):
+        helpers.assert_matches_equal_off_ties(pred["matches0_batched"][b].cpu(), po["matches0_batched"][b], co[b], axis=2)
+        helpers.assert_matches_equal_off_ties(pred["matches1_batched"][b].cpu(), po["matches1_batched"][b], co[b], axis=1)
+        np.testing.assert_allclose(pred["matching_scores0_batched"][b].cpu().numpy(), po["matching_scores0_batched"][b].float().numpy(),
+                                   rtol=1e-3, atol=1e-30)
+    assert torch.equal(pred["matches0"], pred["matches0_batched"][0])
+    return pred, err
+
+
+@pytest.mark.parametrize("damped", [True, False])
+def test_headline_shape_vs_oracle(damped):
+    """BASELINE.json configs[1], the shape every bench number is quoted on (2048 x 8192 x 8 leaves), two frames of one object:
+    conf within 1e-3 of the oracle, match indices equal off near-ties.  Damped weights with the shipped 0.2 threshold (planted
+    correspondences survive), undamped random-init weights with threshold 0."""
+    hp = dict(synth.DEFAULT_HPARAMS)
+    if not damped:
+        hp["match_threshold"] = 0.0
+    w = synth.make_weights(0, damped=damped)
+    obj = synth.make_object(0, 8192, 8)
+    frames = [synth.make_frame(obj, f, 2048) for f in range(2)]
+    pred, _ = _check_vs_oracle(hp, w, obj, frames)
+    assert int((pred["matches0_batched"] > -1).sum()) > (60 if damped else 0)
+
+
+@pytest.mark.parametrize("damped", [True, False])
+def test_config3_large_object_vs_oracle(damped):
+    """BASELINE.json configs[2]: 4096 query keypoints vs 32768 3D points x 16 leaves, one frame, against the oracle."""
+    hp = dict(synth.DEFAULT_HPARAMS)
+    if not damped:
+        hp["match_threshold"] = 0.0
+    w = synth.make_weights(0, damped=damped)
+    obj = synth.make_object(1, 32768, 16)
+    frames = [synth.make_frame(obj, 0, 4096)]
+    pred, _ = _check_vs_oracle(hp, w, obj, frames)
+    assert int((pred["matches0_batched"] > -1).sum()) > (30 if damped else 0)
+
+
 def test_headline_shape_properties():
     """Size-independent properties at the headline shape (2048 x 8192 x 8 leaves), batch of 3 frames."""
     hp = dict(synth.DEFAULT_HPARAMS)

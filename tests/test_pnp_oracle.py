@@ -90,3 +90,26 @@ def test_wrapper_edge_cases_vs_golden():
         assert np.array_equal(g[f"pose_{n}"], np.eye(4)[:3]) and len(g[f"inl_{n}"]) == 0
     for n in (4, 5):     # direct solve, all points returned as inliers
         assert list(g[f"inl_{n}"]) == list(range(n))
+    for n in (6, 50):    # all outliers: cv2 reports failure, the wrapper returns []
+        assert len(g[f"inl_out{n}"]) == 0
+    assert g["p3p_poses"].shape == (8, 3, 4) and len(g["inl_lowinl"]) == 80
+
+
+def test_edge_golden_vs_live_cv2_and_restatement():
+    """The committed edge fixture against the image's cv2 (the library the reference calls) and the C restatement."""
+    pytest.importorskip("cv2")
+    g = np.load(os.path.join(helpers.GOLDEN, "pnp_edge.npz"))
+    mg = helpers.load_make_golden()
+    for seed in range(8):
+        pr = synth.make_pnp_problem(900 + seed, 4, 1.0, px_noise=0.5 if seed % 2 else 0.0)
+        pose, _, inl = po.ransac_pnp_cv2(pr["K"], pr["pts2d"], pr["pts3d"], scale=1000)
+        assert list(np.asarray(inl).ravel()) == [0, 1, 2, 3]
+        r_err, t_err = po.pose_error(pose, g["p3p_poses"][seed])
+        assert r_err < 1e-4 and t_err < 1e-6
+    for n in (6, 50):
+        p2, p3 = mg.all_outlier_problem(n)
+        assert len(po.ransac_pnp_cv2(synth.INTRINSIC, p2, p3, scale=1000)[2]) == 0
+        assert len(po.ransac_pnp_restated(synth.INTRINSIC, p2, p3, scale=1000)[2]) == 0
+    pr = synth.make_pnp_problem(4, 400, 0.2)
+    ref = po.ransac_epnp(pr["pts3d"] * 1000.0, pr["pts2d"], pr["K"])
+    assert ref["iters"] == 10000 and np.array_equal(ref["inliers"], g["inl_lowinl"])

@@ -28,3 +28,19 @@ for damped in (False, True):
     _, co = orc.matcher_forward(data, w, hp, dtype=torch.float64)
     _, conf = model(hp, w)({k: v.cuda() for k, v in data.items()})
     print(f"configs[0] 1024 x 4096 x 8, damped={damped}: conf rel err vs float64 oracle {float(helpers.conf_rel_err(conf.cpu(), co)):.2e}")
+
+# the shapes the bench numbers are quoted on: BASELINE.json configs[1] (headline, two frames) and configs[2] (large object, one frame)
+for name, (oid, n2, n3, L, nf) in {"configs[1] 2048 x 8192 x 8": (0, 2048, 8192, 8, 2), "configs[2] 4096 x 32768 x 16": (1, 4096, 32768, 16, 1)}.items():
+    for damped in (False, True):
+        hp = dict(synth.DEFAULT_HPARAMS)
+        w = synth.make_weights(0, damped=damped)
+        obj = synth.make_object(oid, n3, L)
+        data = synth.pack_batch(obj, [synth.make_frame(obj, f, n2) for f in range(nf)])
+        _, conf = model(hp, w)({k: v.cuda() for k, v in data.items()})
+        conf = conf.cpu()
+        _, c32 = orc.matcher_forward(data, w, hp)
+        e32 = float(helpers.conf_rel_err(conf, c32))
+        _, c64 = orc.matcher_forward(data, w, hp, dtype=torch.float64)
+        print(f"{name}, damped={damped}: conf rel err vs fp32 oracle {e32:.2e}, vs float64 oracle {float(helpers.conf_rel_err(conf, c64)):.2e}; "
+              f"fp32 oracle vs float64 oracle {float(helpers.conf_rel_err(c32, c64)):.2e}", flush=True)
+        del c32, c64, conf
