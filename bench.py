@@ -311,7 +311,7 @@ def run_ours(args):
             # fp32-class accuracy from fp16 MMAs costs three MMAs per algorithmic product (hi*hi + lo*hi + hi*lo): the tensor pipe
             # executes 3x the algorithmic flops that `achieved` counts
             roofline.update(mma_passes=3, achieved_issued=3 * d["achieved"], frac_issued=3 * d["frac"])
-        sim = kernels.get("op_sim_dual_softmax_rows") or kernels.get("op_sim_dual_softmax")
+        sim = kernels.get("op_sim_dual_softmax_planes") or kernels.get("op_sim_dual_softmax_rows") or kernels.get("op_sim_dual_softmax")
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             n_cpu = 4
@@ -338,7 +338,7 @@ def run_ours(args):
             "roofline": roofline,
             "roofline_sim_dual_softmax": None if sim is None else dict(
                 {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
-                traffic=(traffic.get("op_sim_dual_softmax_rows") or traffic.get("op_sim_dual_softmax") or {}).get("traffic_bytes"),
+                traffic=(traffic.get("op_sim_dual_softmax_planes") or {}).get("traffic_bytes"),
                 # the similarity is computed twice (statistics pass, write pass); a product is one fp16 MMA plus two fp8 MMAs at twice
                 # the rate (= 2 fp16-equivalent passes; 3 with OPB_SIM_MMA=f16 / OPB_SIM_CG=1)
                 mma_passes_fp16_equivalent=SIM_MMA_UNITS,

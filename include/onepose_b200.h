@@ -90,6 +90,7 @@ int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_bstride, voi
 #define OPB_LIN_A1_BCAST 2048 /* op_linear_tc: A1 is [1, rows, K1], the same rows for every frame (e.g. the shared 3D stream at its first per-frame layer) */
 #define OPB_LIN_A2_BCAST 4096 /* op_linear_tc: the same for A2 */
 #define OPB_LIN_W2_IDENTITY 8192 /* op_linear_tc: W2 is the 256 x 256 identity (planes (64, 0); K2 = Cout = 256): C = epi(A1 . W^T + A2).  The pair form then issues the A2 part as N = 64 MMAs on the diagonal blocks only (a quarter of the tensor work of the residual) */
+#define OPB_LIN_UNIT_PLANES8 16384 /* op_linear_tc (Cout = 256, planes output only): every output row is L2-normalised (x / max(|x|, 1e-12), F.normalize) and written as the operand planes of op_sim_dual_softmax_planes: Ch = fp16(64 u) [B,rows,256], Cl = bytes [2][B,rows,256]: (64 u - hi) as e5m2, then hi as e4m3 */
 #define OPB_LIN_W2_EXACT_HI 1024 /* op_linear_tc: W2's lo plane is all zeros (e.g. the identity of the in-GEMM residual add): its MMA pass is skipped */
 int op_linear(const float *A1, int K1, const float *A2, int K2, const float *W, const float *bias,
               float *C, int B, int rows_per_batch, int Cout, int flags, int elu_cols,
@@ -188,6 +189,12 @@ int op_sim_dual_softmax_rows(const float *x2, const float *x3, int B, int N2, in
                              float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                              float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
                              void *stream);
+/* Same contract on operand planes a producer has already written (op_linear_tc with OPB_LIN_UNIT_PLANES8: final_proj, :241, with
+ * F.normalize, :245-246, in its epilogue): mX_hi = fp16(64 u) [B,N,256], mX_bytes = [2][B,N,256] bytes: (64 u - hi) as e5m2, then hi as
+ * e4m3.  Neither the fp32 projections nor their normalised copy ever exist in HBM. */
+int op_sim_dual_softmax_planes(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
+                               float scale_factor, float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                               float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream);
 /* Same contract on fp32 CUDA cores (exact fp32 dot products, no tensor cores): kept as the on-device
  * cross-check of the tcgen05 split-precision kernel, not used by the product path. */
 int op_sim_dual_softmax_simt(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,

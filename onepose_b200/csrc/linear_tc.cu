@@ -293,6 +293,9 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     OPB_CHECK_ARG(!(flags & OPB_LIN_NORM_RELU), "op_linear_tc: NORM_RELU is applied by op_norm_relu_split");
     OPB_CHECK_ARG(!(flags & OPB_LIN_ELU1) || elu_cols % 32 == 0, "op_linear_tc: elu_cols must be a multiple of 32");
     OPB_CHECK_ARG(B >= 0 && rows_per_batch >= 0, "op_linear_tc: bad B=%d rows=%d", B, rows_per_batch);
+    const bool unit8 = (flags & OPB_LIN_UNIT_PLANES8) != 0;
+    OPB_CHECK_ARG(!unit8 || (Cout == 256 && Ch && Cl && !C && !(flags & (lintc::kEpiMask & ~OPB_LIN_UNIT_PLANES8))),
+                  "op_linear_tc: UNIT_PLANES8 needs Cout == 256, plane outputs only and no other epilogue flag");
     if (B == 0 || rows_per_batch == 0) return OPB_OK;
     const int K = W2h ? K1 : K1 + K2;                 // columns of W
     CUtensorMap ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl;
@@ -322,7 +325,14 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     }
     OPB_CHECK_ARG(((uintptr_t)C | (uintptr_t)Ch | (uintptr_t)Cl) % 16 == 0, "op_linear_tc: outputs must be 16-byte aligned");
     if (C) { if ((rc = make_tmap_f32_3d_store(&tc_, C, B, rows_per_batch, Cout, 32))) return rc; } else tc_ = ta1h;
-    if (Ch) {
+    if (unit8) {
+        // similarity operand planes: hi fp16, then two byte planes in the Cl buffer (lo e5m2 | hi e4m3) -- the byte maps ride in the
+        // kernel's tm_cl / tm_c parameters
+        uint8_t *bytes = (uint8_t *)Cl;
+        if ((rc = make_tmap_f16_3d_store(&tch, Ch, B, rows_per_batch, Cout, 32)) || (rc = make_tmap_u8_3d_store(&tcl, bytes, B, rows_per_batch, Cout, 32)) ||
+            (rc = make_tmap_u8_3d_store(&tc_, bytes + (size_t)B * rows_per_batch * Cout, B, rows_per_batch, Cout, 32)))
+            return rc;
+    } else if (Ch) {
         if ((rc = make_tmap_f16_3d_store(&tch, Ch, B, rows_per_batch, Cout, 32)) || (rc = make_tmap_f16_3d_store(&tcl, Cl, B, rows_per_batch, Cout, 32))) return rc;
     } else { tch = ta1h; tcl = ta1h; }
     lintc::Params p{};
@@ -368,8 +378,10 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     constexpr int kQ = OPB_LIN_ELU1 | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | lintc::kHasP;         // Q projection
     constexpr int kM0 = OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU | lintc::kHasP;                   // MLP layer 0
     constexpr int kM1 = OPB_LIN_COLSUM | lintc::kHasP;                                        // MLP layer 1 (residual inside the GEMM)
-    constexpr int kF = lintc::kHasC;                                                          // final projection
+    constexpr int kF = lintc::kHasC;                                                          // final projection (fp32 output)
+    constexpr int kFN = OPB_LIN_UNIT_PLANES8 | lintc::kHasP;                                  // final projection + F.normalize -> similarity operand planes
     const int smem2 = lintc::Cfg<2>::SMEM_BYTES;
+    OPB_CHECK_ARG(!unit8 || (cg == 2 && !dbg), "op_linear_tc: UNIT_PLANES8 exists in the pair form only (unset OPB_LINEAR_CG / OPB_LIN_DBG)");
     if (cg == 1) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<1, -1>, lintc::Cfg<1>::SMEM_BYTES));
     else if (dbg) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, -1>, smem2));
     else if (key == kK) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kK>, smem2));
@@ -377,6 +389,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     else if (key == kM0) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kM0>, smem2));
     else if (key == kM1) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kM1>, smem2));
     else if (key == kF) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kF>, smem2));
+    else if (key == kFN) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kFN>, smem2));
     else OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, -1>, smem2));
     OPB_CHECK_LAUNCH();
     return OPB_OK;

@@ -13,6 +13,7 @@
 //               and/or re-split into the hi/lo planes the next GEMM consumes.  The epilogue of tile j overlaps
 //               the MMAs of tile j+1 (double-buffered accumulator).
 #pragma once
+#include <cuda_fp8.h>
 #include "tc_common.cuh"
 
 namespace opb {
@@ -99,7 +100,7 @@ __device__ __forceinline__ void split_planes32(const float *vs, uint32_t *h, uin
 // one instantiation per layer kind of the matcher.  The generic kernel (FL = -1) carries every epilogue variant behind run-time
 // branches: 8400 SASS instructions (134 KB) of which a layer executes a fraction, 10 % of its warp samples waiting for instruction
 // fetch (ncu: stall_no_inst) and 8 % resolving branches; the specialised ones are a third of that size.
-constexpr int kEpiMask = OPB_LIN_ELU1 | OPB_LIN_RESIDUAL | OPB_LIN_STATS | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU;
+constexpr int kEpiMask = OPB_LIN_ELU1 | OPB_LIN_RESIDUAL | OPB_LIN_STATS | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU | OPB_LIN_UNIT_PLANES8;
 constexpr int kHasC = 1 << 20, kHasP = 1 << 21;
 
 template <int CG, int FL>
@@ -296,6 +297,59 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             const int row0 = rt * BM + quad * 32;
             tc::mbar_wait(&bar->acc_full[as], aph);
             tc::tcgen05_fence_after();
+            if (flags & OPB_LIN_UNIT_PLANES8) {
+                // final_proj + F.normalize (GATs_SuperGlue.py:241-246) straight into the similarity kernel's operand planes:
+                // hi = fp16(64 u), lo = 64 u - hi as e5m2, hi again as e4m3 (sim_tc.cuh).  Cout = 256 = one column tile, so the
+                // tile holds whole rows: pass A sums the squares of this warp's 128 columns, the two column halves of a row meet
+                // in shared memory (fixed order), pass B re-reads the accumulator from TMEM, scales and emits the planes.
+                float ss = 0.f;
+#pragma unroll 1
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int ccol = half * 128 + hh * 64;
+                    float v[2][32];
+                    tc::tmem_ld_32x32(lane_base + as * BN + ccol, v[0]);
+                    tc::tmem_ld_32x32(lane_base + as * BN + ccol + 32, v[1]);
+                    tc::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 64; ++i) { const float t = fmaf(v[i >> 5][i & 31], 1.f / kScale, s_bias[ccol + i]); ss = fmaf(t, t, ss); }
+                }
+                float *s_ss = s_bias + 256;                           // free: Cout == 256, no ZSCALE
+                s_ss[half * 128 + quad * 32 + lane] = ss;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                // 64 u = vs / max(|value|, 1e-12) with |value| = sqrt(sum vs^2) / 64
+                const float inv_den = 1.f / fmaxf(sqrtf(s_ss[quad * 32 + lane] + s_ss[128 + quad * 32 + lane]) * (1.f / kScale), 1e-12f);
+                asm volatile("bar.sync 1, 256;" ::: "memory");        // everyone has read the sums before the next tile overwrites them
+#pragma unroll 1
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int ccol = half * 128 + hh * 64;
+                    float v[2][32];
+                    tc::tmem_ld_32x32(lane_base + as * BN + ccol, v[0]);
+                    tc::tmem_ld_32x32(lane_base + as * BN + ccol + 32, v[1]);
+                    tc::tmem_ld_wait();
+                    if (hh == 1) {
+                        tc::tcgen05_fence_before();
+                        __syncwarp();
+                        if (lane == 0) { if (CG == 2) tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&bar->acc_empty[as]), 0)); else tc::mbar_arrive(&bar->acc_empty[as]); }
+                    }
+                    uint32_t h[32], l8[16], x8[16];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {                    // element pair (2i, 2i + 1) of the 64 columns
+                        const float a = fmaf(v[i >> 4][(2 * i) & 31], 1.f / kScale, s_bias[ccol + 2 * i]) * inv_den;
+                        const float c = fmaf(v[i >> 4][(2 * i + 1) & 31], 1.f / kScale, s_bias[ccol + 2 * i + 1]) * inv_den;
+                        const __half2 hi = __floats2half2_rn(a, c);
+                        const float2 hf = __half22float2(hi);
+                        h[i] = *reinterpret_cast<const uint32_t *>(&hi);
+                        const uint32_t lo2 = __nv_cvt_float2_to_fp8x2(make_float2(a - hf.x, c - hf.y), __NV_SATFINITE, __NV_E5M2);
+                        const uint32_t hx2 = __nv_cvt_float2_to_fp8x2(hf, __NV_SATFINITE, __NV_E4M3);
+                        if (i & 1) { l8[i >> 1] |= lo2 << 16; x8[i >> 1] |= hx2 << 16; } else { l8[i >> 1] = lo2; x8[i >> 1] = hx2; }
+                    }
+                    stage_store(&tm_ch, ccol, reinterpret_cast<const uint4 *>(h), b, row0);
+                    stage_store(&tm_ch, ccol + 32, reinterpret_cast<const uint4 *>(h + 16), b, row0);
+                    stage_store(&tm_cl, ccol, reinterpret_cast<const uint4 *>(l8), b, row0);
+                    stage_store(&tm_c, ccol, reinterpret_cast<const uint4 *>(x8), b, row0);
+                }
+                continue;
+            }
 #pragma unroll 1
             for (int hh = 0; hh < 2; ++hh) {                      // 64 output columns (one attention head) per iteration
                 const int ccol = half * 128 + hh * 64;            // column inside the tile

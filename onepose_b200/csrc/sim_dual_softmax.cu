@@ -11,6 +11,7 @@
 #include <stdlib.h>
 #include "common.cuh"
 #include "sim_tc.cuh"
+#include "sim_tc16.cuh"
 
 namespace opb {
 
@@ -237,6 +238,8 @@ __global__ void k_mutual_select(const int *__restrict__ idx0, const float *__res
 
 struct SimWorkspace {
     float *rowsum_part, *colsum_part, *invR, *invC, *val0, *val1;
+    float *colsum4;              // sixteen-warp form: column sums per (row tile, TMEM lane quadrant)  [B][tm * 4][N3]
+    uint32_t *colkey4;           // sixteen-warp form: column keys per (row tile, TMEM lane quadrant)  [B][tm * 4][N3]
     __half *m2h, *m2l, *m3h, *m3l;
     unsigned long long *rowmax_part, *colmax_part;
     int *idx0, *idx1;
@@ -244,7 +247,9 @@ struct SimWorkspace {
 };
 
 static SimWorkspace carve(void *base, int B, int N2, int N3) {
-    const size_t tm = ceil_div(N2, SBM), tn = ceil_div(N3, SBN);
+    const size_t tm = ceil_div(N2, SBM);
+    // partials per query row: two per 128-column tile (eight-warp forms) or four per 256-column tile (sixteen-warp form)
+    const size_t tn = ceil_div(N3, SBN) > 2 * (size_t)ceil_div(N3, 256) ? ceil_div(N3, SBN) : 2 * (size_t)ceil_div(N3, 256);
     SimWorkspace w;
     size_t off = 0;
     auto take = [&](size_t bytes) { void *p = base ? (char *)base + off : nullptr; off += align_up(bytes, 256); return p; };
@@ -252,6 +257,8 @@ static SimWorkspace carve(void *base, int B, int N2, int N3) {
     w.colmax_part = (unsigned long long *)take((size_t)B * tm * N3 * 8);
     w.rowsum_part = (float *)take((size_t)B * tn * 2 * N2 * 4);
     w.colsum_part = (float *)take((size_t)B * tm * N3 * 4);
+    w.colsum4 = (float *)take((size_t)B * tm * 4 * N3 * 4);
+    w.colkey4 = (uint32_t *)take((size_t)B * tm * 4 * N3 * 4);
     w.invR = (float *)take((size_t)B * N2 * 4);
     w.invC = (float *)take((size_t)B * N3 * 4);
     w.val0 = (float *)take((size_t)B * N2 * 4);
@@ -272,12 +279,14 @@ extern "C" size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3) {
     return opb::carve(nullptr, B > 0 ? B : 1, N2 > 0 ? N2 : 1, N3 > 0 ? N3 : 1).bytes;
 }
 
+// planes (optional): {m2 hi fp16, m2 bytes, m3 hi fp16, m3 bytes} -- operand planes some producer has already written (the final projection
+// with OPB_LIN_UNIT_PLANES8); bytes = lo e5m2 plane followed by the hi e4m3 plane.  m2 / m3 are then unused.
 static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
                     float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                     float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
-                    void *stream) {
+                    void *stream, const void *const *planes = nullptr) {
     using namespace opb;
-    OPB_CHECK_ARG(m2 && m3 && conf && matches0 && matches1 && scores0 && scores1 && workspace, "op_sim_dual_softmax: null pointer");
+    OPB_CHECK_ARG((planes || (m2 && m3)) && conf && matches0 && matches1 && scores0 && scores1 && workspace, "op_sim_dual_softmax: null pointer");
     OPB_CHECK_ARG(B > 0 && N2 > 0 && N3 > 0 && B <= 65535, "op_sim_dual_softmax: bad shape B=%d N2=%d N3=%d", B, N2, N3);
     OPB_CHECK_ARG(scale_factor > 0.f, "op_sim_dual_softmax: scale_factor must be positive");
     SimWorkspace w = carve(workspace, B, N2, N3);
@@ -310,7 +319,11 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
         // fp8 mode: the 2-byte lo area holds the e5m2 lo plane (first half) and the e4m3 hi plane (second half)
         uint8_t *m2x = (uint8_t *)w.m2l + (size_t)B * N2 * kD, *m3x = (uint8_t *)w.m3l + (size_t)B * N3 * kD;
         const long long r2 = (long long)B * N2, r3 = (long long)B * N3;
-        if (normalize && f8) {
+        if (planes) {
+            if (!f8) { set_error("op_sim_dual_softmax_planes: the byte planes belong to the pair form with fp8 cross terms (unset OPB_SIM_CG / OPB_SIM_MMA)"); return OPB_ERR_ARG; }
+            w.m2h = (__half *)planes[0]; w.m2l = (__half *)planes[1]; m2x = (uint8_t *)planes[1] + (size_t)B * N2 * kD;
+            w.m3h = (__half *)planes[2]; w.m3l = (__half *)planes[3]; m3x = (uint8_t *)planes[3] + (size_t)B * N3 * kD;
+        } else if (normalize && f8) {
             simtc::k_normalize_split_planes<1><<<ceil_div(r2, 8), 256, 0, st>>>(m2, w.m2h, w.m2l, m2x, r2, simtc::kOperandScale);
             simtc::k_normalize_split_planes<1><<<ceil_div(r3, 8), 256, 0, st>>>(m3, w.m3h, w.m3l, m3x, r3, simtc::kOperandScale);
         } else if (normalize) {
@@ -334,6 +347,60 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
         } else {
             if ((rc = make_tmap_f16_3d(&t2l, w.m2l, B, N2, kD, simtc::BM)) || (rc = make_tmap_f16_3d(&t3l, w.m3l, B, N3, kD, 128))) return rc;
             t2x = t2l; t3x = t3l;
+        }
+        // sixteen epilogue warps (sim_tc16.cuh) are the production form of the pair kernels; OPB_SIM_EW=8 selects the eight-warp form for A/B runs
+        static const bool ew16 = [] { const char *e = getenv("OPB_SIM_EW"); return !(e && e[0] == '8'); }();
+        if (cg == 2 && ew16) {
+            const int tiles_n = ceil_div(N3, simtc16::BN);
+            int splits = ceil_div(2 * 148, (long long)B * p.tiles_m);
+            splits = splits < 1 ? 1 : (splits > tiles_n ? tiles_n : splits);
+            simtc16::Params q{};
+            q.N2 = N2; q.N3 = N3; q.tiles_n = tiles_n; q.tiles_m = p.tiles_m; q.tiles_per_split = ceil_div(tiles_n, splits);
+            splits = ceil_div(tiles_n, q.tiles_per_split);
+            const double log2e = 1.4426950408889634;
+            q.c1 = (float)(log2e / ((double)scale_factor * simtc::kOperandScale * simtc::kOperandScale));
+            q.c0 = (float)(log2e / (double)scale_factor);
+            q.c2 = 2.f * q.c1;
+            q.tma_store = (N3 % 4 == 0) && ((uintptr_t)conf % 16 == 0);
+            if (q.tma_store) { if ((rc = make_tmap_f32_3d_store(&tconf, conf, B, N2, N3, 32))) return rc; } else tconf = t2h;
+            { const char *e = getenv("OPB_SIM_DBG"); q.dbg = e ? atoi(e) : 0; }
+            q.rowsum_part = w.rowsum_part; q.colsum_part = w.colsum4; q.lgR = w.invR; q.lgC = w.invC;
+            q.rowmax_part = w.rowmax_part; q.colkey_part = w.colkey4; q.conf = conf;
+            static bool configured16 = false;
+            if (!configured16) {
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<1>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<1>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2>()));
+                configured16 = true;
+            }
+            cudaLaunchConfig_t cfg = {};
+            cudaLaunchAttribute attr[1];
+            cfg.gridDim = dim3(ceil_div(p.tiles_m, 2) * 2, splits, B);        // a ghost row tile completes the last pair
+            cfg.blockDim = dim3(simtc16::THREADS);
+            cfg.stream = st;
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            cfg.dynamicSmemBytes = simtc16::smem_bytes<1>();
+            if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+            else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<1, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+            k_sim_finalize_sums<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowsum_part, tiles_n * 4, N2, w.invR, 1);
+            k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum4, p.tiles_m * 4, N3, w.invC, 1);
+            OPB_CHECK_LAUNCH();
+            cfg.dynamicSmemBytes = simtc16::smem_bytes<2>();
+            static const bool keys_redux = [] { const char *e = getenv("OPB_SIM_KEYS"); return e && e[0] == 'r'; }();
+            if (f8 && keys_redux) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+            else if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+            else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+            k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, splits * 4, N2, N3, w.idx0, w.val0, conf);
+            simtc16::k_sim_finalize_colkeys<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colkey4, p.tiles_m * 4, N3, N2, w.idx1, w.val1);
+            OPB_CHECK_LAUNCH();
+            const int nmax16 = N2 > N3 ? N2 : N3;
+            k_mutual_select<<<dim3(ceil_div(nmax16, 256), B), 256, 0, st>>>(w.idx0, conf, w.idx1, N2, N3, match_threshold, matches0, matches1, scores0, scores1);
+            OPB_CHECK_LAUNCH();
+            return OPB_OK;
         }
         const int tiles_n = ceil_div(N3, 128 * cg);          // column tiles of the tensor-core passes: 128 wide, 256 for a CTA pair
         // enough CTAs for ~2 waves over 148 SMs: split the column tiles when frames x row tiles is small
@@ -410,4 +477,14 @@ extern "C" int op_sim_dual_softmax_rows(const float *x2, const float *x3, int B,
                                         float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
     return sim_impl(true, true, x2, x3, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
                     workspace, workspace_bytes, stream);
+}
+
+extern "C" int op_sim_dual_softmax_planes(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
+                                          float scale_factor, float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                                          float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
+    OPB_CHECK_ARG(m2_hi && m2_bytes && m3_hi && m3_bytes, "op_sim_dual_softmax_planes: null plane");
+    OPB_CHECK_ARG((((uintptr_t)m2_hi | (uintptr_t)m2_bytes | (uintptr_t)m3_hi | (uintptr_t)m3_bytes) & 15) == 0, "op_sim_dual_softmax_planes: planes must be 16-byte aligned");
+    const void *planes[4] = {m2_hi, m2_bytes, m3_hi, m3_bytes};
+    return sim_impl(true, false, nullptr, nullptr, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
+                    workspace, workspace_bytes, stream, planes);
 }

@@ -250,6 +250,8 @@ int make_tmap_u8_3d(CUtensorMap *map, const void *base, int batch, int rows, int
 int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // same for fp16: box = {32 cols, box_rows, 1} (64-byte rows), 64-byte swizzle
 int make_tmap_f16_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// same for bytes (fp8 planes): box = {64 bytes, box_rows, 1}, 64-byte swizzle
+int make_tmap_u8_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // host: tensor map of an fp16 NHWC image batch [B, H, W, C], box = {64 channels, box_w pixels, box_h rows, 1}, 128-byte swizzle.
 // Coordinates may be negative or past the end: out-of-range pixels are zero-filled (the convolution's zero padding).
 int make_tmap_f16_nhwc(CUtensorMap *map, const void *base, int B, int H, int W, int C, int box_w, int box_h);

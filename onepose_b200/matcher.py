@@ -126,6 +126,7 @@ class GATsSuperGlue(nn.Module):
         # kept as the on-device cross-check of the tensor-core path (tests), not as a fallback
         self.use_tensor_cores = True
         self.two_streams = True      # 2D / 3D streams of a layer on two CUDA streams (tensor-core path)
+        self.fused_final_normalize = True   # final_proj + F.normalize write the similarity kernel's operand planes (False: fp32 rows, for A/B runs and tests)
         self._side = {}
         # Pipelines only (off by default: the drop-in contract returns a pose that is ready on the caller's stream).  True: gather +
         # PnP of a call run on the module's pose stream, so that the (latency-bound, few-CTA) RANSAC of one block of frames overlaps
@@ -577,8 +578,16 @@ class GATsSuperGlue(nn.Module):
         main.wait_stream(side)
         if single3:                                               # no cross layer at all (not the shipped layer list)
             broadcast3()
+        if m2 is None:
+            # final_proj (:241) with F.normalize (:245-246) in its epilogue, written as the similarity kernel's operand planes
+            u2 = (self._ws.get("u2h", (B, N2, _D), torch.float16, dev), self._ws.get("u2b", (2, B, N2, _D), torch.uint8, dev))
+            u3 = (self._ws.get("u3h", (B, N3, _D), torch.float16, dev), self._ws.get("u3b", (2, B, N3, _D), torch.uint8, dev))
+            self._linear_tc(s2.p, pk["Wf_p"], pk["bf"], B, N2, Cp=u2, flags=16384, tag="final")          # OPB_LIN_UNIT_PLANES8
+            self._linear_tc(s3.p, pk["Wf_p"], pk["bf"], B, N3, Cp=u3, flags=16384, tag="final")
+            return u2, u3
         self._linear_tc(s2.p, pk["Wf_p"], pk["bf"], B, N2, C=m2, tag="final")          # final_proj, :241
         self._linear_tc(s3.p, pk["Wf_p"], pk["bf"], B, N3, C=m3, tag="final")
+        return None
 
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
@@ -620,15 +629,22 @@ class GATsSuperGlue(nn.Module):
             raise ValueError(f"bad descriptor shapes {tuple(desc2d.shape)} {tuple(desc3d.shape)} {tuple(leaves.shape)}")
         pk = self._pack_weights(dev)
         db = self._static_db(desc3d, leaves[:, :, :N3 * L], L)
-        m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
-        m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
+        # the final projections leave as unit-row operand planes of the similarity kernel (production), or as fp32 rows (the exact-fp32
+        # cross-check path and the A/B switches of the similarity kernel: OPB_SIM_CG=1, OPB_SIM_MMA=f16, OPB_LINEAR_CG=1, OPB_LIN_DBG)
+        unit_planes = self.use_tensor_cores and self.fused_final_normalize and not any(
+            os.environ.get(k) for k in ("OPB_SIM_CG", "OPB_SIM_MMA", "OPB_LINEAR_CG", "OPB_LIN_DBG"))
+        m2 = m3 = None
+        if not unit_planes:
+            m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
+            m3 = self._ws.get("m3", (B, N3, _D), torch.float32, dev)
+        planes = None
         if self.use_tensor_cores and not self.hparams["with_linear_transform"]:
             # planes-only streams: the query descriptors go from the public channel-major layout straight into planes + column sums
-            self._encode_tc(None, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=desc2d)
+            planes = self._encode_tc(None, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=desc2d)
         else:
             x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
             if self.use_tensor_cores:
-                self._encode_tc(x2, db, pk, B, N2, N3, L, m2, m3, dev)
+                planes = self._encode_tc(x2, db, pk, B, N2, N3, L, m2, m3, dev)
             else:
                 self._encode_simt(x2, db, pk, B, N2, N3, L, m2, m3, dev)
         if not self.use_tensor_cores:                                 # the tensor-core op normalises while it splits the operands
@@ -643,9 +659,13 @@ class GATsSuperGlue(nn.Module):
         nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
         w = self._ws.get("simws", (nbytes,), torch.uint8, dev)
         timeline.work = B * (4.0 * _D * (N2 + N3) + 4.0 * N2 * N3 + 24.0 * (N2 + N3))   # bytes, SURVEY.md 8(d)
-        call("op_sim_dual_softmax_rows" if self.use_tensor_cores else "op_sim_dual_softmax", ptr(m2), ptr(m3), B, N2, N3, float(self.hparams["scale_factor"]),
-                                      float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
-                                      ptr(s1), ptr(w), nbytes, stream_ptr())
+        tail = (B, N2, N3, float(self.hparams["scale_factor"]), float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
+                ptr(s1), ptr(w), nbytes, stream_ptr())
+        if planes is not None:
+            (u2h, u2b), (u3h, u3b) = planes
+            call("op_sim_dual_softmax_planes", ptr(u2h), ptr(u2b), ptr(u3h), ptr(u3b), *tail)
+        else:
+            call("op_sim_dual_softmax_rows" if self.use_tensor_cores else "op_sim_dual_softmax", ptr(m2), ptr(m3), *tail)
         pred = {
             "matches0": i0[0], "matches1": i1[0],                     # batch element 0 only, :269-274
             "matching_scores0": s0[0], "matching_scores1": s1[0],

@@ -361,3 +361,51 @@ def test_channel_major_to_planes_equals_the_three_kernel_path(shape):
     call("op_channel_major_to_planes", ptr(x), x.stride(0), ptr(h1), ptr(l1), ptr(cs1), B, N, stream_ptr())
     torch.cuda.synchronize()
     assert torch.equal(h0, h1) and torch.equal(l0, l1) and torch.equal(cs0, cs1)
+
+
+def test_final_projection_with_fused_normalize_writes_similarity_planes():
+    """OPB_LIN_UNIT_PLANES8: final_proj (GATs_SuperGlue.py:241) + F.normalize (:245-246) in the GEMM epilogue, emitted as the operand
+    planes of op_sim_dual_softmax_planes: hi = fp16(64 u), lo = (64 u - hi) as e5m2, hi again as e4m3."""
+    from onepose_b200._lib import call, ptr, stream_ptr
+    g = torch.Generator().manual_seed(11)
+    B, N = 2, 333
+    x = torch.randn(B, N, 256, generator=g).cuda()
+    x[1, 5] = 0.0
+    W = (torch.randn(256, 256, generator=g) / 16).cuda()
+    bias = (torch.randn(256, generator=g) * 0.1).cuda()
+    split = lambda t: (torch.empty_like(t, dtype=torch.float16), torch.empty_like(t, dtype=torch.float16))
+    xp, wp = split(x), split(W)
+    call("op_split_planes", ptr(x), ptr(xp[0]), ptr(xp[1]), x.numel(), stream_ptr())
+    call("op_split_planes", ptr(W), ptr(wp[0]), ptr(wp[1]), W.numel(), stream_ptr())
+    uh = torch.zeros(B, N, 256, dtype=torch.float16, device="cuda")
+    ub = torch.zeros(2, B, N, 256, dtype=torch.uint8, device="cuda")
+    call("op_linear_tc", ptr(xp[0]), ptr(xp[1]), 256, None, None, 0, ptr(wp[0]), ptr(wp[1]), None, None, ptr(bias), None, ptr(uh), ptr(ub),
+         B, N, 256, 16384, 0, None, None, 1.0, stream_ptr())
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.normalize(x.double() @ W.double().t() + bias.double(), dim=2) * 64.0
+    hi = uh.double()
+    assert float((hi - ref).abs().max()) <= 2.0 ** -11 * 64 * 1.01                   # fp16 rounding of |64 u| <= 64
+    lo = ub[0].view(torch.float8_e5m2).double()
+    assert float((hi + lo - ref).abs().max()) < 6e-4                                  # e5m2 lo: 2 mantissa bits of a remainder <= 2^-12 * 16
+    hx = ub[1].view(torch.float8_e4m3fn).double()
+    assert float((hx - hi).abs().max()) <= 2.0 ** -4 * 64 * 1.01                     # e4m3 copy of hi: 3 mantissa bits
+    # unit rows: |hi + lo| / 64 = 1 (the all-zero input row has the bias as its projection, so it is a unit row too)
+    nrm = ((hi + lo) / 64.0).norm(dim=2)
+    assert float((nrm - 1).abs().max()) < 1e-4
+    # the planes feed the similarity op: same conf as the fp32-rows entry on the unnormalised projection
+    m = (x.double() @ W.double().t() + bias.double()).float()
+    from tests.test_gpu_matcher import _run_sim
+    rows = _run_sim("op_sim_dual_softmax_rows", m[:, :200].contiguous(), m[:, 200:].contiguous())
+    conf = torch.empty(B, 200, 133, device="cuda")
+    i0 = torch.empty(B, 200, dtype=torch.int64, device="cuda"); i1 = torch.empty(B, 133, dtype=torch.int64, device="cuda")
+    s0 = torch.empty(B, 200, device="cuda"); s1 = torch.empty(B, 133, device="cuda")
+    from onepose_b200._lib import lib
+    nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, 200, 133)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    a_h, a_b = uh[:, :200].contiguous(), ub[:, :, :200].contiguous()
+    b_h, b_b = uh[:, 200:].contiguous(), ub[:, :, 200:].contiguous()
+    call("op_sim_dual_softmax_planes", ptr(a_h), ptr(a_b), ptr(b_h), ptr(b_b), B, 200, 133, 0.07, 0.2, ptr(conf), ptr(i0), ptr(i1), ptr(s0), ptr(s1),
+         ptr(ws), nbytes, stream_ptr())
+    torch.cuda.synchronize()
+    rel = ((conf - rows[0]).abs() / rows[0].clamp_min(1e-30)).max().item()
+    assert rel < 2e-4, rel
