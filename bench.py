@@ -28,10 +28,16 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "query frames/sec (match+PnP) at N2d=2048,N3d=8192"
 UNIT = "frames/s"
+# BASELINE.json configs the bench can run (--config): the driver's default is the headline (configs[1]); "large" (configs[2]) and
+# "pnp" (configs[3]) print the same JSON schema for profiles/
+WORKLOADS = {
+    "headline": dict(n2=2048, n3=8192, leaves=8, frames=64, object_id=0, metric="query frames/sec (match+PnP) at N2d=2048,N3d=8192"),
+    "large": dict(n2=4096, n3=32768, leaves=16, frames=4, object_id=1, metric="query frames/sec (match+PnP) at N2d=4096,N3d=32768 (large object model)"),
+}
+METRIC = WORKLOADS["headline"]["metric"]
 N2, N3, LEAVES, FRAMES = 2048, 8192, 8, 64
-PNP_HYPOTHESES = 4096
+PNP_STRESS = dict(ncorr=10000, inlier_ratio=0.3, frames=64, metric="PnP-RANSAC frames/sec at 10k correspondences, 30% inliers (cv2.solvePnPRansac semantics, up to 10000 iterations)")
 
 
 def load_peaks():
@@ -84,71 +90,121 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------- CPU side
-def cpu_frame_runner(object_id=0):
-    """Returns (run_one_frame(f) -> n_matches, cores): the oracle matcher + the reference wrapper over cv2."""
+def cpu_frame_runner(object_id=0, n2=N2, n3=N3, leaves=LEAVES):
+    """Returns (run_one_frame(f) -> n_matches, cores, kind).  kind "reference": the reference's own GATsSuperGlue.forward and
+    ransac_PnP, staged unmodified under oracle/_ref/ by oracle/build_oracle.py (they travel with the working tree); kind "port":
+    the oracle restatement + the same wrapper over cv2, when the files were not staged."""
     import torch
     from onepose_b200 import synth
     from oracle import gats_spg_oracle as orc
     from oracle import pnp_oracle as po
+    from oracle import ref_loader
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     hp = dict(synth.DEFAULT_HPARAMS)
     w = synth.make_weights(0, damped=True)
-    obj = synth.make_object(object_id, N3, LEAVES)
+    obj = synth.make_object(object_id, n3, leaves)
+    ref = ref_loader.load()
+    if ref is not None:
+        RefModel, ref_pnp = ref
+        model = RefModel(hp).eval()
+        model.load_state_dict(w, strict=True)
 
     def run(f):
-        fr = synth.make_frame(obj, f, N2)
+        fr = synth.make_frame(obj, f, n2)
         data = synth.pack_batch(obj, [fr])
         with torch.no_grad():
-            pred, _ = orc.matcher_forward(data, w, hp)
+            pred, _ = model(data) if ref is not None else orc.matcher_forward(data, w, hp)
         mk2, mk3, _ = orc.gather_matches(pred["matches0"].numpy(), pred["matching_scores0"].numpy(),
                                          fr.keypoints2d, obj.keypoints3d)
-        po.ransac_pnp_cv2(fr.K, mk2, mk3, scale=1000)
+        (ref_pnp if ref is not None else po.ransac_pnp_cv2)(fr.K, mk2, mk3, scale=1000)
         return len(mk2)
 
-    return run, cores
+    return run, cores, ("reference" if ref is not None else "port")
 
 
-def time_cpu(steps, warmup):
-    run, cores = cpu_frame_runner()
+def time_cpu(steps, warmup, budget_s=None, **shape):
+    """steps frames (or as many as fit budget_s seconds, at least 2) after warmup; returns (seconds, frames, cores, kind)."""
+    run, cores, kind = cpu_frame_runner(**shape)
     for f in range(warmup):
         run(f)
     t0 = time.perf_counter()
-    for f in range(steps):
-        run(1000 + f)
-    dt = time.perf_counter() - t0
-    return dt, cores
+    n = 0
+    while n < steps:
+        run(1000 + n)
+        n += 1
+        if budget_s is not None and n >= 2 and time.perf_counter() - t0 > budget_s:
+            break
+    return time.perf_counter() - t0, n, cores, kind
+
+
+def cpu_kind_text(kind):
+    return ("the reference's own GATsSuperGlue.forward + ransac_PnP (oracle/_ref, staged unmodified from the reference tree)" if kind == "reference"
+            else "oracle restatement of the matcher (torch CPU) + cv2.solvePnPRansac")
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return                                      # rank 0 alone runs the CPU arm
-    dt, cores = time_cpu(args.steps, args.warmup)
-    fps = args.steps / dt
-    sample = f"{args.steps} single-frame steps (B=1) of the headline workload after {args.warmup} warm-up"
+    if args.config == "pnp":
+        return run_pnp_reference(args)
+    wl = WORKLOADS[args.config]
+    dt, n, cores, kind = time_cpu(args.steps, args.warmup, n2=wl["n2"], n3=wl["n3"], leaves=wl["leaves"], object_id=wl["object_id"])
+    fps = n / dt
+    sample = f"{n} single-frame steps (B=1, the reference's own usage, inference.py:146) of the {args.config} workload after {args.warmup} warm-up: {cpu_kind_text(kind)}"
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": wl["metric"], "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": n,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / n, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"headline: N2d={N2}, N3d={N3} x {LEAVES} leaves, 1 frame per step (B=1), match + gather + "
+        "config": {"workload": f"{args.config}: N2d={wl['n2']}, N3d={wl['n3']} x {wl['leaves']} leaves, 1 frame per step (B=1), match + gather + "
                                "cv2.solvePnPRansac(EPNP, 5 px, 10000 it)", "weights": "random-init, damped (SURVEY.md 8c)"},
-        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
 
 
+def pnp_problems(frames):
+    from onepose_b200 import synth
+    return [synth.make_pnp_problem(200 + f, PNP_STRESS["ncorr"], PNP_STRESS["inlier_ratio"], scale=1000.0) for f in range(frames)]
+
+
+def time_cv2_pnp(prs, budget_s=20.0):
+    """The reference wrapper (eval_utils.py:18-42) over the image's cv2 on the same problems; returns (seconds, frames, kind)."""
+    from oracle import pnp_oracle as po
+    from oracle import ref_loader
+    ref = ref_loader.load()
+    fn = ref[1] if ref is not None else po.ransac_pnp_cv2
+    fn(prs[0]["K"], prs[0]["pts2d"], prs[0]["pts3d"] / 1000.0, scale=1000)
+    t0 = time.perf_counter()
+    n = 0
+    for p in prs:
+        fn(p["K"], p["pts2d"], p["pts3d"] / 1000.0, scale=1000)
+        n += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    return time.perf_counter() - t0, n, ("reference" if ref is not None else "port")
+
+
+def run_pnp_reference(args):
+    prs = pnp_problems(max(args.steps, 2))
+    dt, n, kind = time_cv2_pnp(prs, budget_s=120.0)
+    fps = n / dt
+    print(json.dumps({
+        "impl": "reference", "metric": PNP_STRESS["metric"], "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": n, "warmup": 1,
+        "ms_per_step": 1e3 * dt / n, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "pnp stress (BASELINE.json configs[3]): 10k correspondences, 30 % inliers, one frame per step, ransac_PnP over cv2.solvePnPRansac"},
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": kind, "sample": f"{n} frames after 1 warm-up (cv2 threads: default)"},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+    }))
+
+
 # ---------------------------------------------------------------------------------------------- own arm
-def run_ours(args):
-    import numpy as np
+def init_dist():
     import torch
     import torch.distributed as dist
-    from onepose_b200 import synth
-    from onepose_b200._lib import timeline
-    from onepose_b200.matcher import GATsSuperGlue
-
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -168,32 +224,86 @@ def run_ours(args):
             sys.stdout.flush()
             os.dup2(saved_stdout, 1)
             os.close(saved_stdout)
-    peaks = load_peaks()
+    return rank, local_rank, world, dev
 
-    # --- synthetic workload: this rank's object + FRAMES query frames (seeded) ---
+
+def make_timer(dev, world, extra_streams=()):
+    """timed(fn, steps) -> (max-over-ranks ms, per-rank ms list, last result): K calls bracketed by barrier + synchronize, CUDA events on
+    the current stream; streams the step forks work onto (pose stream) are joined before the end event is recorded."""
+    import torch
+    import torch.distributed as dist
+    from onepose_b200._lib import timeline
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, instrument=False):
+        barrier()
+        timeline.reset()
+        timeline.enabled = instrument
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            out = fn()
+        main = torch.cuda.current_stream(dev)
+        for st in extra_streams:
+            main.wait_stream(st)                      # the last step's gather + PnP + read-back are inside the timed interval
+        e.record()
+        barrier()
+        timeline.enabled = False
+        mine = torch.tensor([s.elapsed_time(e)], device=dev)
+        per_rank = [mine.clone() for _ in range(world)]
+        if world > 1:
+            dist.all_gather(per_rank, mine)
+        per_rank = [float(t.item()) for t in per_rank]
+        return max(per_rank), per_rank, out
+
+    return timed
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from onepose_b200 import synth
+    from onepose_b200._lib import timeline
+    from onepose_b200.matcher import GATsSuperGlue
+
+    rank, local_rank, world, dev = init_dist()
+    peaks = load_peaks()
+    wl = WORKLOADS[args.config]
+    n2, n3, leaves, nframes = wl["n2"], wl["n3"], wl["leaves"], (args.frames or wl["frames"])
+
+    # --- synthetic workload: this rank's object + nframes query frames (seeded; SURVEY.md 8d) ---
     hp = dict(synth.DEFAULT_HPARAMS)
     model = GATsSuperGlue(hp).to(dev).eval()
     model.load_state_dict(synth.make_weights(0, damped=True), strict=True)
-    obj = synth.make_object(rank, N3, LEAVES)
-    frames = [synth.make_frame(obj, f, N2) for f in range(FRAMES)]
+    obj = synth.make_object(wl["object_id"] + rank, n3, leaves)
+    frames = [synth.make_frame(obj, f, n2) for f in range(nframes)]
     host = synth.pack_batch(obj, frames)                       # CPU tensors, DB expand()-ed over the batch
     K_dev = torch.from_numpy(frames[0].K)[None].to(dev)
-    db_dev = {k: host[k][:1].to(dev).expand(FRAMES, *host[k].shape[1:]) for k in
+    db_dev = {k: host[k][:1].to(dev).expand(nframes, *host[k].shape[1:]) for k in
               ("keypoints3d", "descriptors3d_db", "descriptors2d_db")}
     q_pin = {k: host[k].contiguous().pin_memory() for k in ("keypoints2d", "descriptors2d_query")}
     resident = dict(db_dev, **{k: v.to(dev) for k, v in q_pin.items()}, query_intrinsic=K_dev)
-    out_pin = dict(pose=torch.empty(FRAMES, 3, 4, dtype=torch.float64).pin_memory(),
-                   n_inliers=torch.empty(FRAMES, dtype=torch.int32).pin_memory(),
-                   matches0=torch.empty(FRAMES, N2, dtype=torch.int64).pin_memory(),
-                   scores0=torch.empty(FRAMES, N2, dtype=torch.float32).pin_memory())
+    out_pin = dict(pose=torch.empty(nframes, 3, 4, dtype=torch.float64).pin_memory(),
+                   n_inliers=torch.empty(nframes, dtype=torch.int32).pin_memory(),
+                   matches0=torch.empty(nframes, n2, dtype=torch.int64).pin_memory(),
+                   scores0=torch.empty(nframes, n2, dtype=torch.float32).pin_memory())
     h2d_bytes = sum(v.numel() * v.element_size() for v in q_pin.values())
     d2h_bytes = sum(v.numel() * v.element_size() for v in out_pin.values())
+    use_graph = not args.no_graph
+    if use_graph:
+        model.enable_graphs(True)
 
     def step_resident():
         pred, conf = model(resident)
         return pred
 
-    # End to end: every step uploads its 64 query frames from pinned host memory and reads its results back.  The upload of
+    # End to end: every step uploads its query frames from pinned host memory and reads its results back.  The upload of
     # step i+1 is issued on a copy stream while step i computes (a double-buffered input pipeline, what a frame loader
     # does); the first upload of a timed region is not hidden, every upload is inside the region.
     copy_stream = torch.cuda.Stream(device=dev)
@@ -223,48 +333,27 @@ def run_ours(args):
         out_pin["scores0"].copy_(pred["matching_scores0_batched"], non_blocking=True)
         return pred
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps, instrument=False):
-        barrier()
-        timeline.reset()
-        timeline.enabled = instrument
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for _ in range(steps):
-            pred = fn()
-        e.record()
-        barrier()
-        timeline.enabled = False
-        ms = torch.tensor([s.elapsed_time(e)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return ms.item(), pred
-
     # Steps are pipelined as a frame server would run them: gather + PnP of step i go to the module's pose stream and overlap the
-    # matcher of step i+1 (GATsSuperGlue.pnp_overlap); every step's work is complete at the barrier that ends the timed region.
+    # matcher of step i+1 (GATsSuperGlue.pnp_overlap); the pose stream is joined before the end event of the timed region.
     model.pnp_overlap = not args.no_pnp_overlap
+    timed = make_timer(dev, world, extra_streams=[model.pose_stream(dev)] if model.pnp_overlap else [])
     clocks = ClockSampler(local_rank)
     clocks.start()
     for _ in range(max(args.warmup, 3)):
         step_resident()
-    ms, pred = timed(step_resident, args.steps)
+    ms, ms_ranks, pred = timed(step_resident, args.steps)
     clk = clocks.stop()
-    # per-kernel durations (roofline, shares, launch count): the same K steps once more with CUDA events around every
-    # launch and the 2D / 3D streams serialised on one CUDA stream, so that no launch's interval contains another's
-    model.two_streams = False
-    overlap = model.pnp_overlap
-    model.pnp_overlap = False
-    step_resident()
-    ms_serial, _ = timed(step_resident, args.steps, instrument=True)
-    model.two_streams = True
-    model.pnp_overlap = overlap
-    summary = timeline.summary()
-    launches = timeline.launches // args.steps
+    sanity = {"frames_with_pose": int((pred["n_inliers"] > 0).sum()), "mean_matches": float(pred["n_matches"].float().mean()),
+              "mean_inliers": float(pred["n_inliers"].float().mean()), "mean_ransac_iterations": float(pred["ransac_iters"].float().mean())}
+    host_ms = None
+    if rank == 0:                                 # host time to enqueue one step (the GPU runs ahead: this is what a CUDA graph removes)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_resident()
+        host_ms = 1e3 * (time.perf_counter() - t0) / args.steps
+        torch.cuda.synchronize()
+    # end to end (before the instrumented pass, with the production configuration)
     for _ in range(2):
         step_e2e(prefetch_next=False)
     e2e_calls = [0]
@@ -273,14 +362,24 @@ def run_ours(args):
         e2e_calls[0] += 1
         return step_e2e(prefetch_next=e2e_calls[0] < args.steps)
 
-    ms_e2e, pred_e = timed(e2e_step_counted, args.steps)
+    ms_e2e, ms_e2e_ranks, pred_e = timed(e2e_step_counted, args.steps)
+    # per-kernel durations (roofline, shares, launch count): the same K steps once more, launch by launch (no CUDA graph), with CUDA
+    # events around every launch and the 2D / 3D streams serialised on one CUDA stream, so that no launch's interval contains another's
+    model.enable_graphs(False)
+    model.two_streams = False
+    overlap = model.pnp_overlap
+    model.pnp_overlap = False
+    step_resident()
+    timed_serial = make_timer(dev, world)
+    ms_serial, _, _ = timed_serial(step_resident, args.steps, instrument=True)
+    model.two_streams = True
+    model.pnp_overlap = overlap
+    summary = timeline.summary()
+    launches = timeline.launches // args.steps
 
-    total_frames = FRAMES * args.steps * world
+    total_frames = nframes * args.steps * world
     value = total_frames / (ms / 1e3)
     e2e_value = total_frames / (ms_e2e / 1e3)
-    n_inl = pred["n_inliers"].float()
-    sanity = {"frames_with_pose": int((pred["n_inliers"] > 0).sum()), "mean_matches": float(pred["n_matches"].float().mean()),
-              "mean_inliers": float(n_inl.mean())}
 
     if rank == 0:
         # --- per-kernel time shares + roofline of the dominant kernel group -----------------------
@@ -302,49 +401,135 @@ def run_ours(args):
                 traffic = json.load(f)
         except (OSError, ValueError):
             traffic = {}
-        tr = traffic.get(dom)
+        tr = traffic.get(dom) if args.config == "headline" else None
         roofline = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"], "peak": d["peak"], "unit": d["unit"],
                     "frac": d["frac"], "traffic": None if tr is None else tr["traffic_bytes"],
                     "traffic_launch": None if tr is None else tr["launch"], "peak_source": peaks["source"] + (", sustained" if d["bound"] == "tensor" else ""),
                     "share_of_step": d["share"]}
         if d["bound"] == "tensor":
             # fp32-class accuracy from fp16 MMAs costs three MMAs per algorithmic product (hi*hi + lo*hi + hi*lo): the tensor pipe
-            # executes 3x the algorithmic flops that `achieved` counts
+            # executes 3x the algorithmic flops that `achieved` counts; ncu's sm__pipe_tensor..pct of the same launch is in
+            # profiles/ (the cuBLAS figure `peak` itself runs the pipe at ~62 % of nominal under the 1 kW power cap)
             roofline.update(mma_passes=3, achieved_issued=3 * d["achieved"], frac_issued=3 * d["frac"])
         sim = kernels.get("op_sim_dual_softmax_planes") or kernels.get("op_sim_dual_softmax_rows") or kernels.get("op_sim_dual_softmax")
+        sim_roof = None
+        if sim is not None:
+            # achieved = max(bytes / BW, flops / peak) / t with both terms shown.  Algorithmic figures per frame: one
+            # GEMM of 2 N2 N3 256 flops and 4*256*(N2+N3) + 4 N2 N3 + 24 (N2+N3) bytes; what the kernel issues to stay within 1e-3
+            # (two passes, one fp16 + two fp8 MMAs per product) is reported next to it
+            t = sim["ms_per_step"] * 1e-3
+            alg_bytes = nframes * (4.0 * 256 * (n2 + n3) + 4.0 * n2 * n3 + 24.0 * (n2 + n3))
+            alg_flops = nframes * 2.0 * n2 * n3 * 256
+            t_hbm, t_tc = alg_bytes / (peaks["hbm"] * 1e9), alg_flops / (peaks["tensor"] * 1e12)
+            issued = 2 * SIM_MMA_UNITS * alg_flops
+            sim_roof = dict({k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
+                            traffic=(traffic.get("op_sim_dual_softmax_planes") or {}).get("traffic_bytes") if args.config == "headline" else None,
+                            t_hbm_ms=1e3 * t_hbm, t_tensor_ms=1e3 * t_tc, frac_max_of_both=max(t_hbm, t_tc) / t,
+                            mma_passes_fp16_equivalent=SIM_MMA_UNITS, tensor_issued_tflops=issued / t / 1e12,
+                            t_tensor_issued_ms=1e3 * issued / (peaks["tensor"] * 1e12), tensor_frac_issued=issued / t / 1e12 / peaks["tensor"])
+            roofline["north_star_target_kernel"] = dict(kernel="op_sim_dual_softmax_planes", **sim_roof)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            n_cpu = 4
-            dt, cores = time_cpu(n_cpu, 1)
-            cpu = {"value": n_cpu / dt, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"{n_cpu} frames (B=1 per call) of the headline workload after 1 warm-up: oracle torch-CPU matcher "
-                             "+ cv2.solvePnPRansac"}
+            dt, n_cpu, cores, kind = time_cpu(64, 1, budget_s=12.0, n2=n2, n3=n3, leaves=leaves, object_id=wl["object_id"])
+            cpu = {"value": n_cpu / dt, "unit": UNIT, "cores": cores, "kind": kind,
+                   "sample": f"{n_cpu} frames (B=1 per call) of the {args.config} workload after 1 warm-up, {dt:.1f} s: {cpu_kind_text(kind)}"}
         print(json.dumps({
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "metric": wl["metric"], "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "ms_per_step_per_rank": [m / args.steps for m in ms_ranks], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"headline: {FRAMES} frames/step of one object per GPU, N2d={N2}, N3d={N3} x {LEAVES} leaves, "
-                                   f"match + gather + PnP-RANSAC ({PNP_HYPOTHESES} hypotheses/frame)",
+            "config": {"workload": f"{args.config}: {nframes} frames/step of one object per GPU, N2d={n2}, N3d={n3} x {leaves} leaves, "
+                                   f"match + gather + PnP-RANSAC (cv2 semantics: up to 10000 iterations per frame, adaptive stop -- "
+                                   f"{sanity['mean_ransac_iterations']:.0f} run on average here, see sanity)",
                        "weights": "random-init, damped (SURVEY.md 8c) so PnP sees real correspondences",
-                       "l2": "working set per step (~6 GB of activations + 4 GiB conf) exceeds the 126 MB L2; no flush needed",
+                       "l2": "working set per step (activations + conf, several GB) exceeds the 126 MB L2; no flush needed",
                        "pipeline": "gather + PnP of step i on a pose stream, overlapping the matcher of step i+1" if model.pnp_overlap else "none",
+                       "cuda_graph": "one graph per (shape, B): a step is one graph launch" if use_graph else "off (--no-graph): one launch per kernel",
                        "db_resident": True, "parallelism": f"dp{world} (objects sharded, no collective)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                    "ms_per_step": ms_e2e / args.steps,
+                    "ms_per_step": ms_e2e / args.steps, "ms_per_step_per_rank": [m / args.steps for m in ms_e2e_ranks],
                     "h2d": "pinned host -> device on a copy stream, step i+1 uploaded while step i computes (all K uploads in the timed region)"},
             "gpu_launches": launches * args.steps, "gpu_launches_per_step": launches,
-            "kernel_timing": {"how": "CUDA events around every launch in a second pass of the same steps with the two matcher "
-                                     "streams serialised on one CUDA stream", "ms_per_step": ms_serial / args.steps},
+            "host_enqueue_ms_per_step": host_ms,
+            "kernel_timing": {"how": "CUDA events around every launch in a second pass of the same steps, launch by launch (no CUDA graph), with the two "
+                                     "matcher streams serialised on one CUDA stream", "ms_per_step": ms_serial / args.steps},
             "roofline": roofline,
-            "roofline_sim_dual_softmax": None if sim is None else dict(
-                {k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
-                traffic=(traffic.get("op_sim_dual_softmax_planes") or {}).get("traffic_bytes"),
-                # the similarity is computed twice (statistics pass, write pass); a product is one fp16 MMA plus two fp8 MMAs at twice
-                # the rate (= 2 fp16-equivalent passes; 3 with OPB_SIM_MMA=f16 / OPB_SIM_CG=1)
-                mma_passes_fp16_equivalent=SIM_MMA_UNITS,
-                tensor_issued_tflops=2 * SIM_MMA_UNITS * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12,
-                tensor_frac_issued=2 * SIM_MMA_UNITS * 2.0 * FRAMES * N2 * N3 * 256 / (sim["ms_per_step"] * 1e-3) / 1e12 / peaks["tensor"]),
+            "roofline_sim_dual_softmax": sim_roof,
             "cpu_baseline": cpu, "clocks": clk, "kernels": kernels, "sanity": sanity,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_pnp_ours(args):
+    """BASELINE.json configs[3]: F frames of 10k correspondences at 30 % inliers through op_pnp_ransac (cv2 semantics)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from onepose_b200._lib import timeline
+    from onepose_b200.pnp import ransac_pnp_batched
+
+    rank, local_rank, world, dev = init_dist()
+    peaks = load_peaks()
+    F = args.frames or PNP_STRESS["frames"]
+    prs = pnp_problems(F)
+    S = PNP_STRESS["ncorr"]
+    pin = dict(K=torch.from_numpy(np.stack([p["K"] for p in prs])).pin_memory(),
+               p2=torch.from_numpy(np.stack([p["pts2d"] for p in prs])).pin_memory(),
+               p3=torch.from_numpy(np.stack([p["pts3d"] for p in prs])).pin_memory())
+    counts = torch.full((F,), S, dtype=torch.int32, device=dev)
+    res = {k: v.to(dev) for k, v in pin.items()}
+    out_pin = dict(pose=torch.empty(F, 3, 4, dtype=torch.float64).pin_memory(), n_inliers=torch.empty(F, dtype=torch.int32).pin_memory())
+    h2d = sum(v.numel() * v.element_size() for v in pin.values())
+    d2h = sum(v.numel() * v.element_size() for v in out_pin.values())
+
+    def step_resident():
+        return ransac_pnp_batched(res["K"], res["p2"], res["p3"], counts, scale=1000.0, return_debug=True)
+
+    def step_e2e():
+        up = {k: v.to(dev, non_blocking=True) for k, v in pin.items()}
+        r = ransac_pnp_batched(up["K"], up["p2"], up["p3"], counts, scale=1000.0)
+        out_pin["pose"].copy_(r["pose"], non_blocking=True)
+        out_pin["n_inliers"].copy_(r["n_inliers"], non_blocking=True)
+        return r
+
+    timed = make_timer(dev, world)
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    ms, ms_ranks, r = timed(step_resident, args.steps)
+    clk = clocks.stop()
+    step_e2e()
+    ms_e2e, _, _ = timed(step_e2e, args.steps)
+    ms_serial, _, _ = timed(step_resident, args.steps, instrument=True)
+    summary = timeline.summary()
+    evaluated = int((r["hyp_counts"] >= 0).sum())            # hypotheses the adaptive rounds actually solved + scored this step
+    iters = r["iters_run"].float()
+    if rank == 0:
+        fps = F * args.steps * world / (ms / 1e3)
+        # algorithmic bytes of the inlier count: every evaluated hypothesis streams the frame's correspondences (20 B each, float32) once
+        count_bytes = evaluated * S * 20.0
+        t = ms / args.steps * 1e-3
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            dt, n, kind = time_cv2_pnp(prs, budget_s=20.0)
+            cpu = {"value": n / dt, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": kind, "sample": f"{n} of the same frames through ransac_PnP over cv2.solvePnPRansac after 1 warm-up, {dt:.1f} s"}
+        print(json.dumps({
+            "metric": PNP_STRESS["metric"], "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "ms_per_step_per_rank": [m / args.steps for m in ms_ranks], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"pnp stress (BASELINE.json configs[3]): {F} frames/step of {S} correspondences, 30 % inliers, cv2 sample stream, adaptive rounds "
+                                   f"up to 10000 hypotheses; {evaluated / F:.0f} hypotheses evaluated and {float(iters.mean()):.0f} sequential iterations replayed per frame",
+                       "l2": "20 B x 10k correspondences per frame stay L2 / L1 resident: the kernel is compute / latency bound (SURVEY.md 8d), HBM GB/s for completeness"},
+            "hypotheses_per_s": evaluated / t, "hypotheses_evaluated_per_frame": evaluated / F, "ransac_iterations_per_frame": float(iters.mean()),
+            "e2e": {"value": F * args.steps * world / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": timeline.launches, "gpu_launches_per_step": timeline.launches // args.steps,
+            "roofline": {"kernel": "k_pnp_hypotheses (inlier count)", "bound": "hbm", "achieved": count_bytes / t / 1e9, "peak": peaks["hbm"], "unit": "GB/s",
+                         "frac": count_bytes / t / 1e9 / peaks["hbm"], "traffic": None,
+                         "note": "bytes the inlier count streams from cache per evaluated hypothesis; the solve side is fp64 EPnP (latency bound)"},
+            "cpu_baseline": cpu, "clocks": clk,
+            "kernels": {k: {"ms_per_step": v[0] / args.steps, "calls_per_step": v[1] / args.steps} for k, v in summary.items()},
+            "sanity": {"mean_inliers": float(r["n_inliers"].float().mean()), "frames_with_pose": int((r["n_inliers"] > 0).sum())},
         }))
     if world > 1:
         dist.destroy_process_group()
@@ -361,6 +546,10 @@ def main():
     ap.add_argument("--no-pnp-overlap", action="store_true", help="gather + PnP on the matcher's stream (no pipelining across steps)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", default="headline", choices=["headline", "large", "pnp"],
+                    help="BASELINE.json configs[1] (default, the metric's configuration), configs[2] (large object), configs[3] (PnP stress)")
+    ap.add_argument("--frames", type=int, default=0, help="frames per step (default: the workload's)")
+    ap.add_argument("--no-graph", action="store_true", help="enqueue every kernel from the host instead of one CUDA graph per step")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -371,7 +560,10 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
-    run_ours(args)
+    if args.config == "pnp":
+        run_pnp_ours(args)
+    else:
+        run_ours(args)
 
 
 if __name__ == "__main__":

@@ -300,6 +300,13 @@ int op_pnp_ransac(const double *pts2d, const double *pts3d, const int32_t *count
                   double reproj_thr, double confidence, int max_iters, double scale,
                   double *pose, uint8_t *inlier_mask, int32_t *n_inliers, int32_t *iters_run,
                   int32_t *hyp_counts, double *hyp_pose, void *workspace, size_t workspace_bytes, void *stream);
+/* Optional Levenberg-Marquardt polish of the poses op_pnp_ransac returned, on each frame's inliers (north_star item 4, "followed by a final
+ * LM refinement").  NOT part of the parity path: the reference call (eval_utils.py:28-29) ends with cv2's EPnP on the inliers.  pts2d / pts3d /
+ * count / K / scale as for op_pnp_ransac; inlier_mask [F,stride] and n_inliers [F] are its outputs; pose [F,3,4] is refined in place
+ * (frames with fewer than 4 inliers are left alone).  rms (optional) [F,2]: reprojection RMS in pixels over the inliers before and after. */
+int op_pnp_refine_lm(const double *pts2d, const double *pts3d, const int32_t *count, int F, int stride, const double *K,
+                     const uint8_t *inlier_mask, const int32_t *n_inliers, double scale, int max_iters, double *pose, double *rms,
+                     void *stream);
 
 #ifdef __cplusplus
 }

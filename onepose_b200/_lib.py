@@ -76,6 +76,7 @@ _SIGS = {
     "op_gather_matches": (i32, [vp, vp, vp, vp, i64, i32, i32, i32, f64, vp, vp, vp, vp, vp, vp]),
     "op_pnp_workspace_bytes": (sz, [i32, i32, i32]),
     "op_pnp_cv_samples": (i32, [vp, i32, i32, vp, vp, vp]),
+    "op_pnp_refine_lm": (i32, [vp, vp, vp, i32, i32, vp, vp, vp, f64, i32, vp, vp, vp]),
     "op_pnp_ransac": (i32, [vp, vp, vp, i32, i32, vp, vp, vp, i32, f64, f64, i32, f64,
                             vp, vp, vp, vp, vp, vp, vp, sz, vp]),
 }

@@ -44,6 +44,13 @@ k_gather_matches(const int64_t *__restrict__ matches0, const float *__restrict__
         __syncthreads();
     }
     if (tid == 0) count[b] = base;
+    // rows past the compacted list are zero, so that callers can hand in uninitialised buffers
+    for (int pos = base + tid; pos < N2; pos += 1024) {
+        const long long o = (long long)b * N2 + pos;
+        out2d[o * 2] = 0.0; out2d[o * 2 + 1] = 0.0;
+        out3d[o * 3] = 0.0; out3d[o * 3 + 1] = 0.0; out3d[o * 3 + 2] = 0.0;
+        out_conf[o] = 0.f; out_qidx[o] = 0;
+    }
 }
 
 }  // namespace opb

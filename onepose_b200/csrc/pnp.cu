@@ -202,3 +202,4 @@ __device__ void block_reduce(double *v, double *scratch /* [8][K] */, double *ou
 
 #include "pnp_p3p.cuh"
 #include "pnp_refit.cuh"
+#include "pnp_lm.cuh"

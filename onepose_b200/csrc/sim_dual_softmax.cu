@@ -390,8 +390,11 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
             k_sim_finalize_sums<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colsum4, p.tiles_m * 4, N3, w.invC, 1);
             OPB_CHECK_LAUNCH();
             cfg.dynamicSmemBytes = simtc16::smem_bytes<2>();
-            static const bool keys_redux = [] { const char *e = getenv("OPB_SIM_KEYS"); return e && e[0] == 'r'; }();
-            if (f8 && keys_redux) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
+            // conf leaves as TMA stores of 16 rows x 128 bytes (OPB_SIM_STORE=narrow: 32 rows x 64 bytes, the eight-warp form's boxes)
+            static const bool wide = [] { const char *e = getenv("OPB_SIM_STORE"); return !(e && e[0] == 'n'); }();
+            CUtensorMap tconf_w = tconf;
+            if (f8 && wide && q.tma_store) { if ((rc = make_tmap_f32_3d_store_wide(&tconf_w, conf, B, N2, N3, 16))) return rc; }
+            if (f8 && wide) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q));
             else if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
             else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
             k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, splits * 4, N2, N3, w.idx0, w.val0, conf);

@@ -42,7 +42,7 @@ struct Params {
     uint32_t *colkey_part;                            // [B][tiles_m * 4][N3]: conf bits, low 7 bits = 127 - row inside the CTA's 128 rows
     float *conf;
     int tma_store;
-    int dbg;                                          // OPB_SIM_DBG (timing experiments): 1 = no conf stores, 8 = no MMAs
+    int dbg;                                          // OPB_SIM_DBG (timing experiments): 1 = no conf stores, 4 = stores into one L2-resident patch, 8 = no MMAs
 };
 
 struct Barriers {
@@ -50,7 +50,7 @@ struct Barriers {
     uint32_t tmem_base;
 };
 
-template <int PASS, int F8, int KEYS_REDUX = 0>
+template <int PASS, int F8, int WIDE = 0>
 __global__ void __launch_bounds__(THREADS, 1)
 k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l, const __grid_constant__ CUtensorMap tm_m2x,
         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l, const __grid_constant__ CUtensorMap tm_m3x,
@@ -223,7 +223,6 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
             // resolve to the smaller row; the exact score is read back from conf by k_mutual_select)
             const int tc_c = lane & 15, tc_par = lane >> 4;
             const uint32_t rinv0 = 127u - (uint32_t)(quad * 32 + tc_par);
-            const uint32_t rinv_lane = 127u - (uint32_t)(quad * 32 + lane);
             uint32_t tc_off[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) tc_off[k] = (uint32_t)(tc_par * 64 + (((tc_c >> 2) ^ k) << 4) + (tc_c & 3) * 4);
@@ -249,6 +248,46 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
                     if (cc == 1) release_acc(as);
                     const int col0 = colq + cc * 32;
                     const float lgc = cc ? lg1 : lg0;
+                    if (WIDE) {
+                        // 32 columns of arithmetic; then the chunk leaves as two TMA stores of 16 rows x 128 BYTES (whole 128-byte lines of
+                        // conf per row instead of 64-byte halves), staged by the half-warp that owns the rows; the column keys are read
+                        // back transposed from the same staging buffer (lane = column, 16 rows per half, bank-conflict-free under the
+                        // 128-byte swizzle)
+                        uint32_t bm0 = 0u, bm1 = 0u;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            v[i] = tc::ex2(fmaf(v[i], p.c2, rowc + __shfl_sync(0xffffffffu, lgc, i)));
+                            if (i < 16) bm0 = max(bm0, __float_as_uint(v[i])); else bm1 = max(bm1, __float_as_uint(v[i]));
+                        }
+                        if (bm0 > row_best) { row_best = bm0; row_blk = (uint32_t)col0; }
+                        if (bm1 > row_best) { row_best = bm1; row_blk = (uint32_t)(col0 + 16); }
+                        uint32_t ck = 0u;
+#pragma unroll
+                        for (int hf = 0; hf < 2; ++hf) {
+                            if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
+                            __syncwarp();
+                            if ((lane >> 4) == hf) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q)
+                                    *reinterpret_cast<float4 *>(stg + (lane & 15) * 128 + ((q ^ (lane & 7)) << 4)) =
+                                        make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                            }
+                            tc::fence_proxy_async();
+                            __syncwarp();
+                            if (p.tma_store && lane == 0 && !(p.dbg & 1)) {
+                                if (p.dbg & 4) tc::tma_store_3d(&tm_conf, stg, col0 & 255, quad * 32 + hf * 16, 0);   // timing experiment: every store lands in one L2-resident patch
+                                else tc::tma_store_3d(&tm_conf, stg, col0, m0 + quad * 32 + hf * 16, b);
+                                tc::tma_store_commit();
+                            }
+                            const uint32_t rinv = 127u - (uint32_t)(quad * 32 + hf * 16);
+#pragma unroll
+                            for (int r = 0; r < 16; ++r) {
+                                const uint32_t w = *reinterpret_cast<const uint32_t *>(stg + r * 128 + ((((lane >> 2) ^ (r & 7)) << 4) | ((lane & 3) << 2)));
+                                ck = max(ck, (w & 0xFFFFFF80u) | (rinv - (uint32_t)r));
+                            }
+                        }
+                        if (tile_ok && col0 + lane < p.N3) p.colkey_part[part_row * p.N3 + col0 + lane] = ck;
+                    } else {
 #pragma unroll
                     for (int hc = 0; hc < 2; ++hc) {
                         // 16 columns of arithmetic, then their store: the TMA engine reads the staging buffer while the column keys are built
@@ -274,25 +313,6 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
                             tc::tma_store_3d(&tm_conf, stg, col0 + hc * 16, m0 + quad * 32, b);
                             tc::tma_store_commit();
                         }
-                        if (KEYS_REDUX) {
-                            // column keys by warp reduction (REDUX.MAX): one instruction per column instead of a transposed read-back
-                            // of the staged block (16 LDS + 16 VIMNMX per lane and a third of the epilogue's shared-memory traffic)
-                            uint32_t ck[16];
-#pragma unroll
-                            for (int e = 0; e < 16; ++e)
-                                ck[e] = __reduce_max_sync(0xffffffffu, (__float_as_uint(v[16 * hc + e]) & 0xFFFFFF80u) | rinv_lane);
-                            const int kcol = col0 + 16 * hc;
-                            if (lane == 0 && tile_ok) {
-                                uint32_t *dst = p.colkey_part + part_row * p.N3 + kcol;
-                                if (vec_ok && kcol + 15 < p.N3) {
-#pragma unroll
-                                    for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4 *>(dst + 4 * q) = make_uint4(ck[4 * q], ck[4 * q + 1], ck[4 * q + 2], ck[4 * q + 3]);
-                                } else {
-#pragma unroll
-                                    for (int e = 0; e < 16; ++e) if (kcol + e < p.N3) dst[e] = ck[e];
-                                }
-                            }
-                        } else {
                         // column keys: 16 rows of one parity per lane (even rows sit in banks 0-15, odd rows in 16-31: conflict-free)
                         uint32_t ck = 0u;
 #pragma unroll
@@ -303,7 +323,7 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
                         ck = max(ck, __shfl_xor_sync(0xffffffffu, ck, 16));
                         const int kcol = col0 + 16 * hc + lane;
                         if (lane < 16 && tile_ok && kcol < p.N3) p.colkey_part[part_row * p.N3 + kcol] = ck;
-                        }
+                    }
                     }
                     if (!p.tma_store && row_ok) {
                         if (vec_ok && col0 + 31 < p.N3) {

@@ -248,6 +248,8 @@ int make_tmap_u8_3d(CUtensorMap *map, const void *base, int batch, int rows, int
 // host: tensor map of an fp32 [batch, rows, cols] row-major array for TMA stores, box = {16 cols, box_rows, 1}, 64-byte swizzle
 // (cols must be a multiple of 4: global strides are multiples of 16 bytes).
 int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// fp32 stores with whole 128-byte lines per row: box = {32 cols, box_rows, 1}, 128-byte swizzle (staging buffer 1024-byte aligned)
+int make_tmap_f32_3d_store_wide(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // same for fp16: box = {32 cols, box_rows, 1} (64-byte rows), 64-byte swizzle
 int make_tmap_f16_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // same for bytes (fp8 planes): box = {64 bytes, box_rows, 1}, 64-byte swizzle

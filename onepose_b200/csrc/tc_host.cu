@@ -54,6 +54,10 @@ int make_tmap_f32_3d_store(CUtensorMap *map, const void *base, int batch, int ro
     return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, batch, rows, cols, 16, box_rows, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
+int make_tmap_f32_3d_store_wide(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows) {
+    return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, batch, rows, cols, 32, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
 int make_tmap_u8_3d_store(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows) {
     return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, batch, rows, cols, 64, box_rows, CU_TENSOR_MAP_SWIZZLE_64B);
 }

@@ -134,6 +134,11 @@ class GATsSuperGlue(nn.Module):
         # wait for it.  Work that consumes the pose can also be enqueued on ``pose_stream(device)`` directly.
         self.pnp_overlap = False
         self._pose_streams = {}
+        # CUDA graphs (enable_graphs): one captured graph per (device, shapes, object DB, weights) so that a forward is a few host calls
+        # instead of ~150 launches from Python -- see _forward_graphed
+        self._graphs_on = False
+        self._graphs = {}
+        self.pnp_refine = None       # None = cv2's result (parity mode); "lm" = optional Levenberg-Marquardt polish (pnp.py)
 
     # ------------------------------------------------------------------ weights in kernel layout
     def _weights_key(self):
@@ -622,6 +627,27 @@ class GATsSuperGlue(nn.Module):
             return self._forward_cuda(data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
 
     def _forward_cuda(self, data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev):
+        K = data.get("query_intrinsic", data.get("K"))
+        scale = float(data.get("pnp_scale", 1000.0))
+        if self._graphs_on and self.use_tensor_cores and self._trace is None and not timeline.enabled:
+            return self._forward_graphed(kpts2d, kpts3d, desc2d, desc3d, leaves, K, scale, dev)
+        pred, conf, i0, s0 = self._match(kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
+        if K is not None:
+            from . import pnp
+            if self.pnp_overlap:
+                main, ps = torch.cuda.current_stream(dev), self.pose_stream(dev)
+                ps.wait_stream(main)                                  # the matches are complete
+                with torch.cuda.stream(ps):
+                    pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=scale, refine=self.pnp_refine))
+                    for t in (i0, s0, kpts2d, kpts3d):                # read on the pose stream after the caller may have dropped them
+                        t.record_stream(ps)
+                    pred["pose_event"] = ps.record_event()
+            else:
+                pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=scale, refine=self.pnp_refine))
+        return pred, conf
+
+    def _match(self, kpts2d, kpts3d, desc2d, desc3d, leaves, dev):
+        """The matcher proper (:232-274) on the current stream: returns (pred, conf, matches0 [B,N2], scores0 [B,N2])."""
         B, D, N2 = desc2d.shape
         N3 = desc3d.shape[2]
         L = int(leaves.shape[2] / N3)                                 # GATs.py:65
@@ -658,9 +684,9 @@ class GATsSuperGlue(nn.Module):
         s1 = torch.empty(B, N3, dtype=torch.float32, device=dev)
         nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
         w = self._ws.get("simws", (nbytes,), torch.uint8, dev)
-        timeline.work = B * (4.0 * _D * (N2 + N3) + 4.0 * N2 * N3 + 24.0 * (N2 + N3))   # bytes, SURVEY.md 8(d)
         tail = (B, N2, N3, float(self.hparams["scale_factor"]), float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
                 ptr(s1), ptr(w), nbytes, stream_ptr())
+        timeline.work = B * (4.0 * _D * (N2 + N3) + 4.0 * N2 * N3 + 24.0 * (N2 + N3))   # bytes, SURVEY.md 8(d)
         if planes is not None:
             (u2h, u2b), (u3h, u3b) = planes
             call("op_sim_dual_softmax_planes", ptr(u2h), ptr(u2b), ptr(u3h), ptr(u3b), *tail)
@@ -672,20 +698,83 @@ class GATsSuperGlue(nn.Module):
             "matches0_batched": i0, "matches1_batched": i1,
             "matching_scores0_batched": s0, "matching_scores1_batched": s1,
         }
-        K = data.get("query_intrinsic", data.get("K"))
+        return pred, conf, i0, s0
+
+    # ------------------------------------------------------------------ CUDA graphs
+    def enable_graphs(self, on=True):
+        """Serving mode: ``forward`` replays one captured CUDA graph per (device, B, N2, N3, L, object DB, weights, intrinsics layout)
+        instead of enqueuing ~150 launches from Python ("CUDA graphs per (shape, B) to keep 8 GPUs fed").  The inputs of a
+        call are copied into the graph's static buffers; the tensors of ``pred`` / ``conf`` are the graph's static outputs: two slots
+        are used in turn, so the results of a call stay valid until the second next call with the same key.  The object DB tensors are
+        captured by address (they are static: keep them alive and unmodified, as ``ObjectDB`` does).  With ``pnp_overlap`` the gather runs
+        at the end of the matcher graph and the RANSAC is a second graph on the pose stream, overlapping the next call's matcher."""
+        self._graphs_on = bool(on)
+        if not on:
+            self._graphs.clear()
+        return self
+
+    def _forward_graphed(self, kpts2d, kpts3d, desc2d, desc3d, leaves, K, scale, dev):
+        from . import pnp
+        B, _, N2 = desc2d.shape
+        Kt = None
         if K is not None:
-            from . import pnp
+            Kt = (K if isinstance(K, torch.Tensor) else torch.as_tensor(K)).to(device=dev, dtype=torch.float64).reshape(-1, 3, 3)
+        key = (dev.index, B, N2, tuple(desc3d.shape), tuple(leaves.shape), tuple(kpts3d.shape), desc3d.data_ptr(), leaves.data_ptr(), kpts3d.data_ptr(),
+               desc3d._version, leaves._version, kpts3d._version, desc3d.stride(0), leaves.stride(0), kpts3d.stride(0),
+               None if Kt is None else Kt.shape[0], scale, self.pnp_overlap, self.pnp_refine, self.two_streams, self.fused_final_normalize,
+               float(self.hparams["match_threshold"]), float(self.hparams["scale_factor"])) + self._weights_key()
+        ent = self._graphs.get(key)
+        if ent is None:
+            if len(self._graphs) >= 2:                                # static outputs (conf!) are large: keep at most two shapes alive
+                self._graphs.pop(next(iter(self._graphs)))
+            ent = self._graphs[key] = self._capture(kpts2d, kpts3d, desc2d, desc3d, leaves, Kt, scale, dev)
+        slot = ent["slots"][ent["turn"]]
+        ent["turn"] ^= 1
+        main = torch.cuda.current_stream(dev)
+        if slot["pose_event"] is not None:
+            main.wait_event(slot["pose_event"])                       # the RANSAC that last read this slot's gather buffers has finished
+        slot["desc2d"].copy_(desc2d, non_blocking=True)
+        slot["kpts2d"].copy_(kpts2d, non_blocking=True)
+        if Kt is not None:
+            slot["K"].copy_(Kt, non_blocking=True)
+        slot["match_graph"].replay()
+        pred = dict(slot["pred"])
+        if Kt is not None:
             if self.pnp_overlap:
-                main, ps = torch.cuda.current_stream(dev), self.pose_stream(dev)
-                ps.wait_stream(main)                                  # the matches are complete
+                ps = self.pose_stream(dev)
+                ps.wait_stream(main)
                 with torch.cuda.stream(ps):
-                    pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
-                    for t in (i0, s0, kpts2d, kpts3d):                # read on the pose stream after the caller may have dropped them
-                        t.record_stream(ps)
-                    pred["pose_event"] = ps.record_event()
+                    slot["pnp_graph"].replay()
+                    slot["pose_event"] = pred["pose_event"] = ps.record_event()
             else:
-                pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=float(data.get("pnp_scale", 1000.0))))
-        return pred, conf
+                slot["pnp_graph"].replay()
+        return pred, slot["conf"]
+
+    def _capture(self, kpts2d, kpts3d, desc2d, desc3d, leaves, Kt, scale, dev):
+        from . import pnp
+        # one eager call first: weights packed, DB cached, every workspace buffer allocated, every kernel's attributes configured
+        _, _, i0, s0 = self._match(kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
+        if Kt is not None:
+            pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, Kt, scale=scale, refine=self.pnp_refine)
+        torch.cuda.synchronize(dev)
+        slots = []
+        for _ in range(2):
+            slot = dict(desc2d=desc2d.detach().clone().contiguous(), kpts2d=kpts2d.detach().clone().contiguous(),
+                        K=None if Kt is None else Kt.detach().clone().contiguous(), pose_event=None, pnp_graph=None)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                pred, conf, i0, s0 = self._match(slot["kpts2d"], kpts3d, slot["desc2d"], desc3d, leaves, dev)
+                gathered = pnp.gather_matches_device(i0, s0, slot["kpts2d"], kpts3d, scale) if Kt is not None else None
+            slot.update(match_graph=g, conf=conf)
+            if Kt is not None:
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2, pool=g.pool()):
+                    pred.update(pnp.pose_from_gathered(gathered, slot["K"], scale, refine=self.pnp_refine))
+                slot["pnp_graph"] = g2
+            slot["pred"] = pred
+            slots.append(slot)
+        torch.cuda.synchronize(dev)
+        return dict(slots=slots, turn=0, keep=(desc3d, leaves, kpts3d))
 
 
 _POSE_KEYS = ("mkpts2d", "mkpts3d", "mconf", "n_matches", "match_query_idx", "pose", "inliers", "n_inliers", "ransac_iters")

@@ -51,8 +51,11 @@ def cv_sample_stream(npoints: int, count: int) -> np.ndarray:
     return out
 
 
+LM_ITERS = 20               # cv2's solvePnPRefineLM default iteration cap
+
+
 def ransac_pnp_batched(K, pts2d, pts3d, counts, samples=None, sample_set=None, scale=1.0,
-                       hypotheses=DEFAULT_HYPOTHESES, return_debug=False):
+                       hypotheses=DEFAULT_HYPOTHESES, return_debug=False, refine=None):
     """Batched PnP-RANSAC on device.
 
     K [F,3,3] float64, pts2d [F,S,2] / pts3d [F,S,3] float64 (pts3d already multiplied by ``scale``),
@@ -80,20 +83,29 @@ def ransac_pnp_batched(K, pts2d, pts3d, counts, samples=None, sample_set=None, s
     n_inl = torch.empty(F, dtype=torch.int32, device=dev)
     iters = torch.empty(F, dtype=torch.int32, device=dev)
     hyp_counts = torch.empty(F, H, dtype=torch.int32, device=dev)
-    hyp_pose = torch.zeros(F, H, 6, dtype=torch.float64, device=dev)
+    hyp_pose = torch.empty(F, H, 6, dtype=torch.float64, device=dev)      # only evaluated hypotheses are ever read back
     nbytes = lib.op_pnp_workspace_bytes(F, S, H)
     ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         call("op_pnp_ransac", ptr(pts2d), ptr(pts3d), ptr(counts), F, S, ptr(K), ptr(samples), ptr(sample_set), H,
                                 REPROJ_ERROR, CONFIDENCE, MAX_ITERS, float(scale), ptr(pose), ptr(mask), ptr(n_inl),
                                 ptr(iters), ptr(hyp_counts), ptr(hyp_pose), ptr(ws), nbytes, stream_ptr())
-    out = dict(pose=pose, inlier_mask=mask.bool(), n_inliers=n_inl, iters_run=iters)
+    out = dict(pose=pose, inlier_mask=mask.view(torch.bool), n_inliers=n_inl, iters_run=iters)      # the kernel writes 0 / 1 bytes
+    if refine not in (None, "lm"):
+        raise ValueError(f"refine={refine!r}: None (cv2's result, the parity mode) or 'lm'")
+    if refine == "lm":
+        # opt-in polish (north_star item 4): Levenberg-Marquardt on the winner's inliers, float64, analytic Jacobian (csrc/pnp_lm.cuh)
+        rms = torch.empty(F, 2, dtype=torch.float64, device=dev)
+        with torch.cuda.device(dev):
+            call("op_pnp_refine_lm", ptr(pts2d), ptr(pts3d), ptr(counts), F, S, ptr(K), ptr(mask), ptr(n_inl), float(scale), LM_ITERS, ptr(pose),
+                 ptr(rms), stream_ptr())
+        out["reproj_rms"] = rms
     if return_debug:
         out.update(hyp_counts=hyp_counts, hyp_pose=hyp_pose)
     return out
 
 
-def ransac_PnP(K, pts_2d, pts_3d, scale=1, device=None):
+def ransac_PnP(K, pts_2d, pts_3d, scale=1, device=None, refine=None):
     """Same signature / return triple as the reference ``ransac_PnP`` (eval_utils.py:18-42).
 
     numpy or torch inputs; numpy float64 outputs: ``pose`` [3,4], ``pose_homo`` [4,4] and ``inliers`` (int32
@@ -110,7 +122,7 @@ def ransac_PnP(K, pts_2d, pts_3d, scale=1, device=None):
         return np.eye(4)[:3], np.eye(4), []
     S = max(n, 1)
     r = ransac_pnp_batched(Kt[None], p2[None], p3[None], torch.tensor([n], dtype=torch.int32, device=dev),
-                           scale=float(scale), hypotheses=_hypotheses_for(n))
+                           scale=float(scale), hypotheses=_hypotheses_for(n), refine=refine)
     pose = r["pose"][0].cpu().numpy()
     pose_homo = np.concatenate([pose, np.array([[0, 0, 0, 1.0]])], axis=0)
     n_in = int(r["n_inliers"][0])
@@ -123,31 +135,47 @@ def _hypotheses_for(n):
     return DEFAULT_HYPOTHESES if n > 5 else 1
 
 
-def pose_from_matches(matches0, scores0, kpts2d, kpts3d, K, scale=1000.0, hypotheses=DEFAULT_HYPOTHESES):
-    """Device-side version of the caller's gather + PnP (inference.py:147-155).
-
-    matches0 [B,N2] int64, scores0 [B,N2], kpts2d [B,N2,2], kpts3d [B,N3,3] (batch stride may be 0),
-    K [3,3] or [B,3,3].  Returns the extra ``pred`` keys documented in ``GATsSuperGlue.forward``.
-    """
+def gather_matches_device(matches0, scores0, kpts2d, kpts3d, scale=1000.0):
+    """Device-side valid-match gather of the caller (inference.py:147-152): matches0 [B,N2] int64, scores0 [B,N2], kpts2d [B,N2,2],
+    kpts3d [B,N3,3] (batch stride may be 0).  Returns dict(mkpts2d [B,N2,2] f64, mkpts3d_scaled [B,N2,3] f64 = kpts3d * scale, mconf,
+    match_query_idx, n_matches), valid rows first in ascending query order, zeros behind them."""
     dev = matches0.device
     B, N2 = matches0.shape
     N3 = kpts3d.shape[1]
     k2 = kpts2d.float().contiguous()
     shared3 = kpts3d.shape[0] == 1 or kpts3d.stride(0) == 0
     k3 = kpts3d[:1].float().contiguous() if shared3 else kpts3d.float().contiguous()
-    out2d = torch.zeros(B, N2, 2, dtype=torch.float64, device=dev)
-    out3d = torch.zeros(B, N2, 3, dtype=torch.float64, device=dev)
-    conf = torch.zeros(B, N2, dtype=torch.float32, device=dev)
-    qidx = torch.zeros(B, N2, dtype=torch.int32, device=dev)
+    out2d = torch.empty(B, N2, 2, dtype=torch.float64, device=dev)
+    out3d = torch.empty(B, N2, 3, dtype=torch.float64, device=dev)
+    conf = torch.empty(B, N2, dtype=torch.float32, device=dev)
+    qidx = torch.empty(B, N2, dtype=torch.int32, device=dev)
     count = torch.empty(B, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         call("op_gather_matches", ptr(matches0), ptr(scores0.contiguous()), ptr(k2), ptr(k3), 0 if shared3 else N3 * 3,
                                     B, N2, N3, float(scale), ptr(out2d), ptr(out3d), ptr(conf), ptr(qidx), ptr(count),
                                     stream_ptr())
+    return dict(mkpts2d=out2d, mkpts3d_scaled=out3d, mconf=conf, match_query_idx=qidx, n_matches=count)
+
+
+def pose_from_gathered(g, K, scale=1000.0, hypotheses=DEFAULT_HYPOTHESES, refine=None):
+    """PnP-RANSAC on gathered matches (inference.py:153-155).  K [3,3] or [B,3,3]; returns the pose keys of ``pred``.
+    refine="lm": optional Levenberg-Marquardt polish of the pose on the winner's inliers (off by default: cv2's last step is EPnP)."""
+    dev = g["mkpts2d"].device
+    B = g["mkpts2d"].shape[0]
     Kt = torch.as_tensor(np.asarray(K) if not isinstance(K, torch.Tensor) else K).to(device=dev, dtype=torch.float64)
     Kt = Kt.reshape(-1, 3, 3)
     if Kt.shape[0] == 1:
         Kt = Kt.expand(B, 3, 3)
-    r = ransac_pnp_batched(Kt, out2d, out3d, count, scale=scale, hypotheses=hypotheses)
-    return dict(mkpts2d=out2d, mkpts3d=out3d / scale, mconf=conf, n_matches=count, match_query_idx=qidx,
-                pose=r["pose"], inliers=r["inlier_mask"], n_inliers=r["n_inliers"], ransac_iters=r["iters_run"])
+    r = ransac_pnp_batched(Kt, g["mkpts2d"], g["mkpts3d_scaled"], g["n_matches"], scale=scale, hypotheses=hypotheses, refine=refine)
+    return dict(mkpts2d=g["mkpts2d"], mkpts3d=g["mkpts3d_scaled"] / scale, mconf=g["mconf"], n_matches=g["n_matches"],
+                match_query_idx=g["match_query_idx"], pose=r["pose"], inliers=r["inlier_mask"], n_inliers=r["n_inliers"],
+                ransac_iters=r["iters_run"])
+
+
+def pose_from_matches(matches0, scores0, kpts2d, kpts3d, K, scale=1000.0, hypotheses=DEFAULT_HYPOTHESES, refine=None):
+    """Device-side version of the caller's gather + PnP (inference.py:147-155).
+
+    matches0 [B,N2] int64, scores0 [B,N2], kpts2d [B,N2,2], kpts3d [B,N3,3] (batch stride may be 0),
+    K [3,3] or [B,3,3].  Returns the extra ``pred`` keys documented in ``GATsSuperGlue.forward``.
+    """
+    return pose_from_gathered(gather_matches_device(matches0, scores0, kpts2d, kpts3d, scale), K, scale, hypotheses, refine)
