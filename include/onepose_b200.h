@@ -107,6 +107,17 @@ int op_instnorm_finalize(const double *stats_partial, int B, int row_tiles, int 
 size_t op_kv_reduce_workspace_bytes(int B, int M);
 int op_kv_reduce(const float *kv, float *KV, float *Ksum, int B, int M, void *workspace,
                  size_t workspace_bytes, void *stream);
+/* op_kv_reduce without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernels, same summation order and therefore the same bits as op_kv_reduce; the chunk partials live in a file-scope
+ * static __device__ array of OPB_KV_STATIC_SCRATCH_BYTES (8 MiB, held by every GPU that loads the library until the process exits).
+ * Limit: op_kv_reduce_workspace_bytes(B, M) <= OPB_KV_STATIC_SCRATCH_BYTES, i.e. B * ceil(M / 256) <= 126 (three frames at M = 8192);
+ * larger shapes return OPB_ERR_WORKSPACE with a message and launch nothing.  Every call on a device shares the array: calls in one
+ * stream are ordered, calls that overlap on the GPU (two streams, unordered graph branches) RACE on it.  Nothing has to be cleared
+ * between calls (every partial that is read is written first).  Calls no cudaMalloc / cudaFree / allocating routine. */
+#define OPB_KV_STATIC_SCRATCH_BYTES (8u << 20)
+size_t op_kv_reduce_static_max_bytes(void);
+int op_kv_reduce_static(const float *kv, float *KV, float *Ksum, int B, int M, void *stream);
 /* out[b,n,h*64+q] = (sum_d Q'[b,n,h,d] KV[b,h,d,q]) * M / (sum_d Q'[b,n,h,d] Ksum[b,h,d] + 1e-6)  (:97-98) */
 int op_attn_apply(const float *Qp, const float *KV, const float *Ksum, float *out, int B, int N, int M,
                   void *stream);

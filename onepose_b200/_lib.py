@@ -34,6 +34,8 @@ _SIGS = {
     "op_instnorm_finalize": (i32, [vp, i32, i32, i32, i32, f32, vp, vp, vp]),
     "op_kv_reduce_workspace_bytes": (sz, [i32, i32]),
     "op_kv_reduce": (i32, [vp, vp, vp, i32, i32, vp, sz, vp]),
+    "op_kv_reduce_static_max_bytes": (sz, []),
+    "op_kv_reduce_static": (i32, [vp, vp, vp, i32, i32, vp]),
     "op_attn_apply": (i32, [vp, vp, vp, vp, i32, i32, i32, vp]),
     "op_split_planes": (i32, [vp, vp, vp, i64, vp]),
     "op_norm_relu_split": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
@@ -110,7 +112,7 @@ def stream_ptr():
 LAUNCHES = {
     "op_atb_tc": 1, "op_kv_post": 1, "op_split_planes": 1, "op_norm_relu_split": 1, "op_linear_tc": 1, "op_instnorm_finalize_tc": 1, "op_attn_apply_planes": 1,
     "op_channel_major_to_point_major": 1, "op_channel_major_to_planes": 1, "op_gats_leaf_aggregate": 1, "op_linear": 1, "op_instnorm_finalize": 1,
-    "op_kv_reduce": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 9, "op_sim_dual_softmax_rows": 9, "op_sim_dual_softmax_planes": 7, "op_sim_dual_softmax_simt": 7,
+    "op_kv_reduce": 2, "op_kv_reduce_static": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 9, "op_sim_dual_softmax_rows": 9, "op_sim_dual_softmax_planes": 7, "op_sim_dual_softmax_simt": 7,
     "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 5,
 }
 

@@ -172,3 +172,68 @@ extern "C" int op_attn_apply_planes(const float *Qp, const float *KV, const floa
     OPB_CHECK_LAUNCH();
     return OPB_OK;
 }
+
+// ---- op_kv_reduce_static: the same KV reduction for callers that may not allocate -----------------------------------------
+// No counterpart in the reference; added (callers under CUDA graph capture, tight serving
+// loops and harnesses that forbid cudaMalloc cannot provide a workspace).  The chunk partials live in a file-scope device array of
+// OPB_KV_STATIC_SCRATCH_BYTES (8 MiB) that every GPU loading the library holds until the process exits.
+//  * In HOST code the array's name is only a stand-in for the symbol, not a device address: the address is resolved once per
+//    device, with that device current, by cudaGetSymbolAddress, and that pointer is what the kernels get.
+//  * Nothing in the array has to start at zero: k_kv_partial writes every element k_kv_finalize reads (all nchunks partials of
+//    every (frame, head)), so the previous call's contents are never observed and nothing is cleared.
+//  * All calls on a device share the one array: two calls that overlap on the GPU (different streams, or graph branches without
+//    a dependency) race on it.  Calls in one stream are ordered and safe.
+// The entry point calls no cudaMalloc / cudaFree and no allocating library routine.
+#include <mutex>
+
+namespace opb {
+
+constexpr size_t kKvStaticFloats = OPB_KV_STATIC_SCRATCH_BYTES / sizeof(float);
+static __device__ __align__(256) float g_kv_static_scratch[kKvStaticFloats];
+
+// device address of g_kv_static_scratch on the CURRENT device (resolved at first use per device, then cached)
+static cudaError_t kv_static_scratch_ptr(float **out) {
+    constexpr int kMaxDevices = 64;
+    static float *cached[kMaxDevices] = {};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        float *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_kv_static_scratch);     // `dev` is current: this is that device's copy of the array
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return cudaSuccess;
+}
+
+}  // namespace opb
+
+extern "C" size_t op_kv_reduce_static_max_bytes(void) { return OPB_KV_STATIC_SCRATCH_BYTES; }
+
+extern "C" int op_kv_reduce_static(const float *kv, float *KV, float *Ksum, int B, int M, void *stream) {
+    OPB_CHECK_ARG(kv && KV && Ksum, "op_kv_reduce_static: null pointer");
+    OPB_CHECK_ARG(B > 0 && M > 0 && B <= 65535, "op_kv_reduce_static: bad shape B=%d M=%d", B, M);
+    const size_t need = op_kv_reduce_workspace_bytes(B, M);
+    if (need > (size_t)OPB_KV_STATIC_SCRATCH_BYTES) {
+        opb::set_error("op_kv_reduce_static: B=%d M=%d needs %zu bytes of scratch, the static array holds %zu (B * ceil(M / 256) <= %zu); "
+                       "use op_kv_reduce with a caller-owned workspace", B, M, need, (size_t)OPB_KV_STATIC_SCRATCH_BYTES,
+                       (size_t)OPB_KV_STATIC_SCRATCH_BYTES / (opb::kHeads * opb::kKvPartial * sizeof(float)));
+        return OPB_ERR_WORKSPACE;
+    }
+    float *scratch = nullptr;
+    OPB_CHECK_CUDA(opb::kv_static_scratch_ptr(&scratch));
+    const int nchunks = opb::ceil_div(M, opb::kKvChunk);
+    dim3 grid(nchunks, opb::kHeads, B);
+    opb::k_kv_partial<<<grid, 256, 0, (cudaStream_t)stream>>>(kv, scratch, M, nchunks);
+    OPB_CHECK_LAUNCH();
+    dim3 grid2(opb::ceil_div(opb::kKvPartial, 256), B * opb::kHeads);
+    opb::k_kv_finalize<<<grid2, 256, 0, (cudaStream_t)stream>>>(scratch, KV, Ksum, nchunks);
+    OPB_CHECK_LAUNCH();
+    return OPB_OK;
+}
