@@ -524,7 +524,7 @@ def run_pnp_ours(args):
             "hypotheses_per_s": evaluated / t, "hypotheses_evaluated_per_frame": evaluated / F, "ransac_iterations_per_frame": float(iters.mean()),
             "e2e": {"value": F * args.steps * world / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": timeline.launches, "gpu_launches_per_step": timeline.launches // args.steps,
-            "roofline": {"kernel": "k_pnp_hypotheses (inlier count)", "bound": "hbm", "achieved": count_bytes / t / 1e9, "peak": peaks["hbm"], "unit": "GB/s",
+            "roofline": {"kernel": "k_pnp_count (inlier count)", "bound": "hbm", "achieved": count_bytes / t / 1e9, "peak": peaks["hbm"], "unit": "GB/s",
                          "frac": count_bytes / t / 1e9 / peaks["hbm"], "traffic": None,
                          "note": "bytes the inlier count streams from cache per evaluated hypothesis; the solve side is fp64 EPnP (latency bound)"},
             "cpu_baseline": cpu, "clocks": clk,

@@ -44,6 +44,15 @@ int op_channel_major_to_point_major(const float *in, float *out, int B, int C, i
  * in one pass, bit-identical, C = 256. */
 int op_channel_major_to_planes(const float *in, long long bstride_in, void *hi, void *lo, float *colsum_partial, int B, int N,
                                void *stream);
+/* Ragged batches.  The reference runs one frame per call with whatever keypoint count SuperPoint found (inference.py:140-146,
+ * GATs_SuperGlue.py:203-278 at B = 1); a batch of frames with different counts is handed over padded to a common N, with
+ * row_counts [B] (device, int32) giving each frame's valid rows.  The *_ragged forms of the entry points on the query stream take
+ * that array (NULL = every row valid, the plain entry point): rows past a frame's count are left out of every cross-row quantity
+ * (column sums, K'^T X and Ksum, InstanceNorm1d statistics, the dual-softmax sums and arg-maxima), so that frame b's results equal
+ * the reference run on its first row_counts[b] points alone.  Padding rows of the outputs: zero planes, conf rows of +0,
+ * matches0 = -1.  This one zero-fills the padding points' planes. */
+int op_channel_major_to_planes_ragged(const float *in, long long bstride_in, void *hi, void *lo, float *colsum_partial, int B, int N,
+                                      const int *row_counts, void *stream);
 
 /* ---- (1) GATs leaf aggregation: GATs.py:62-123 ------------------------------------------------
  * For every 3D point n (and frame b): logits over its (include_self ? 1 : 0) + L entries,
@@ -140,6 +149,12 @@ int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, cons
                  const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B,
                  int rows_per_batch, int Cout, int flags, int elu_cols, float *stats_partial, const float *ksum,
                  float zscale_num, void *stream);
+/* Ragged form: OPB_LIN_COLSUM / OPB_LIN_CSTATS_RELU statistics over rows < row_counts[b] only, and the COLSUM producers (K', Q'',
+ * the new x) write zeros to the padding rows.  OPB_LIN_STATS is refused. */
+int op_linear_tc_ragged(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
+                        const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B,
+                        int rows_per_batch, int Cout, int flags, int elu_cols, float *stats_partial, const float *ksum,
+                        float zscale_num, const int *row_counts, void *stream);
 int op_linear_tc_stat_parts(int rows_per_batch);
 /* The merge projection folded into MLP layer 0 (:119,135-147): message = Q'' P_b^T + bm and h = W0 [x | message] + b0, so
  *   h = W0a x + (W0b P_b) Q'' + const = W0a x + P'_b Q'' + const, with P'_b[c,(h,d)] = sum_q KV_h[d,q] (W0b Wm)[c,(h,q)] straight from
@@ -156,11 +171,17 @@ int op_linear_tc_stat_parts(int rows_per_batch);
 int op_colsum_partial(const float *x, int B, int rows, int C, float *partial, void *stream);
 int op_mlp_center_bias(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
                        const void *Pl, int p_batched, int B, int rows, float *bias_out, void *stream);
+/* ragged form: the means divide by row_counts[b] (at least 1) instead of rows */
+int op_mlp_center_bias_ragged(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
+                              const void *Pl, int p_batched, int B, int rows, const int *row_counts, float *bias_out, void *stream);
 int op_scale_weight_planes(const float *W, const float *rstd, int B, int Cout, int K, void *hi, void *lo, void *stream);
 /* op_instnorm_finalize_tc + op_scale_weight_planes in one launch: rstd from the CSTATS_RELU partials [B][parts][K][2] straight
  * into the per-frame layer-1 weight planes [B,Cout,K] (K a multiple of 64); rstd [B,K] is written too when not NULL. */
 int op_instnorm_scale_weight_planes(const float *stats_partial, int B, int parts, int rows_per_batch, float eps, const float *W,
                                     int Cout, int K, void *hi, void *lo, float *rstd, void *stream);
+/* ragged form: variance over row_counts[b] rows (at least 1) */
+int op_instnorm_scale_weight_planes_ragged(const float *stats_partial, int B, int parts, int rows_per_batch, const int *row_counts,
+                                           float eps, const float *W, int Cout, int K, void *hi, void *lo, float *rstd, void *stream);
 int op_instnorm_finalize_tc(const float *stats_partial, const float *bias, int B, int parts, int C, int rows_per_batch,
                             float eps, float *mean, float *rstd, void *stream);
 /* Source side of linear attention on the tensor cores (:88-99), re-associated so that the V projection is never
@@ -206,6 +227,13 @@ int op_sim_dual_softmax_rows(const float *x2, const float *x3, int B, int N2, in
 int op_sim_dual_softmax_planes(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
                                float scale_factor, float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                                float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream);
+/* Ragged form (see op_channel_major_to_planes_ragged): n2_counts [B] valid query rows per frame.  Rows past the count take no part in
+ * the column softmax / column arg-maxima, their conf rows are +0 and their matches0 -1; frame b equals the reference run on its first
+ * n2_counts[b] query points (GATs_SuperGlue.py:245-274 at B = 1).  Sixteen-warp pair form only. */
+int op_sim_dual_softmax_planes_ragged(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
+                                      const int *n2_counts, float scale_factor, float match_threshold, float *conf, int64_t *matches0,
+                                      int64_t *matches1, float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
+                                      void *stream);
 /* Same contract on fp32 CUDA cores (exact fp32 dot products, no tensor cores): kept as the on-device
  * cross-check of the tcgen05 split-precision kernel, not used by the product path. */
 int op_sim_dual_softmax_simt(const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,

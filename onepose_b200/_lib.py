@@ -28,6 +28,7 @@ _SIGS = {
     "op_abi_version": (i32, []),
     "op_channel_major_to_point_major": (i32, [vp, vp, i32, i32, i32, i64, vp]),
     "op_channel_major_to_planes": (i32, [vp, i64, vp, vp, vp, i32, i32, vp]),
+    "op_channel_major_to_planes_ragged": (i32, [vp, i64, vp, vp, vp, i32, i32, vp, vp]),
     "op_gats_leaf_aggregate": (i32, [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, vp]),
     "op_linear": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp]),
     "op_linear_row_tiles": (i32, [i32]),
@@ -59,12 +60,15 @@ _SIGS = {
     "op_sp_desc_prepare": (i32, [vp, i32, i32, vp, vp]),
     "op_sp_sample": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "op_linear_tc": (i32, [vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, f32, vp]),
+    "op_linear_tc_ragged": (i32, [vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp]),
     "op_linear_tc_stat_parts": (i32, [i32]),
     "op_colsum_partial": (i32, [vp, i32, i32, i32, vp, vp]),
     "op_mlp_center_bias": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp]),
+    "op_mlp_center_bias_ragged": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp]),
     "op_scale_weight_planes": (i32, [vp, vp, i32, i32, i32, vp, vp, vp]),
     "op_instnorm_finalize_tc": (i32, [vp, vp, i32, i32, i32, i32, f32, vp, vp, vp]),
     "op_instnorm_scale_weight_planes": (i32, [vp, i32, i32, i32, f32, vp, i32, i32, vp, vp, vp, vp]),
+    "op_instnorm_scale_weight_planes_ragged": (i32, [vp, i32, i32, i32, vp, f32, vp, i32, i32, vp, vp, vp, vp]),
     "op_atb_chunks": (i32, [i32]),
     "op_atb_tc": (i32, [vp, vp, vp, vp, i32, i32, vp, vp]),
     "op_kv_post": (i32, [vp, i32, vp, i32, vp, vp, vp, i32, i32, f32, vp, vp, vp, vp, vp]),
@@ -75,6 +79,7 @@ _SIGS = {
     "op_sim_dual_softmax_simt": (i32, [vp, vp, i32, i32, i32, f32, f32, vp, vp, vp, vp, vp, vp, sz, vp]),
     "op_sim_dual_softmax_rows": (i32, [vp, vp, i32, i32, i32, f32, f32, vp, vp, vp, vp, vp, vp, sz, vp]),
     "op_sim_dual_softmax_planes": (i32, [vp, vp, vp, vp, i32, i32, i32, f32, f32, vp, vp, vp, vp, vp, vp, sz, vp]),
+    "op_sim_dual_softmax_planes_ragged": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, f32, f32, vp, vp, vp, vp, vp, vp, sz, vp]),
     "op_gather_matches": (i32, [vp, vp, vp, vp, i64, i32, i32, i32, f64, vp, vp, vp, vp, vp, vp]),
     "op_pnp_workspace_bytes": (sz, [i32, i32, i32]),
     "op_pnp_cv_samples": (i32, [vp, i32, i32, vp, vp, vp]),
@@ -112,8 +117,8 @@ def stream_ptr():
 LAUNCHES = {
     "op_atb_tc": 1, "op_kv_post": 1, "op_split_planes": 1, "op_norm_relu_split": 1, "op_linear_tc": 1, "op_instnorm_finalize_tc": 1, "op_attn_apply_planes": 1,
     "op_channel_major_to_point_major": 1, "op_channel_major_to_planes": 1, "op_gats_leaf_aggregate": 1, "op_linear": 1, "op_instnorm_finalize": 1,
-    "op_kv_reduce": 2, "op_kv_reduce_static": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 9, "op_sim_dual_softmax_rows": 9, "op_sim_dual_softmax_planes": 7, "op_sim_dual_softmax_simt": 7,
-    "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 5,
+    "op_kv_reduce": 2, "op_kv_reduce_static": 2, "op_attn_apply": 1, "op_l2_normalize_rows": 1, "op_sim_dual_softmax": 9, "op_sim_dual_softmax_rows": 9, "op_sim_dual_softmax_planes": 7, "op_sim_dual_softmax_planes_ragged": 7, "op_linear_tc_ragged": 1, "op_channel_major_to_planes_ragged": 1, "op_sim_dual_softmax_simt": 7,
+    "op_gather_matches": 1, "op_pnp_cv_samples": 1, "op_pnp_ransac": 25,
 }
 
 

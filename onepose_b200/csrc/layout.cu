@@ -28,12 +28,15 @@ __global__ void k_cm_to_pm(const float *__restrict__ in, float *__restrict__ out
 // op_colsum_partial produce, bit for bit (same split, same summation order), without the fp32 point-major copy.
 // Block = 32 points x 256 channels: warps read channel rows (128 bytes along N), thread = channel writes 32 points.
 __global__ void __launch_bounds__(256) k_cm_to_planes(const float *__restrict__ in, long long bstride_in, __half *__restrict__ hi,
-                                                      __half *__restrict__ lo, float2 *__restrict__ colsum, int N, int parts) {
+                                                      __half *__restrict__ lo, float2 *__restrict__ colsum, int N, int parts,
+                                                      const int *__restrict__ row_counts) {
     __shared__ float tile[256][33];
     const int b = blockIdx.y, part = blockIdx.x, n0 = part * 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float *src = in + (long long)b * bstride_in;
-    for (int c = warp; c < 256; c += 8) tile[c][lane] = (n0 + lane < N) ? src[(long long)c * N + n0 + lane] : 0.f;
+    // ragged batch: points past this frame's count are padding -- zero planes, no part in the sums
+    const int nvalid = row_counts ? min(N, __ldg(row_counts + b)) : N;
+    for (int c = warp; c < 256; c += 8) tile[c][lane] = (n0 + lane < nvalid) ? src[(long long)c * N + n0 + lane] : 0.f;
     __syncthreads();
     const int c = threadIdx.x, n1 = max(0, min(32, N - n0));      // a part past the end (N not a multiple of 128) holds zero sums
     float s = 0.f;
@@ -50,15 +53,20 @@ __global__ void __launch_bounds__(256) k_cm_to_planes(const float *__restrict__ 
 
 }  // namespace opb
 
-extern "C" int op_channel_major_to_planes(const float *in, long long bstride_in, void *hi, void *lo, float *colsum_partial, int B, int N,
-                                          void *stream) {
+extern "C" int op_channel_major_to_planes_ragged(const float *in, long long bstride_in, void *hi, void *lo, float *colsum_partial, int B, int N,
+                                                 const int *row_counts, void *stream) {
     OPB_CHECK_ARG(in && hi && lo && colsum_partial, "op_channel_major_to_planes: null pointer");
     OPB_CHECK_ARG(B >= 0 && N >= 0 && B <= 65535, "op_channel_major_to_planes: bad shape B=%d N=%d", B, N);
     if (B == 0 || N == 0) return OPB_OK;
     const int parts = opb::ceil_div(N, 128) * 4;           // = op_linear_tc_stat_parts(N)
-    opb::k_cm_to_planes<<<dim3(parts, B), 256, 0, (cudaStream_t)stream>>>(in, bstride_in, (__half *)hi, (__half *)lo, (float2 *)colsum_partial, N, parts);
+    opb::k_cm_to_planes<<<dim3(parts, B), 256, 0, (cudaStream_t)stream>>>(in, bstride_in, (__half *)hi, (__half *)lo, (float2 *)colsum_partial, N, parts, row_counts);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
+}
+
+extern "C" int op_channel_major_to_planes(const float *in, long long bstride_in, void *hi, void *lo, float *colsum_partial, int B, int N,
+                                          void *stream) {
+    return op_channel_major_to_planes_ragged(in, bstride_in, hi, lo, colsum_partial, B, N, nullptr, stream);
 }
 
 extern "C" int op_channel_major_to_point_major(const float *in, float *out, int B, int C, int N,

@@ -76,13 +76,14 @@ __global__ void k_colsum_partial(const float *__restrict__ x, int rows, int C, i
 __global__ void __cluster_dims__(1, 8, 1) __launch_bounds__(256)
 k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__restrict__ qpart, int qparts,
                   const float *__restrict__ W0aT, const __half *__restrict__ Ph, const __half *__restrict__ Pl, int p_batched,
-                  int rows, float *__restrict__ bias_out) {
+                  int rows, const int *__restrict__ row_counts, float *__restrict__ bias_out) {
     __shared__ float red[4][64];
     __shared__ float mean_loc[64];
     __shared__ __align__(16) float mean_in[512];
     __shared__ float pdot[64];
     cg::cluster_group cluster = cg::this_cluster();
     const int b = blockIdx.x, r = blockIdx.y, tid = threadIdx.x, j = tid & 63, sl = tid >> 6;
+    if (row_counts) rows = max(1, min(rows, __ldg(row_counts + b)));      // ragged batch: the mean is over this frame's valid rows
     {
         const float2 *src = r < 4 ? xpart : qpart;
         const int parts = r < 4 ? xparts : qparts;
@@ -130,11 +131,13 @@ k_mlp_center_bias(const float2 *__restrict__ xpart, int xparts, const float2 *__
 // per-frame layer-1 weights: W1s[b][o][c] = W1[o][c] * rstd[b][c] as split-precision planes.  CTA (b, g) owns channels
 // [64g, 64g+64): it needs nobody else's statistics.
 __global__ void __launch_bounds__(256)
-k_instnorm_scale_weight_planes(const float2 *__restrict__ part, int parts, int rows, float eps, const float *__restrict__ W,
-                               int Cout, int K, __half *__restrict__ hi, __half *__restrict__ lo, float *__restrict__ rstd_out) {
+k_instnorm_scale_weight_planes(const float2 *__restrict__ part, int parts, int rows, const int *__restrict__ row_counts, float eps,
+                               const float *__restrict__ W, int Cout, int K, __half *__restrict__ hi, __half *__restrict__ lo,
+                               float *__restrict__ rstd_out) {
     __shared__ double red_s[16][64], red_q[16][64];
     __shared__ float rs[64];
     const int b = blockIdx.x, g = blockIdx.y, tid = threadIdx.x;
+    if (row_counts) rows = max(1, min(rows, __ldg(row_counts + b)));      // ragged batch: statistics over this frame's valid rows
     {   // thread = (slice of 16, 4 channels): 32-byte loads, many in flight (four slices of scalar loads were a chain of L2 round trips)
         const int fs = tid >> 4, f4 = (tid & 15) * 4;
         double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
@@ -229,14 +232,19 @@ extern "C" int op_colsum_partial(const float *x, int B, int rows, int C, float *
     return OPB_OK;
 }
 
-extern "C" int op_mlp_center_bias(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
-                                  const void *Pl, int p_batched, int B, int rows, float *bias_out, void *stream) {
+extern "C" int op_mlp_center_bias_ragged(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
+                                         const void *Pl, int p_batched, int B, int rows, const int *row_counts, float *bias_out, void *stream) {
     OPB_CHECK_ARG(xpart && qpart && W0aT && Ph && Pl && bias_out && B > 0 && rows > 0 && xparts > 0 && qparts > 0 && B <= 65535,
                   "op_mlp_center_bias: bad argument");
     opb::k_mlp_center_bias<<<dim3(B, 8), 256, 0, (cudaStream_t)stream>>>((const float2 *)xpart, xparts, (const float2 *)qpart, qparts, W0aT,
-                                                                         (const __half *)Ph, (const __half *)Pl, p_batched, rows, bias_out);
+                                                                         (const __half *)Ph, (const __half *)Pl, p_batched, rows, row_counts, bias_out);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
+}
+
+extern "C" int op_mlp_center_bias(const float *xpart, int xparts, const float *qpart, int qparts, const float *W0aT, const void *Ph,
+                                  const void *Pl, int p_batched, int B, int rows, float *bias_out, void *stream) {
+    return op_mlp_center_bias_ragged(xpart, xparts, qpart, qparts, W0aT, Ph, Pl, p_batched, B, rows, nullptr, bias_out, stream);
 }
 
 extern "C" int op_scale_weight_planes(const float *W, const float *rstd, int B, int Cout, int K, void *hi, void *lo, void *stream) {
@@ -246,15 +254,20 @@ extern "C" int op_scale_weight_planes(const float *W, const float *rstd, int B, 
     return OPB_OK;
 }
 
-extern "C" int op_instnorm_scale_weight_planes(const float *stats_partial, int B, int parts, int rows_per_batch, float eps, const float *W,
-                                               int Cout, int K, void *hi, void *lo, float *rstd, void *stream) {
+extern "C" int op_instnorm_scale_weight_planes_ragged(const float *stats_partial, int B, int parts, int rows_per_batch, const int *row_counts,
+                                                      float eps, const float *W, int Cout, int K, void *hi, void *lo, float *rstd, void *stream) {
     OPB_CHECK_ARG(stats_partial && W && hi && lo, "op_instnorm_scale_weight_planes: null pointer");
     OPB_CHECK_ARG(B > 0 && B <= 65535 && parts > 0 && rows_per_batch > 0 && Cout > 0 && K > 0 && K % 64 == 0,
                   "op_instnorm_scale_weight_planes: bad shape B=%d parts=%d rows=%d Cout=%d K=%d", B, parts, rows_per_batch, Cout, K);
-    opb::k_instnorm_scale_weight_planes<<<dim3(B, K / 64), 256, 0, (cudaStream_t)stream>>>((const float2 *)stats_partial, parts, rows_per_batch, eps,
-                                                                                           W, Cout, K, (__half *)hi, (__half *)lo, rstd);
+    opb::k_instnorm_scale_weight_planes<<<dim3(B, K / 64), 256, 0, (cudaStream_t)stream>>>((const float2 *)stats_partial, parts, rows_per_batch, row_counts,
+                                                                                           eps, W, Cout, K, (__half *)hi, (__half *)lo, rstd);
     OPB_CHECK_LAUNCH();
     return OPB_OK;
+}
+
+extern "C" int op_instnorm_scale_weight_planes(const float *stats_partial, int B, int parts, int rows_per_batch, float eps, const float *W,
+                                               int Cout, int K, void *hi, void *lo, float *rstd, void *stream) {
+    return op_instnorm_scale_weight_planes_ragged(stats_partial, B, parts, rows_per_batch, nullptr, eps, W, Cout, K, hi, lo, rstd, stream);
 }
 
 extern "C" int op_linear_tc_stat_parts(int rows_per_batch) { return opb::ceil_div(rows_per_batch, opb::lintc::BM) * 4; }
@@ -270,10 +283,11 @@ extern "C" int op_instnorm_finalize_tc(const float *stats_partial, const float *
     return OPB_OK;
 }
 
-extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
-                            const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
-                            int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream) {
+extern "C" int op_linear_tc_ragged(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
+                                   const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
+                                   int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, const int *row_counts, void *stream) {
     using namespace opb;
+    OPB_CHECK_ARG(!row_counts || !(flags & OPB_LIN_STATS), "op_linear_tc_ragged: OPB_LIN_STATS is not available with row_counts (use OPB_LIN_CSTATS_RELU)");
     OPB_CHECK_ARG(A1h && A1l && Wh && Wl, "op_linear_tc: null operand plane");
     OPB_CHECK_ARG(K1 > 0 && K1 % lintc::BK == 0 && K2 >= 0 && K2 % lintc::BK == 0, "op_linear_tc: K1=%d K2=%d must be multiples of 64", K1, K2);
     OPB_CHECK_ARG((K2 == 0) == (A2h == nullptr) && (A2h == nullptr) == (A2l == nullptr), "op_linear_tc: A2/K2 mismatch");
@@ -347,6 +361,7 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     p.w2 = W2h ? ((flags & OPB_LIN_W2BATCHED) ? 2 : 1) : 0;
     p.w2_ident = w2_ident ? 1 : 0;
     p.a_bcast = ((flags & OPB_LIN_A1_BCAST) ? 1 : 0) | ((flags & OPB_LIN_A2_BCAST) ? 2 : 0);
+    p.row_counts = row_counts;
     static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
     const int groups = sm_count() / cg;                                   // persistent CTAs (or CTA pairs), one per SM
@@ -393,4 +408,11 @@ extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void
     else OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, -1>, smem2));
     OPB_CHECK_LAUNCH();
     return OPB_OK;
+}
+
+extern "C" int op_linear_tc(const void *A1h, const void *A1l, int K1, const void *A2h, const void *A2l, int K2, const void *Wh,
+                            const void *Wl, const void *W2h, const void *W2l, const float *bias, float *C, void *Ch, void *Cl, int B, int rows_per_batch, int Cout,
+                            int flags, int elu_cols, float *stats_partial, const float *ksum, float zscale_num, void *stream) {
+    return op_linear_tc_ragged(A1h, A1l, K1, A2h, A2l, K2, Wh, Wl, W2h, W2l, bias, C, Ch, Cl, B, rows_per_batch, Cout, flags, elu_cols, stats_partial, ksum,
+                               zscale_num, nullptr, stream);
 }

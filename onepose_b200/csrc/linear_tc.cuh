@@ -58,6 +58,8 @@ struct Params {
     int w2_ident;                  // pair form: W2 is the 256 x 256 identity (planes (64, 0)); the A2 part is issued as N = 64 MMAs on its diagonal blocks
     int a_bcast;                   // bit 0: A1 is one [1, rows, K1] tensor read by every frame; bit 1: the same for A2
     int w2;                        // 0: W spans K1+K2 columns; 1: the A2 part has its own weight W2 [Cout][K2]; 2: W2 is [B][Cout][K2]
+    const int *row_counts;         // ragged batches (op_linear_tc_ragged): [B] valid rows per frame, rows past a frame's count are padding --
+                                   // left out of every cross-row statistic and written as zeros by the COLSUM producers; null = all rows valid
 };
 
 struct Barriers {
@@ -291,8 +293,9 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 cur_b = b;
             }
             const int row = rt * BM + quad * 32 + lane;
-            const bool row_ok = row < p.rows;
-            const bool rows_full = rt * BM + BM <= p.rows;         // warp-uniform: no row of this tile needs masking out of the column sums
+            const int nrows = p.row_counts ? min(p.rows, __ldg(p.row_counts + b)) : p.rows;   // valid rows of this frame
+            const bool row_ok = row < nrows;
+            const bool rows_full = rt * BM + BM <= nrows;          // warp-uniform: no row of this tile needs masking out of the column sums
             const long long grow = (long long)b * p.rows + (row_ok ? row : 0);
             const int row0 = rt * BM + quad * 32;
             tc::mbar_wait(&bar->acc_full[as], aph);
@@ -427,7 +430,10 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                     }
                 }
                 if (flags & OPB_LIN_ZSCALE) {
-                    const float z = p.zscale_num / (den * (1.f / kScale) + 1e-6f);
+                    // den == 0 only when the source stream of this frame is empty (a ragged batch's frame without valid rows: Ksum = 0; the
+                    // reference early-outs on such a frame, GATs_SuperGlue.py:223): the message is zero either way, and z = M / 1e-6 would
+                    // overflow the fp16 planes of Q''
+                    const float z = den > 0.f ? p.zscale_num / (den * (1.f / kScale) + 1e-6f) : 0.f;
 #pragma unroll
                     for (int i = 0; i < 32; ++i) { v[0][i] *= z; v[1][i] *= z; }
                 }
@@ -460,6 +466,10 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         }
                     }
                     if (flags & OPB_LIN_COLSUM) {                // column sums of the stored value over the valid rows (Ksum :97; means)
+                        if (p.row_counts && !rows_full) {        // ragged batch: padding rows leave as zeros (K' rows that add nothing to G = K'^T X)
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) vv[i] = row_ok ? vv[i] : 0.f;
+                        }
                         float s[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) s[i] = vv[i];

@@ -2,10 +2,10 @@
 // flags=SOLVEPNP_EPNP) as called by ransac_PnP (src/utils/eval_utils.py:18-42).
 //
 //  k_pnp_prepare     : float64 correspondences -> float32 (cv2 converts its inputs to CV_32F first).
-//  k_pnp_hypotheses  : lane-per-hypothesis 5-point EPnP (a warp solves 32 minimal samples at once, every
-//                      lane busy), then the same warp walks its 32 poses and counts inliers cooperatively
-//                      (lanes over correspondences): projection in float64, squared error in float32,
-//                      inlier iff err <= thr^2 -- the arithmetic of PnPRansacCallback::computeError.
+//  k_pnp_solve       : lane-per-hypothesis 5-point EPnP (a warp solves 32 minimal samples at once, every lane busy).
+//  k_pnp_count       : warp-per-hypothesis inlier count (lanes over correspondences): projection in float64,
+//                      squared error in float32, inlier iff err <= thr^2 -- the arithmetic of
+//                      PnPRansacCallback::computeError.
 //  k_pnp_select_refit: replays cv2's sequential rule over the counts (accept iff strictly greater than
 //                      every earlier count and > 4; niters shrinks adaptively; stop at iter == niters),
 //                      recomputes the winner's inlier mask, refits EPnP on all inliers with block-parallel
@@ -63,63 +63,90 @@ __device__ inline void solve_minimal(const float *X32, const float *uv32, const 
     rodrigues_to_vec(R, rvec);
 }
 
+__device__ inline void cv_samples_frame(int f, const int32_t *__restrict__ count, int H, int h_begin, int h_end,
+                                        const int32_t *__restrict__ bound, unsigned long long *__restrict__ rng_state,
+                                        int32_t *__restrict__ samples, int32_t *__restrict__ sample_set);
+
+// The sequential sample stream of the NEXT round rides along as one extra block column (blockIdx.x == gridDim.x - 1 when next_h1 >
+// next_h0): it only depends on the frames' counts, and on its own launch it was 0.07-0.9 ms per round of one thread per frame with
+// the rest of the GPU idle.
+struct NextSamples { int F, h0, h1; unsigned long long *rng; int32_t *samples, *sample_set; };
+
+// Hypothesis round, stage 1: lane-per-hypothesis minimal solve.  Writes (rvec, tvec) to hyp_pose, the rotation matrix cv2's
+// projectPoints re-derives from rvec plus tvec to round_rt [F][round_cap][12] (slot h - h_begin), and marks the hypothesis in
+// hyp_counts: 0 = solved, to be counted by k_pnp_count; -1 = not evaluated (bad sample, n <= 5, or past the adaptive bound).
 __global__ void __launch_bounds__(kHypBlock)
-k_pnp_hypotheses(const float *__restrict__ X32, const float *__restrict__ uv32, const int32_t *__restrict__ count, int stride,
-                 const double *__restrict__ Kmat, const int32_t *__restrict__ samples, const int32_t *__restrict__ sample_set,
-                 int H_total, int h_begin, int h_end, const int32_t *__restrict__ bound, float thr2, int32_t *__restrict__ hyp_counts,
-                 double *__restrict__ hyp_pose) {
+k_pnp_solve(const float *__restrict__ X32, const float *__restrict__ uv32, const int32_t *__restrict__ count, int stride,
+            const double *__restrict__ Kmat, const int32_t *__restrict__ samples, const int32_t *__restrict__ sample_set,
+            int H_total, int h_begin, int h_end, int round_cap, const int32_t *__restrict__ bound, int32_t *__restrict__ hyp_counts,
+            double *__restrict__ hyp_pose, double *__restrict__ round_rt, const NextSamples nx) {
+    if (nx.h1 > nx.h0 && blockIdx.x == gridDim.x - 1) {
+        if (blockIdx.y == 0)
+            for (int g = threadIdx.x; g < nx.F; g += kHypBlock) cv_samples_frame(g, count, H_total, nx.h0, nx.h1, bound, nx.rng, nx.samples, nx.sample_set);
+        return;
+    }
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int h = h_begin + blockIdx.x * kHypBlock + threadIdx.x;
     // adaptive rounds: cv2's sequential loop never looks at iteration >= niters, and niters only shrinks, so a warp whose
     // first hypothesis is already past the bound replayed over the earlier rounds has nothing to contribute
     if (h - lane >= h_end || (bound && h - lane >= bound[f])) return;
     const int H = h_end < H_total ? h_end : H_total;
+    if (h >= H) return;
     const int n = count[f];
-    if (n <= 5) {                       // no RANSAC for n <= 5 (handled in k_pnp_select_refit)
-        if (h < H) hyp_counts[(long long)f * H_total + h] = -1;
-        return;
-    }
+    if (n <= 5) { hyp_counts[(long long)f * H_total + h] = -1; return; }       // no RANSAC for n <= 5 (handled in k_pnp_select_refit)
     const Cam cam = load_cam(Kmat + (long long)f * 9);
     const float *X = X32 + (long long)f * stride * 3, *uv = uv32 + (long long)f * stride * 2;
-    double rvec[3] = {0, 0, 0}, tvec[3] = {0, 0, 0}, R[9];
-    bool ok = false;
-    if (h < H) {
-        const int32_t *s = samples + ((long long)sample_set[f] * H_total + h) * 5;
-        int idx[5];
-        ok = true;
-        for (int i = 0; i < 5; ++i) { idx[i] = s[i]; ok = ok && idx[i] >= 0 && idx[i] < n; }
-        if (ok) {
-            solve_minimal(X, uv, idx, cam, rvec, tvec);
-            double *dst = hyp_pose + ((long long)f * H_total + h) * 6;
-            dst[0] = rvec[0]; dst[1] = rvec[1]; dst[2] = rvec[2]; dst[3] = tvec[0]; dst[4] = tvec[1]; dst[5] = tvec[2];
-        }
-    }
+    const int32_t *s = samples + ((long long)sample_set[f] * H_total + h) * 5;
+    int idx[5];
+    bool ok = true;
+    for (int i = 0; i < 5; ++i) { idx[i] = s[i]; ok = ok && idx[i] >= 0 && idx[i] < n; }
+    if (!ok) { hyp_counts[(long long)f * H_total + h] = -1; return; }
+    double rvec[3], tvec[3], R[9];
+    solve_minimal(X, uv, idx, cam, rvec, tvec);
+    double *dst = hyp_pose + ((long long)f * H_total + h) * 6;
+    dst[0] = rvec[0]; dst[1] = rvec[1]; dst[2] = rvec[2]; dst[3] = tvec[0]; dst[4] = tvec[1]; dst[5] = tvec[2];
     rodrigues_to_mat(rvec, R);          // cv2 re-derives R from rvec inside projectPoints
-    int my_count = -1;
-    for (int hh = 0; hh < 32; ++hh) {
-        const bool okh = __shfl_sync(0xffffffffu, (int)ok, hh) != 0;
-        if (!okh) continue;             // warp-uniform
-        double Rb[9], tb[3];
+    double *rt = round_rt + ((long long)f * round_cap + (h - h_begin)) * 12;
 #pragma unroll
-        for (int k = 0; k < 9; ++k) Rb[k] = __shfl_sync(0xffffffffu, R[k], hh);
+    for (int k = 0; k < 9; ++k) rt[k] = R[k];
+    rt[9] = tvec[0]; rt[10] = tvec[1]; rt[11] = tvec[2];
+    hyp_counts[(long long)f * H_total + h] = 0;
+}
+
+// Hypothesis round, stage 2: inlier count, one WARP per hypothesis (lanes over the frame's correspondences) -- frames x hypotheses
+// warps fill the machine where the former one-warp-walks-its-32-poses form left 148 SMs to a few warps per frame (BASELINE.json
+// configs[3]: 10k correspondences).  Projection in float64, squared error in float32, inlier iff err <= thr^2: the arithmetic of
+// PnPRansacCallback::computeError; the count is an integer sum, so the split over lanes does not change it.
+constexpr int kCountWarps = 8;
+__global__ void __launch_bounds__(kCountWarps * 32)
+k_pnp_count(const float *__restrict__ X32, const float *__restrict__ uv32, const int32_t *__restrict__ count, int stride,
+            const double *__restrict__ Kmat, int H_total, int h_begin, int h_end, int round_cap, const int32_t *__restrict__ bound,
+            float thr2, const double *__restrict__ round_rt, int32_t *__restrict__ hyp_counts) {
+    const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int h = h_begin + blockIdx.x * kCountWarps + warp;
+    const int H = h_end < H_total ? h_end : H_total;
+    if (h >= H || (bound && (h & ~31) >= bound[f])) return;                 // the bound test of the solving warp (32 consecutive hypotheses)
+    if (hyp_counts[(long long)f * H_total + h] < 0) return;                  // not solved
+    const int n = count[f];
+    const Cam cam = load_cam(Kmat + (long long)f * 9);
+    const float *X = X32 + (long long)f * stride * 3, *uv = uv32 + (long long)f * stride * 2;
+    const double *rt = round_rt + ((long long)f * round_cap + (h - h_begin)) * 12;
+    double R[9], t[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) tb[k] = __shfl_sync(0xffffffffu, tvec[k], hh);
-        int c = 0;
-        for (int i = lane; i < n; i += 32) c += reproj_err(X + 3 * i, uv + 2 * i, Rb, tb, cam) <= thr2 ? 1 : 0;
+    for (int k = 0; k < 9; ++k) R[k] = rt[k];
+    t[0] = rt[9]; t[1] = rt[10]; t[2] = rt[11];
+    int c = 0;
+    for (int i = lane; i < n; i += 32) c += reproj_err(X + 3 * i, uv + 2 * i, R, t, cam) <= thr2 ? 1 : 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-        if (lane == hh) my_count = c;
-    }
-    if (h < H) hyp_counts[(long long)f * H_total + h] = my_count;
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) hyp_counts[(long long)f * H_total + h] = c;
 }
 
 // cv::RNG((uint64)-1) multiply-with-carry stream, one sequential generator per frame.  Samples [h_begin, h_end) are
 // drawn; the generator state is carried in rng_state between rounds (rng_state == nullptr: one shot from the seed).
-__global__ void k_pnp_cv_samples(const int32_t *__restrict__ count, int F, int H, int h_begin, int h_end,
-                                 const int32_t *__restrict__ bound, unsigned long long *__restrict__ rng_state,
-                                 int32_t *__restrict__ samples, int32_t *__restrict__ sample_set) {
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= F) return;
+__device__ inline void cv_samples_frame(int f, const int32_t *__restrict__ count, int H, int h_begin, int h_end,
+                                        const int32_t *__restrict__ bound, unsigned long long *__restrict__ rng_state,
+                                        int32_t *__restrict__ samples, int32_t *__restrict__ sample_set) {
     if (h_begin == 0) sample_set[f] = f;
     if (bound && h_begin >= bound[f]) return;
     const unsigned n = (unsigned)count[f];
@@ -144,6 +171,13 @@ __global__ void k_pnp_cv_samples(const int32_t *__restrict__ count, int F, int H
     if (rng_state) rng_state[f] = state;
 }
 
+__global__ void k_pnp_cv_samples(const int32_t *__restrict__ count, int F, int H, int h_begin, int h_end,
+                                 const int32_t *__restrict__ bound, unsigned long long *__restrict__ rng_state,
+                                 int32_t *__restrict__ samples, int32_t *__restrict__ sample_set) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < F) cv_samples_frame(f, count, H, h_begin, h_end, bound, rng_state, samples, sample_set);
+}
+
 __device__ inline int update_num_iters(double p, double ep, int model_points, int max_iters) {
     p = p < 0 ? 0 : p > 1 ? 1 : p;
     ep = ep < 0 ? 0 : ep > 1 ? 1 : ep;
@@ -154,27 +188,46 @@ __device__ inline int update_num_iters(double p, double ep, int model_points, in
     return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)llrint(num / denom);
 }
 
-// Replays cv2's accept rule over the counts of round [h_begin, h_end) and tightens the per-frame iteration bound
-// (state = {niters, best_count}).  One thread per frame: the rule is a dependent scan.
-__global__ void k_pnp_bound_update(const int32_t *__restrict__ count, int F, int H, int h_begin, int h_end,
-                                   const int32_t *__restrict__ hyp_counts, double confidence, int max_iters,
-                                   int32_t *__restrict__ bound, int32_t *__restrict__ state) {
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= F) return;
-    int niters = h_begin == 0 ? max_iters : state[2 * f], best = h_begin == 0 ? 0 : state[2 * f + 1];
-    const int n = count[f];
-    if (n > 5) {
-        const int32_t *cnt = hyp_counts + (long long)f * H;
-        for (int it = h_begin; it < h_end && it < niters; ++it) {
-            const int good = cnt[it];
-            const int floor_ = best > 4 ? best : 4;
-            if (good > floor_) { best = good; niters = update_num_iters(confidence, (double)(n - good) / n, 5, niters); }
+// cv2's sequential accept rule over the counts of iterations [it_begin, it_end), run by one warp (all 32 lanes call with the same
+// arguments and leave with the same results).  The rule -- accept iff count > max(best so far, 4); niters shrinks on every accept;
+// the loop ends at it == niters -- only changes state at RECORD positions (count above everything before it), so the warp reads the
+// counts 32 at a time, finds the records with a prefix maximum and walks only those in order; a one-thread scan of the list was a
+// chain of dependent global loads (0.25 ms for 3072 iterations).  Unevaluated entries (-1) are never records.
+__device__ inline void replay_accept(const int32_t *__restrict__ cnt, int it_begin, int it_end, int n, double confidence,
+                                     int &niters, int &best, int &best_pos) {
+    const int lane = threadIdx.x & 31;
+    for (int it0 = it_begin; it0 < it_end && it0 < niters; it0 += 32) {
+        const int it = it0 + lane;
+        const int good = (it < it_end) ? cnt[it] : -1;
+        int pm = good;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, pm, o); if (lane >= o) pm = pm > t ? pm : t; }
+        int excl = __shfl_up_sync(0xffffffffu, pm, 1);
+        if (lane == 0) excl = -1;
+        const int floor_ = best > 4 ? best : 4;
+        unsigned rec = __ballot_sync(0xffffffffu, good > (excl > floor_ ? excl : floor_));
+        while (rec) {
+            const int l = __ffs(rec) - 1;
+            rec &= rec - 1;
+            const int pos = it0 + l;
+            if (pos >= niters) { rec = 0; break; }                     // the sequential loop ended before this iteration
+            best = __shfl_sync(0xffffffffu, good, l); best_pos = pos;
+            niters = update_num_iters(confidence, (double)(n - best) / n, 5, niters);
         }
-    } else {
-        niters = 0;
     }
-    state[2 * f] = niters; state[2 * f + 1] = best;
-    bound[f] = niters;
+}
+
+// Tightens the per-frame iteration bound after round [h_begin, h_end) (state = {niters, best_count}).  One warp per frame.
+__global__ void __launch_bounds__(32)
+k_pnp_bound_update(const int32_t *__restrict__ count, int F, int H, int h_begin, int h_end,
+                   const int32_t *__restrict__ hyp_counts, double confidence, int max_iters,
+                   int32_t *__restrict__ bound, int32_t *__restrict__ state) {
+    const int f = blockIdx.x;
+    int niters = h_begin == 0 ? max_iters : state[2 * f], best = h_begin == 0 ? 0 : state[2 * f + 1], pos = -1;
+    const int n = count[f];
+    if (n > 5) replay_accept(hyp_counts + (long long)f * H, h_begin, h_end, n, confidence, niters, best, pos);
+    else niters = 0;
+    if (threadIdx.x == 0) { state[2 * f] = niters; state[2 * f + 1] = best; bound[f] = niters; }
 }
 
 // ordered block reduction of K doubles per thread; result broadcast to all threads through `out`

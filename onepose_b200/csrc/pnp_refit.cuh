@@ -62,28 +62,27 @@ k_pnp_select_refit(const float *__restrict__ X32, const float *__restrict__ uv32
     }
 
     // ---- 1. winner ---------------------------------------------------------------------------
-    if (tid == 0) {
-        S.best_hyp = -1; S.iters = 0; S.have_best = 0;
+    if (warp == 0) {
         if (n == 5) {
-            // cv2 skips RANSAC when npoints == model_points: direct solve, every point is an inlier
-            int idx[5] = {0, 1, 2, 3, 4};
-            double rv[3], tv[3];
-            solve_minimal(X, uv, idx, cam, rv, tv);
-            for (int k = 0; k < 3; ++k) { S.hyp_rt[k] = rv[k]; S.hyp_rt[3 + k] = tv[k]; }
-        } else {
-            const int32_t *cnt = hyp_counts + (long long)f * H;
-            int niters = max_iters, best_count = 0, it;
-            for (it = 0; it < niters && it < H; ++it) {
-                const int good = cnt[it];
-                if (good < 0) continue;
-                const int floor_ = best_count > 4 ? best_count : 4;
-                if (good > floor_) {
-                    S.best_hyp = it; best_count = good;
-                    niters = update_num_iters(confidence, (double)(n - good) / n, 5, niters);
-                }
+            if (tid == 0) {
+                // cv2 skips RANSAC when npoints == model_points: direct solve, every point is an inlier
+                int idx[5] = {0, 1, 2, 3, 4};
+                double rv[3], tv[3];
+                solve_minimal(X, uv, idx, cam, rv, tv);
+                for (int k = 0; k < 3; ++k) { S.hyp_rt[k] = rv[k]; S.hyp_rt[3 + k] = tv[k]; }
+                S.best_hyp = -1; S.iters = 0; S.have_best = 0;
             }
-            S.iters = it;
-            if (S.best_hyp >= 0) for (int k = 0; k < 6; ++k) S.hyp_rt[k] = hyp_pose[((long long)f * H + S.best_hyp) * 6 + k];
+        } else {
+            // the sequential loop `for (it = 0; it < niters && it < H; ++it)` of cv2 replayed by warp 0 (replay_accept); it leaves
+            // the loop at max(niters, last accepted + 1), capped by H
+            int niters = max_iters, best_count = 0, best_pos = -1;
+            replay_accept(hyp_counts + (long long)f * H, 0, H, n, confidence, niters, best_count, best_pos);
+            if (tid == 0) {
+                int it = niters > best_pos + 1 ? niters : best_pos + 1;
+                S.iters = it < H ? it : H;
+                S.best_hyp = best_pos; S.have_best = 0;
+                if (best_pos >= 0) for (int k = 0; k < 6; ++k) S.hyp_rt[k] = hyp_pose[((long long)f * H + best_pos) * 6 + k];
+            }
         }
     }
     __syncthreads();
@@ -242,7 +241,8 @@ k_pnp_select_refit(const float *__restrict__ X32, const float *__restrict__ uv32
     }
 }
 
-struct PnpWorkspace { float *X32, *uv32; double *alphas; int32_t *inl, *bound, *state, *samples, *sample_set; unsigned long long *rng; size_t bytes; };
+constexpr int kRoundCap = 4096;          // hypotheses per adaptive round at most (sizes round_rt)
+struct PnpWorkspace { float *X32, *uv32; double *alphas, *round_rt; int32_t *inl, *bound, *state, *samples, *sample_set; unsigned long long *rng; size_t bytes; };
 static PnpWorkspace carve_pnp(void *base, int F, int stride, int H) {
     PnpWorkspace w; size_t off = 0;
     auto take = [&](size_t bytes) { void *p = base ? (char *)base + off : nullptr; off += align_up(bytes, 256); return p; };
@@ -255,6 +255,7 @@ static PnpWorkspace carve_pnp(void *base, int F, int stride, int H) {
     w.rng = (unsigned long long *)take((size_t)F * sizeof(unsigned long long));
     w.sample_set = (int32_t *)take((size_t)F * sizeof(int32_t));
     w.samples = (int32_t *)take((size_t)F * H * 5 * sizeof(int32_t));     // cv2's stream when the caller supplies no samples
+    w.round_rt = (double *)take((size_t)F * (H < kRoundCap ? H : kRoundCap) * 12 * sizeof(double));   // [R | t] of one round's hypotheses
     w.bytes = off;
     return w;
 }
@@ -297,20 +298,28 @@ extern "C" int op_pnp_ransac(const double *pts2d, const double *pts3d, const int
     const bool own_stream = samples == nullptr;
     if (own_stream) { samples = w.samples; sample_set = w.sample_set; }
     static const int kRoundEnd[] = {32, 256, 1024, 4096};
+    auto round_end = [&](int r, int h0) { int h1 = r < 4 ? kRoundEnd[r] : h0 + 4096; return h1 > H ? H : h1; };
+    const int cap = H < kRoundCap ? H : kRoundCap;
     int h0 = 0;
     for (int r = 0; h0 < H; ++r) {
-        int h1 = r < 4 ? kRoundEnd[r] : h0 + 4096;
-        if (h1 > H) h1 = H;
+        const int h1 = round_end(r, h0);
         const int32_t *bnd = r == 0 ? nullptr : w.bound;
+        NextSamples nx{};
         if (own_stream) {
-            k_pnp_cv_samples<<<ceil_div(F, 32), 32, 0, st>>>(count, F, H, h0, h1, bnd, w.rng, w.samples, w.sample_set);
-            OPB_CHECK_LAUNCH();
+            if (r == 0) {
+                k_pnp_cv_samples<<<ceil_div(F, 32), 32, 0, st>>>(count, F, H, h0, h1, bnd, w.rng, w.samples, w.sample_set);
+                OPB_CHECK_LAUNCH();
+            }
+            // the next round's samples are drawn by one extra block column of this round's solve
+            if (h1 < H) nx = NextSamples{F, h1, round_end(r + 1, h1), w.rng, w.samples, w.sample_set};
         }
-        k_pnp_hypotheses<<<dim3(ceil_div(h1 - h0, kHypBlock), F), kHypBlock, 0, st>>>(w.X32, w.uv32, count, stride, K, samples, sample_set, H,
-                                                                                    h0, h1, bnd, thr2, hyp_counts, hyp_pose);
+        k_pnp_solve<<<dim3(ceil_div(h1 - h0, kHypBlock) + (nx.h1 > nx.h0 ? 1 : 0), F), kHypBlock, 0, st>>>(
+            w.X32, w.uv32, count, stride, K, samples, sample_set, H, h0, h1, cap, bnd, hyp_counts, hyp_pose, w.round_rt, nx);
+        k_pnp_count<<<dim3(ceil_div(h1 - h0, kCountWarps), F), kCountWarps * 32, 0, st>>>(w.X32, w.uv32, count, stride, K, H, h0, h1, cap, bnd,
+                                                                                         thr2, w.round_rt, hyp_counts);
         OPB_CHECK_LAUNCH();
         if (h1 < H) {
-            k_pnp_bound_update<<<ceil_div(F, 64), 64, 0, st>>>(count, F, H, h0, h1, hyp_counts, confidence, max_iters, w.bound, w.state);
+            k_pnp_bound_update<<<F, 32, 0, st>>>(count, F, H, h0, h1, hyp_counts, confidence, max_iters, w.bound, w.state);
             OPB_CHECK_LAUNCH();
         }
         h0 = h1;

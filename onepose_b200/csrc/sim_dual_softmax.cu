@@ -185,13 +185,19 @@ __global__ void k_sim_finalize_sums(const float *__restrict__ part, int tiles, i
     if (i >= n) return;
     float s = 0.f;
     for (int t = 0; t < tiles; ++t) s += part[((long long)b * tiles + t) * n + i];
-    inv[(long long)b * n + i] = as_log2 ? -log2f(s) : 1.f / s;
+    // as_log2: a sum of zero (a frame of a ragged batch without valid rows) gives the neutral term, conf stays +0 instead of inf - inf
+    inv[(long long)b * n + i] = as_log2 ? (s > 0.f ? -log2f(s) : 0.f) : 1.f / s;
 }
 
 __global__ void k_sim_finalize_max(const unsigned long long *__restrict__ part, int tiles, int n, int n_other,
-                                   int *__restrict__ idx, float *__restrict__ val, const float *__restrict__ conf_rows) {
+                                   int *__restrict__ idx, float *__restrict__ val, const float *__restrict__ conf_rows,
+                                   const int *__restrict__ n_counts = nullptr) {
     const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (n_counts && i >= n_counts[b]) {             // padding row of a ragged batch: its partials were never written
+        idx[(long long)b * n + i] = 0; val[(long long)b * n + i] = 0.f;
+        return;
+    }
     unsigned long long k = 0ull;
     for (int t = 0; t < tiles; ++t) { const unsigned long long v = part[((long long)b * tiles + t) * n + i]; k = v > k ? v : k; }
     // an all-zero row / column of conf can select a padding slot of the last tile: every index is then a maximum, clamp it
@@ -214,20 +220,21 @@ __global__ void k_sim_finalize_max(const unsigned long long *__restrict__ part, 
 // The score of a pair is read back from conf itself (exact), the packed keys only select.
 __global__ void k_mutual_select(const int *__restrict__ idx0, const float *__restrict__ conf, const int *__restrict__ idx1,
                                 int N2, int N3, float thr, int64_t *__restrict__ matches0, int64_t *__restrict__ matches1,
-                                float *__restrict__ scores0, float *__restrict__ scores1) {
+                                float *__restrict__ scores0, float *__restrict__ scores1, const int *__restrict__ n2_counts = nullptr) {
     const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
     const int *i0 = idx0 + (long long)b * N2, *i1 = idx1 + (long long)b * N3;
     const float *cb = conf + (long long)b * N2 * N3;
+    const int n2 = n2_counts ? min(N2, n2_counts[b]) : N2;      // ragged batch: rows past the count are padding and never match
     if (i < N2) {
         const int j = i0[i];
-        const bool mutual = i1[j] == i;
+        const bool mutual = i < n2 && i1[j] == i;
         const float ms = mutual ? cb[(long long)i * N3 + j] : 0.f;
         scores0[(long long)b * N2 + i] = ms;
         matches0[(long long)b * N2 + i] = (mutual && ms > thr) ? (int64_t)j : (int64_t)-1;
     }
     if (i < N3) {
         const int n = i1[i];                       // best query for this 3D point
-        const bool mutual1 = i0[n] == i;
+        const bool mutual1 = n < n2 && i0[n] == i;
         const bool mutual0_n = i1[i0[n]] == n;
         const float ms0_n = mutual0_n ? cb[(long long)n * N3 + i0[n]] : 0.f;
         scores1[(long long)b * N3 + i] = mutual1 ? ms0_n : 0.f;
@@ -284,7 +291,7 @@ extern "C" size_t op_sim_dual_softmax_workspace_bytes(int B, int N2, int N3) {
 static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const float *m3, int B, int N2, int N3, float scale_factor,
                     float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
                     float *scores0, float *scores1, void *workspace, size_t workspace_bytes,
-                    void *stream, const void *const *planes = nullptr) {
+                    void *stream, const void *const *planes = nullptr, const int *n2_counts = nullptr) {
     using namespace opb;
     OPB_CHECK_ARG((planes || (m2 && m3)) && conf && matches0 && matches1 && scores0 && scores1 && workspace, "op_sim_dual_softmax: null pointer");
     OPB_CHECK_ARG(B > 0 && N2 > 0 && N3 > 0 && B <= 65535, "op_sim_dual_softmax: bad shape B=%d N2=%d N3=%d", B, N2, N3);
@@ -366,6 +373,7 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
             { const char *e = getenv("OPB_SIM_DBG"); q.dbg = e ? atoi(e) : 0; }
             q.rowsum_part = w.rowsum_part; q.colsum_part = w.colsum4; q.lgR = w.invR; q.lgC = w.invC;
             q.rowmax_part = w.rowmax_part; q.colkey_part = w.colkey4; q.conf = conf;
+            q.n2_counts = n2_counts;
             static bool configured16 = false;
             if (!configured16) {
                 OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<1>()));
@@ -397,14 +405,15 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
             if (f8 && wide) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q));
             else if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
             else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
-            k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, splits * 4, N2, N3, w.idx0, w.val0, conf);
+            k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, splits * 4, N2, N3, w.idx0, w.val0, conf, n2_counts);
             simtc16::k_sim_finalize_colkeys<<<dim3(ceil_div(N3, 256), B), 256, 0, st>>>(w.colkey4, p.tiles_m * 4, N3, N2, w.idx1, w.val1);
             OPB_CHECK_LAUNCH();
             const int nmax16 = N2 > N3 ? N2 : N3;
-            k_mutual_select<<<dim3(ceil_div(nmax16, 256), B), 256, 0, st>>>(w.idx0, conf, w.idx1, N2, N3, match_threshold, matches0, matches1, scores0, scores1);
+            k_mutual_select<<<dim3(ceil_div(nmax16, 256), B), 256, 0, st>>>(w.idx0, conf, w.idx1, N2, N3, match_threshold, matches0, matches1, scores0, scores1, n2_counts);
             OPB_CHECK_LAUNCH();
             return OPB_OK;
         }
+        if (n2_counts) { set_error("op_sim_dual_softmax_planes_ragged: per-frame row counts exist in the sixteen-warp pair form only (unset OPB_SIM_CG / OPB_SIM_EW)"); return OPB_ERR_ARG; }
         const int tiles_n = ceil_div(N3, 128 * cg);          // column tiles of the tensor-core passes: 128 wide, 256 for a CTA pair
         // enough CTAs for ~2 waves over 148 SMs: split the column tiles when frames x row tiles is small
         int splits = ceil_div(2 * 148, (long long)B * p.tiles_m);
@@ -482,12 +491,19 @@ extern "C" int op_sim_dual_softmax_rows(const float *x2, const float *x3, int B,
                     workspace, workspace_bytes, stream);
 }
 
-extern "C" int op_sim_dual_softmax_planes(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
-                                          float scale_factor, float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
-                                          float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
+extern "C" int op_sim_dual_softmax_planes_ragged(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
+                                                 const int *n2_counts, float scale_factor, float match_threshold, float *conf, int64_t *matches0,
+                                                 int64_t *matches1, float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
     OPB_CHECK_ARG(m2_hi && m2_bytes && m3_hi && m3_bytes, "op_sim_dual_softmax_planes: null plane");
     OPB_CHECK_ARG((((uintptr_t)m2_hi | (uintptr_t)m2_bytes | (uintptr_t)m3_hi | (uintptr_t)m3_bytes) & 15) == 0, "op_sim_dual_softmax_planes: planes must be 16-byte aligned");
     const void *planes[4] = {m2_hi, m2_bytes, m3_hi, m3_bytes};
     return sim_impl(true, false, nullptr, nullptr, B, N2, N3, scale_factor, match_threshold, conf, matches0, matches1, scores0, scores1,
-                    workspace, workspace_bytes, stream, planes);
+                    workspace, workspace_bytes, stream, planes, n2_counts);
+}
+
+extern "C" int op_sim_dual_softmax_planes(const void *m2_hi, const void *m2_bytes, const void *m3_hi, const void *m3_bytes, int B, int N2, int N3,
+                                          float scale_factor, float match_threshold, float *conf, int64_t *matches0, int64_t *matches1,
+                                          float *scores0, float *scores1, void *workspace, size_t workspace_bytes, void *stream) {
+    return op_sim_dual_softmax_planes_ragged(m2_hi, m2_bytes, m3_hi, m3_bytes, B, N2, N3, nullptr, scale_factor, match_threshold, conf, matches0, matches1,
+                                             scores0, scores1, workspace, workspace_bytes, stream);
 }

@@ -23,13 +23,12 @@ constexpr int TILE_BYTES = 128 * 128;                 // 128 rows x 64 fp16
 constexpr int A_BYTES = 2 * NKB * TILE_BYTES;         // 131072
 constexpr int RING_BYTES = 4 * TILE_BYTES;            // 65536
 constexpr int MAX_UNITS = 4;
-// CG = 1: one CTA per 128 query rows; a ring unit is a whole 128-column k-block of B (16 KB, 4 units).
-// CG = 2: a CTA pair (cta_group::2) per 256 query rows: each CTA keeps its own 128 rows of A resident and stages HALF of every
-//         B k-block (64 columns, 8 KB, 8 units), the leader issues M256 N128 MMAs.  Every row tile re-streams all of the frame's
-//         3D descriptors from L2, and that L2 -> SM stream (17 GB per 64 frames and two passes, against ~12 TB/s chip-wide) is
-//         what bounds the kernel: with MMAs, conf arithmetic and stores switched off (OPB_SIM_DBG = 25) 0.86 + 0.81 of the
-//         1.26 + 1.87 ms remain (37 B/clk/SM of ring traffic).  The pair halves the bytes per CTA but, with 8 KB units, not the
-//         time (the ring is round-trip bound), so CG = 1 stays the default.
+// CG = 1: one CTA per 128 query rows, M128 x N128 MMAs on 128-column tiles (OPB_SIM_CG=1, A/B runs only).
+// CG = 2 (default since r01zb): a CTA pair (cta_group::2) per 256 query rows on 256-column tiles.  Each CTA keeps its own 128 rows
+//         of A resident and stages HALF of every B k-block in 16 KB ring units (128 columns x 128 bytes of one plane); the leader
+//         issues M256 x N256 MMAs, which halves the L2 -> SM operand stream per flop that bounds the one-CTA form.
+// The production kernels are the sixteen-epilogue-warp pair kernels of sim_tc16.cuh (k_sim16); the eight-warp kernels in this file
+// remain as the A/B forms (OPB_SIM_EW=8, OPB_SIM_CG=1, OPB_SIM_MMA=f16) and as the source of the shared constants / helpers.
 template <int CG>
 struct SimCfg {
     static constexpr int BN = 128 * CG;               // columns of a tile: 128 (one CTA) / 256 (pair, M256 x N256 like the projections)

@@ -42,6 +42,8 @@ struct Params {
     uint32_t *colkey_part;                            // [B][tiles_m * 4][N3]: conf bits, low 7 bits = 127 - row inside the CTA's 128 rows
     float *conf;
     int tma_store;
+    const int *n2_counts;                             // ragged batches: [B] valid query rows per frame (rows past the count are padding: conf rows of
+                                                      // zeros, no part in the column sums / column maxima); null = N2 rows everywhere
     int dbg;                                          // OPB_SIM_DBG (timing experiments): 1 = no conf stores, 4 = stores into one L2-resident patch, 8 = no MMAs
 };
 
@@ -170,8 +172,9 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
         // ================= epilogue (warps 0-15): TMEM lane quadrant = warp % 4 (thread = query row), column quarter = warp / 4 =========
         const int quad = warp & 3, qtr = warp >> 2;
         const int row = m0 + quad * 32 + lane;
-        const bool row_ok = row < p.N2;
-        const bool rows_full = m0 + BM <= p.N2;                           // warp-uniform
+        const int n2 = p.n2_counts ? min(p.N2, __ldg(p.n2_counts + b)) : p.N2;       // valid query rows of this frame
+        const bool row_ok = row < n2, row_in = row < p.N2;
+        const bool rows_full = m0 + BM <= n2;                             // warp-uniform
         const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(qtr * QCOLS);
         const long long part_row = ((long long)b * p.tiles_m + row_tile) * 4 + quad;     // this warp's row of the per-(row tile, quadrant) partials
         const uint32_t acc_empty0 = tc::mapa(tc::smem_u32(&bar->acc_empty[0]), 0), acc_empty1 = tc::mapa(tc::smem_u32(&bar->acc_empty[1]), 0);
@@ -213,7 +216,7 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
         } else {
             // conf = exp2(2 c1 acc - 2 c0 + log2(1/R_n) + log2(1/C_m)); rows / columns past the end carry -inf => conf = +0
             const float rowc = row_ok ? p.lgR[(long long)b * p.N2 + row] - 2.f * p.c0 : -INFINITY;
-            float *crow = p.conf + ((long long)b * p.N2 + (row_ok ? row : 0)) * p.N3;
+            float *crow = p.conf + ((long long)b * p.N2 + (row_in ? row : 0)) * p.N3;
             const bool vec_ok = (p.N3 & 3) == 0;
             // row selection: running maximum of the raw conf bits (conf >= +0: unsigned order = float order) and the first column of the
             // 16-column block that holds it (strictly greater: the earliest block wins ties); k_sim_finalize_max finds the exact column
@@ -325,7 +328,7 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
                         if (lane < 16 && tile_ok && kcol < p.N3) p.colkey_part[part_row * p.N3 + kcol] = ck;
                     }
                     }
-                    if (!p.tma_store && row_ok) {
+                    if (!p.tma_store && row_in) {
                         if (vec_ok && col0 + 31 < p.N3) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q)
@@ -337,7 +340,7 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
                 }
             }
             if (lane == 0) tc::tma_store_wait_all();
-            if (row_ok)      // (value bits, inverted first column of the winning 16-column block)
+            if (row_in)      // (value bits, inverted first column of the winning 16-column block); padding rows of a ragged batch: (0, column 0)
                 p.rowmax_part[((long long)b * (gridDim.y * 4) + split * 4 + qtr) * p.N2 + row] =
                     ((unsigned long long)row_best << 32) | (unsigned long long)(0xffffffffu - row_blk);
         }

@@ -333,18 +333,22 @@ class GATsSuperGlue(nn.Module):
 
     # ------------------------------------------------------------------ tcgen05 launchers (linear_tc.cuh)
     def _linear_tc(self, A1, W, bias, B, rows, *, A2=None, W2=None, C=None, Cp=None, flags=0, elu_cols=0, stats=None, ksum=None, zscale_num=1.0, tag="",
-                   work_k=None):
+                   work_k=None, counts=None):
         """A1/A2/W/W2/Cp are (hi, lo) plane pairs; C an fp32 tensor; at least one of C / Cp.  work_k: the K of the reference's
         own projection when the GEMM carries extra columns (the identity block of the in-GEMM residual add)."""
         K1 = A1[0].shape[-1]
         K2 = 0 if A2 is None else A2[0].shape[-1]
         Cout = W[0].shape[-2]
         timeline.work = 2.0 * B * rows * (work_k or (K1 + K2)) * Cout
-        call("op_linear_tc", ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
-             ptr(W[0]), ptr(W[1]), ptr(W2[0]) if W2 else None, ptr(W2[1]) if W2 else None, ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
-             B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num), stream_ptr(), tag=tag)
+        head = (ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
+                ptr(W[0]), ptr(W[1]), ptr(W2[0]) if W2 else None, ptr(W2[1]) if W2 else None, ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
+                B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num))
+        if counts is None:
+            call("op_linear_tc", *head, stream_ptr(), tag=tag)
+        else:
+            call("op_linear_tc_ragged", *head, ptr(counts), stream_ptr(), tag=tag)
 
-    def _kv_tc(self, src_p, B, M, lw, tag):
+    def _kv_tc(self, src_p, B, M, lw, tag, counts=None):
         """Source side of linear attention (:90-97) re-associated for the tensor cores (atb_tc.cu): K' projection with
         column sums, G = K'^T X, then per frame Ksum and P'_b = W0b Wm blockdiag(KV')^T [512,256] (merge and the message half
         of MLP layer 0 in one matrix).  Returns (ksum, P'_b planes)."""
@@ -352,7 +356,9 @@ class GATsSuperGlue(nn.Module):
         kp = self._planes("kp" + tag, (B, M, _D), dev)
         parts = lib.op_linear_tc_stat_parts(M)
         ks_part = self._ws.get("kspart" + tag, (B, parts, _D, 2), torch.float32, dev)
-        self._linear_tc(src_p, lw["Wk_p"], lw["bk"], B, M, Cp=kp, flags=1 | 16, elu_cols=_D, stats=ks_part, tag="k")   # ELU1 | COLSUM
+        # counts (ragged batch): K' rows past a frame's count are written as zeros and left out of Ksum, so they add nothing to G either;
+        # the 1/M of :93 and the M of :98 cancel, both stay the padded M
+        self._linear_tc(src_p, lw["Wk_p"], lw["bk"], B, M, Cp=kp, flags=1 | 16, elu_cols=_D, stats=ks_part, tag="k", counts=counts)   # ELU1 | COLSUM
         nch = lib.op_atb_chunks(M)
         part = self._ws.get("gpart" + tag, (B, nch, _D, _D), torch.float32, dev)
         timeline.work = 2.0 * B * M * _D * _D
@@ -375,6 +381,7 @@ class GATsSuperGlue(nn.Module):
         layer): the GEMMs read it as a broadcast operand (OPB_LIN_A1_BCAST / A2_BCAST) and write the per-frame result to st.p, so
         the B-fold copy of the prefix is never made."""
         B, N, ch, x_p = st.B, st.N, st.ch, (x_in if x_in is not None else st.p)
+        cnt = st.counts                  # ragged batch: valid rows per frame of THIS stream (None: all N)
         b1, b2 = (2048, 4096) if x_in is not None else (0, 0)
         dev = x_p[0].device
         parts = lib.op_linear_tc_stat_parts(N)
@@ -386,25 +393,33 @@ class GATsSuperGlue(nn.Module):
         q_p = self._planes("q" + ch, (B, N, _D), dev)
         qs = self._ws.get("qpart" + ch, (B, parts, _D, 2), torch.float32, dev)
         self._linear_tc(x_p, lw["Wq_p"], lw["bq"], B, N, Cp=q_p, flags=1 | 16 | 32 | b1, elu_cols=_D, stats=qs, ksum=ksum, zscale_num=M,
-                        tag="q")                                                                                  # ELU1 | COLSUM | ZSCALE
+                        tag="q", counts=cnt)                                                                      # ELU1 | COLSUM | ZSCALE
         cb = self._ws.get("cbias" + ch, (B, 2 * _D), torch.float32, dev)
-        call("op_mlp_center_bias", ptr(st.xs), st.parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cb),
-             stream_ptr())
+        if cnt is None:
+            call("op_mlp_center_bias", ptr(st.xs), st.parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cb),
+                 stream_ptr())
+        else:
+            call("op_mlp_center_bias_ragged", ptr(st.xs), st.parts, ptr(qs), parts, ptr(lw["W0aT"]), ptr(P[0]), ptr(P[1]), int(pflag != 0), B, N, ptr(cnt),
+                 ptr(cb), stream_ptr())
         hn_p = self._planes("hn" + ch, (B, N, 2 * _D), dev)
         stats = self._ws.get("tcstats" + ch, (B, parts, 2 * _D, 2), torch.float32, dev)
-        self._linear_tc(x_p, lw["W0a_p"], cb, B, N, A2=q_p, W2=P, Cp=hn_p, flags=128 | 256 | pflag | b1, stats=stats, tag="mlp0")   # BIASB | CSTATS_RELU
+        self._linear_tc(x_p, lw["W0a_p"], cb, B, N, A2=q_p, W2=P, Cp=hn_p, flags=128 | 256 | pflag | b1, stats=stats, tag="mlp0", counts=cnt)   # BIASB | CSTATS_RELU
         W1s = self._planes("W1s" + ch, (B, _D, 2 * _D), dev)
-        call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
-             stream_ptr())
+        if cnt is None:
+            call("op_instnorm_scale_weight_planes", ptr(stats), B, parts, N, 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
+                 stream_ptr())
+        else:
+            call("op_instnorm_scale_weight_planes_ragged", ptr(stats), B, parts, N, ptr(cnt), 1e-5, ptr(lw["W1"]), _D, 2 * _D, ptr(W1s[0]), ptr(W1s[1]), None,
+                 stream_ptr())
         if st.x is None:
             # residual add (:78,83) inside the GEMM: x_new = [hn | x] [W1 diag(rstd) | I]^T.  The old value streams through the
             # prefetched TMA pipeline as a second operand instead of being fetched by the epilogue (exposed latency); the
             # identity's planes are exact (64, 0), so the tensor core reproduces hi + lo of x to fp32 rounding.  In place: a
             # row tile is read completely (all MMAs retired) before its epilogue stores, and Cout = 256 is one column tile.
             self._linear_tc(hn_p, W1s, lw["b1"], B, N, A2=x_p, W2=self._packed["eye_p"], Cp=st.p, flags=16 | 64 | 1024 | 8192 | b2, stats=st.xs,
-                            tag="mlp1", work_k=2 * _D)                                                                      # COLSUM | WBATCHED | W2_EXACT_HI
+                            tag="mlp1", work_k=2 * _D, counts=cnt)                                                          # COLSUM | WBATCHED | W2_EXACT_HI
         else:   # an fp32 copy is kept (with_linear_transform): residual add onto it in the epilogue
-            self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1")  # RESIDUAL | COLSUM | WBATCHED
+            self._linear_tc(hn_p, W1s, lw["b1"], B, N, C=st.x, Cp=x_p, flags=2 | 16 | 64, stats=st.xs, tag="mlp1", counts=cnt)  # RESIDUAL | COLSUM | WBATCHED
         st.parts = parts
 
     def _new_stream(self, ch, B, N, dev, keep_fp32, name=None):
@@ -418,6 +433,7 @@ class GATsSuperGlue(nn.Module):
         st.xs = self._ws.get("xs" + name, (B, maxparts, _D, 2), torch.float32, dev)
         st.parts = 0
         st.x = self._ws.get("xf" + name, (B, N, _D), torch.float32, dev) if keep_fp32 else None
+        st.counts = None
         return st
 
     def _load_stream(self, st, x):
@@ -502,16 +518,21 @@ class GATsSuperGlue(nn.Module):
         self._linear(x2, pk["Wf"], pk["bf"], m2, B, N2, tag="final")
         self._linear(x3, pk["Wf"], pk["bf"], m3, B, N3, tag="final")
 
-    def _encode_tc(self, x2, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=None):
+    def _encode_tc(self, x2, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=None, count2d=None):
         """Tensor-core path.  The streams live as split-precision planes + per-frame column sums; an fp32 copy is kept
         only when the GATs layers need one (with_linear_transform)."""
         keep = bool(self.hparams["with_linear_transform"])
         s2 = self._new_stream("2", B, N2, dev, keep)
+        s2.counts = count2d
         if x2 is None:
             x = x2_cm
             if x.dtype != torch.float32 or x.stride(2) != 1 or x.stride(1) != N2:
                 x = (x[:1] if x.stride(0) == 0 else x).float().contiguous()
-            call("op_channel_major_to_planes", ptr(x), x.stride(0) if x.shape[0] > 1 else 0, ptr(s2.p[0]), ptr(s2.p[1]), ptr(s2.xs), B, N2, stream_ptr())
+            if count2d is None:
+                call("op_channel_major_to_planes", ptr(x), x.stride(0) if x.shape[0] > 1 else 0, ptr(s2.p[0]), ptr(s2.p[1]), ptr(s2.xs), B, N2, stream_ptr())
+            else:
+                call("op_channel_major_to_planes_ragged", ptr(x), x.stride(0) if x.shape[0] > 1 else 0, ptr(s2.p[0]), ptr(s2.p[1]), ptr(s2.xs), B, N2,
+                     ptr(count2d), stream_ptr())
             s2.parts = lib.op_linear_tc_stat_parts(N2)
         else:
             self._load_stream(s2, x2)
@@ -557,7 +578,7 @@ class GATsSuperGlue(nn.Module):
                     k3 = self._kv_tc(cur3.p, cur3.B, N3, lw, "3")     # desc2d attends to desc3d
                     e3 = main.record_event()
                     with torch.cuda.stream(side):
-                        k2 = self._kv_tc(s2.p, B, N2, lw, "2")        # desc3d attends to desc2d
+                        k2 = self._kv_tc(s2.p, B, N2, lw, "2", counts=count2d)        # desc3d attends to desc2d
                         e2 = side.record_event()
                         side.wait_event(e3)
                         self._propagate_tc(s2, N3, *k3, lw, shared_src=single3)
@@ -573,7 +594,7 @@ class GATsSuperGlue(nn.Module):
                     ev3 = main.record_event()
                 else:
                     with torch.cuda.stream(side):
-                        k2 = self._kv_tc(s2.p, B, N2, lw, "2")
+                        k2 = self._kv_tc(s2.p, B, N2, lw, "2", counts=count2d)
                         self._propagate_tc(s2, N2, *k2, lw)
                     k3 = self._kv_tc(cur3.p, cur3.B, N3, lw, "3")
                     self._propagate_tc(cur3, N3, *k3, lw)
@@ -603,6 +624,11 @@ class GATsSuperGlue(nn.Module):
         ``matching_scores{0,1}_batched``; and, when ``data`` carries ``'query_intrinsic'`` (as in
         eval_utils.py:68) or ``'K'``, the products of the caller's gather + PnP (inference.py:147-155):
         ``mkpts2d``, ``mkpts3d``, ``mconf``, ``pose`` [B,3,4], ``inliers`` -- see ``onepose_b200.pnp``.
+
+        Ragged batches (an extra input key, the reference contract untouched): ``data['count2d']`` [B] int gives the number of valid
+        query keypoints of every frame of a batch padded to a common N2 (``SuperPoint.forward_batched`` pads that way).  Frame b's
+        results then equal the reference run on its first ``count2d[b]`` keypoints alone (inference.py:140-146 runs B = 1 with
+        whatever count SuperPoint found); padding rows come back as conf rows of zeros and ``matches0 = -1``.
         """
         kpts2d, kpts3d = data["keypoints2d"].float(), data["keypoints3d"].float()
         desc2d = data["descriptors2d_query"].float()
@@ -623,15 +649,22 @@ class GATsSuperGlue(nn.Module):
             raise RuntimeError("onepose_b200.GATsSuperGlue runs on CUDA only (no CPU fallback): move the inputs "
                                "to a B200 device")
         dev = desc2d.device
+        count2d = data.get("count2d")
+        if count2d is not None:
+            count2d = torch.as_tensor(count2d).to(device=dev, dtype=torch.int32).reshape(-1).contiguous()
+            if count2d.numel() != desc2d.shape[0]:
+                raise ValueError(f"count2d has {count2d.numel()} entries for a batch of {desc2d.shape[0]} frames")
+            if not self.use_tensor_cores or self.hparams["with_linear_transform"] or not self.fused_final_normalize:
+                raise NotImplementedError("count2d (ragged batches) exists on the production path only: tensor cores, planes-only streams")
         with torch.cuda.device(dev):
-            return self._forward_cuda(data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
+            return self._forward_cuda(data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev, count2d)
 
-    def _forward_cuda(self, data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev):
+    def _forward_cuda(self, data, kpts2d, kpts3d, desc2d, desc3d, leaves, dev, count2d=None):
         K = data.get("query_intrinsic", data.get("K"))
         scale = float(data.get("pnp_scale", 1000.0))
         if self._graphs_on and self.use_tensor_cores and self._trace is None and not timeline.enabled:
-            return self._forward_graphed(kpts2d, kpts3d, desc2d, desc3d, leaves, K, scale, dev)
-        pred, conf, i0, s0 = self._match(kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
+            return self._forward_graphed(kpts2d, kpts3d, desc2d, desc3d, leaves, K, scale, dev, count2d)
+        pred, conf, i0, s0 = self._match(kpts2d, kpts3d, desc2d, desc3d, leaves, dev, count2d)
         if K is not None:
             from . import pnp
             if self.pnp_overlap:
@@ -646,7 +679,7 @@ class GATsSuperGlue(nn.Module):
                 pred.update(pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, K, scale=scale, refine=self.pnp_refine))
         return pred, conf
 
-    def _match(self, kpts2d, kpts3d, desc2d, desc3d, leaves, dev):
+    def _match(self, kpts2d, kpts3d, desc2d, desc3d, leaves, dev, count2d=None):
         """The matcher proper (:232-274) on the current stream: returns (pred, conf, matches0 [B,N2], scores0 [B,N2])."""
         B, D, N2 = desc2d.shape
         N3 = desc3d.shape[2]
@@ -659,6 +692,8 @@ class GATsSuperGlue(nn.Module):
         # cross-check path and the A/B switches of the similarity kernel: OPB_SIM_CG=1, OPB_SIM_MMA=f16, OPB_LINEAR_CG=1, OPB_LIN_DBG)
         unit_planes = self.use_tensor_cores and self.fused_final_normalize and not any(
             os.environ.get(k) for k in ("OPB_SIM_CG", "OPB_SIM_MMA", "OPB_LINEAR_CG", "OPB_LIN_DBG"))
+        if count2d is not None and not unit_planes:
+            raise NotImplementedError("count2d (ragged batches) needs the production kernels: unset the OPB_SIM_* / OPB_LIN* A/B switches")
         m2 = m3 = None
         if not unit_planes:
             m2 = self._ws.get("m2", (B, N2, _D), torch.float32, dev)
@@ -666,7 +701,7 @@ class GATsSuperGlue(nn.Module):
         planes = None
         if self.use_tensor_cores and not self.hparams["with_linear_transform"]:
             # planes-only streams: the query descriptors go from the public channel-major layout straight into planes + column sums
-            planes = self._encode_tc(None, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=desc2d)
+            planes = self._encode_tc(None, db, pk, B, N2, N3, L, m2, m3, dev, x2_cm=desc2d, count2d=count2d)
         else:
             x2 = self._to_point_major(desc2d, self._ws.get("x2", (B, N2, _D), torch.float32, dev))
             if self.use_tensor_cores:
@@ -684,14 +719,17 @@ class GATsSuperGlue(nn.Module):
         s1 = torch.empty(B, N3, dtype=torch.float32, device=dev)
         nbytes = lib.op_sim_dual_softmax_workspace_bytes(B, N2, N3)
         w = self._ws.get("simws", (nbytes,), torch.uint8, dev)
-        tail = (B, N2, N3, float(self.hparams["scale_factor"]), float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
+        tail = (float(self.hparams["scale_factor"]), float(self.hparams["match_threshold"]), ptr(conf), ptr(i0), ptr(i1), ptr(s0),
                 ptr(s1), ptr(w), nbytes, stream_ptr())
         timeline.work = B * (4.0 * _D * (N2 + N3) + 4.0 * N2 * N3 + 24.0 * (N2 + N3))   # bytes, SURVEY.md 8(d)
         if planes is not None:
             (u2h, u2b), (u3h, u3b) = planes
-            call("op_sim_dual_softmax_planes", ptr(u2h), ptr(u2b), ptr(u3h), ptr(u3b), *tail)
+            if count2d is None:
+                call("op_sim_dual_softmax_planes", ptr(u2h), ptr(u2b), ptr(u3h), ptr(u3b), B, N2, N3, *tail)
+            else:
+                call("op_sim_dual_softmax_planes_ragged", ptr(u2h), ptr(u2b), ptr(u3h), ptr(u3b), B, N2, N3, ptr(count2d), *tail)
         else:
-            call("op_sim_dual_softmax_rows" if self.use_tensor_cores else "op_sim_dual_softmax", ptr(m2), ptr(m3), *tail)
+            call("op_sim_dual_softmax_rows" if self.use_tensor_cores else "op_sim_dual_softmax", ptr(m2), ptr(m3), B, N2, N3, *tail)
         pred = {
             "matches0": i0[0], "matches1": i1[0],                     # batch element 0 only, :269-274
             "matching_scores0": s0[0], "matching_scores1": s1[0],
@@ -713,7 +751,7 @@ class GATsSuperGlue(nn.Module):
             self._graphs.clear()
         return self
 
-    def _forward_graphed(self, kpts2d, kpts3d, desc2d, desc3d, leaves, K, scale, dev):
+    def _forward_graphed(self, kpts2d, kpts3d, desc2d, desc3d, leaves, K, scale, dev, count2d=None):
         from . import pnp
         B, _, N2 = desc2d.shape
         Kt = None
@@ -722,12 +760,12 @@ class GATsSuperGlue(nn.Module):
         key = (dev.index, B, N2, tuple(desc3d.shape), tuple(leaves.shape), tuple(kpts3d.shape), desc3d.data_ptr(), leaves.data_ptr(), kpts3d.data_ptr(),
                desc3d._version, leaves._version, kpts3d._version, desc3d.stride(0), leaves.stride(0), kpts3d.stride(0),
                None if Kt is None else Kt.shape[0], scale, self.pnp_overlap, self.pnp_refine, self.two_streams, self.fused_final_normalize,
-               float(self.hparams["match_threshold"]), float(self.hparams["scale_factor"])) + self._weights_key()
+               float(self.hparams["match_threshold"]), float(self.hparams["scale_factor"]), count2d is not None) + self._weights_key()
         ent = self._graphs.get(key)
         if ent is None:
             if len(self._graphs) >= 2:                                # static outputs (conf!) are large: keep at most two shapes alive
                 self._graphs.pop(next(iter(self._graphs)))
-            ent = self._graphs[key] = self._capture(kpts2d, kpts3d, desc2d, desc3d, leaves, Kt, scale, dev)
+            ent = self._graphs[key] = self._capture(kpts2d, kpts3d, desc2d, desc3d, leaves, Kt, scale, dev, count2d)
         slot = ent["slots"][ent["turn"]]
         ent["turn"] ^= 1
         main = torch.cuda.current_stream(dev)
@@ -735,6 +773,8 @@ class GATsSuperGlue(nn.Module):
             main.wait_event(slot["pose_event"])                       # the RANSAC that last read this slot's gather buffers has finished
         slot["desc2d"].copy_(desc2d, non_blocking=True)
         slot["kpts2d"].copy_(kpts2d, non_blocking=True)
+        if count2d is not None:
+            slot["count2d"].copy_(count2d, non_blocking=True)
         if Kt is not None:
             slot["K"].copy_(Kt, non_blocking=True)
         slot["match_graph"].replay()
@@ -750,20 +790,21 @@ class GATsSuperGlue(nn.Module):
                 slot["pnp_graph"].replay()
         return pred, slot["conf"]
 
-    def _capture(self, kpts2d, kpts3d, desc2d, desc3d, leaves, Kt, scale, dev):
+    def _capture(self, kpts2d, kpts3d, desc2d, desc3d, leaves, Kt, scale, dev, count2d=None):
         from . import pnp
         # one eager call first: weights packed, DB cached, every workspace buffer allocated, every kernel's attributes configured
-        _, _, i0, s0 = self._match(kpts2d, kpts3d, desc2d, desc3d, leaves, dev)
+        _, _, i0, s0 = self._match(kpts2d, kpts3d, desc2d, desc3d, leaves, dev, count2d)
         if Kt is not None:
             pnp.pose_from_matches(i0, s0, kpts2d, kpts3d, Kt, scale=scale, refine=self.pnp_refine)
         torch.cuda.synchronize(dev)
         slots = []
         for _ in range(2):
             slot = dict(desc2d=desc2d.detach().clone().contiguous(), kpts2d=kpts2d.detach().clone().contiguous(),
-                        K=None if Kt is None else Kt.detach().clone().contiguous(), pose_event=None, pnp_graph=None)
+                        K=None if Kt is None else Kt.detach().clone().contiguous(), pose_event=None, pnp_graph=None,
+                        count2d=None if count2d is None else count2d.detach().clone())
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                pred, conf, i0, s0 = self._match(slot["kpts2d"], kpts3d, slot["desc2d"], desc3d, leaves, dev)
+                pred, conf, i0, s0 = self._match(slot["kpts2d"], kpts3d, slot["desc2d"], desc3d, leaves, dev, slot["count2d"])
                 gathered = pnp.gather_matches_device(i0, s0, slot["kpts2d"], kpts3d, scale) if Kt is not None else None
             slot.update(match_graph=g, conf=conf)
             if Kt is not None:
@@ -782,7 +823,7 @@ _POSE_KEYS = ("mkpts2d", "mkpts3d", "mconf", "n_matches", "match_query_idx", "po
 
 class _StreamState:
     """One descriptor stream (2D query / 3D object) of the tensor-core path: see GATsSuperGlue._new_stream."""
-    __slots__ = ("ch", "B", "N", "p", "xs", "parts", "x")
+    __slots__ = ("ch", "B", "N", "p", "xs", "parts", "x", "counts")
 
 
 class LitModelGATsSPG(nn.Module):

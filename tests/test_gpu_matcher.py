@@ -115,6 +115,88 @@ def test_config3_large_object_vs_oracle(damped):
     assert int((pred["matches0_batched"] > -1).sum()) > (30 if damped else 0)
 
 
+def _ragged_batch(obj, counts, n_pad, seed=5):
+    """Frames with different keypoint counts padded to n_pad rows; the padding holds large non-zero junk on purpose."""
+    rng = np.random.default_rng(seed)
+    frames = [synth.make_frame(obj, f, c) for f, c in enumerate(counts) if c > 0]
+    it = iter(frames)
+    q = (50.0 * rng.standard_normal((len(counts), 256, n_pad))).astype(np.float32)
+    k2 = rng.uniform(0, 512, (len(counts), n_pad, 2)).astype(np.float32)
+    per_frame = []
+    for b, c in enumerate(counts):
+        fr = next(it) if c > 0 else None
+        per_frame.append(fr)
+        if fr is not None:
+            q[b, :, :c] = fr.descriptors2d_query
+            k2[b, :c] = fr.keypoints2d
+    data = synth.pack_batch(obj, [f for f in per_frame if f is not None][:1] * len(counts))
+    data["descriptors2d_query"] = torch.from_numpy(q)
+    data["keypoints2d"] = torch.from_numpy(k2)
+    data["count2d"] = torch.tensor(counts, dtype=torch.int32)
+    return data, per_frame
+
+
+@pytest.mark.parametrize("damped", [True, False])
+def test_ragged_batch_equals_oracle_frame_by_frame(damped):
+    """A padded batch of frames with different keypoint counts (data['count2d']) against the oracle run frame by frame at each
+    frame's own N2 -- the reference's usage, inference.py:140-146 (B = 1, whatever count SuperPoint found)."""
+    from oracle import gats_spg_oracle as orc
+    hp = dict(synth.DEFAULT_HPARAMS)
+    if not damped:
+        hp["match_threshold"] = 0.0
+    w = synth.make_weights(0, damped=damped)
+    obj = synth.make_object(0, 1024, 4)
+    counts = [300, 257, 128, 77, 0, 320]
+    data, per_frame = _ragged_batch(obj, counts, 320)
+    m = _model(hp, w)
+    pred, conf = m(_cuda(data))
+    assert torch.isfinite(conf).all()
+    n_matched = 0
+    for b, (c, fr) in enumerate(zip(counts, per_frame)):
+        assert float(conf[b, c:].abs().max()) == 0.0 if c < 320 else True          # padding rows: conf rows of zeros
+        assert bool((pred["matches0_batched"][b, c:] == -1).all())
+        if c == 0:
+            assert float(conf[b].abs().max()) == 0.0 and bool((pred["matches1_batched"][b] == -1).all())
+            continue
+        po, co = orc.matcher_forward(synth.pack_batch(obj, [fr]), w, hp)
+        err = helpers.conf_rel_err(conf[b, :c].cpu(), co[0])
+        assert err < helpers.CONF_RTOL, (b, c, err)
+        helpers.assert_matches_equal_off_ties(pred["matches0_batched"][b, :c].cpu(), po["matches0"], co[0], axis=2)
+        helpers.assert_matches_equal_off_ties(pred["matches1_batched"][b].cpu(), po["matches1"], co[0], axis=1)
+        n_matched += int((pred["matches0_batched"][b, :c] > -1).sum())
+    assert n_matched > (100 if damped else 0)
+    # the same batch through the CUDA-graph serving mode: same bits
+    m.enable_graphs(True)
+    pred_g, conf_g = m(_cuda(data))
+    assert torch.equal(conf_g, conf) and torch.equal(pred_g["matches0_batched"], pred["matches0_batched"])
+    # and the counts are an input of the graph, not baked into it
+    data2 = dict(data); data2["count2d"] = torch.tensor([c // 2 for c in counts], dtype=torch.int32)
+    pred_h, conf_h = m(_cuda(data2))
+    m.enable_graphs(False)
+    pred_e, conf_e = m(_cuda(data2))
+    assert torch.equal(conf_h, conf_e) and torch.equal(pred_h["matches0_batched"], pred_e["matches0_batched"])
+
+
+def test_ragged_batch_pose():
+    """count2d through gather + PnP: padding rows never become correspondences; poses equal the frame-by-frame run."""
+    hp = dict(synth.DEFAULT_HPARAMS)
+    w = synth.make_weights(0, damped=True)
+    obj = synth.make_object(0, 1024, 4)
+    counts = [320, 200, 131]
+    data, per_frame = _ragged_batch(obj, counts, 320)
+    data["query_intrinsic"] = torch.from_numpy(np.stack([synth.INTRINSIC] * len(counts)))
+    m = _model(hp, w)
+    pred, _ = m(_cuda(data))
+    for b, (c, fr) in enumerate(zip(counts, per_frame)):
+        one = synth.pack_batch(obj, [fr]); one["query_intrinsic"] = torch.from_numpy(synth.INTRINSIC[None])
+        p1, _ = m(_cuda(one))
+        assert int(pred["n_matches"][b]) == int(p1["n_matches"][0]) > 20
+        np.testing.assert_allclose(pred["pose"][b].cpu().numpy(), p1["pose"][0].cpu().numpy(), rtol=0, atol=1e-6)
+        R, t = pred["pose"][b, :, :3].cpu().numpy(), pred["pose"][b, :, 3].cpu().numpy()
+        assert np.degrees(np.arccos(np.clip((np.trace(R @ fr.pose_gt[:, :3].T) - 1) / 2, -1, 1))) < 1.0
+        assert np.linalg.norm(t - fr.pose_gt[:, 3]) < 0.01
+
+
 def test_headline_shape_properties():
     """Size-independent properties at the headline shape (2048 x 8192 x 8 leaves), batch of 3 frames."""
     hp = dict(synth.DEFAULT_HPARAMS)

@@ -16,7 +16,7 @@ for line in src:
 blocks = blocks[::2] if len(blocks) == 2 * (len(rows) - 2) else blocks
 for n, r in enumerate(rows[2:]):
     name = r[hdr.index("Kernel Name")][:48]
-    vals = " ".join(f"{lab}={float(r[hdr.index(k)]):.4g}{rows[1][hdr.index(k)] if lab in ('us','rd','wr') else ''}" for k, lab in want.items() if k in hdr and r[hdr.index(k)])
+    vals = " ".join(f"{lab}={float(r[hdr.index(k)]):.4g}{rows[1][hdr.index(k)] if lab in ('us','rd','wr') else ''}" for k, lab in want.items() if k in hdr and r[hdr.index(k)] not in ("", "no data", "n/a"))
     st = ""
     if n < len(blocks):
         b = list(csv.reader(blocks[n])); h = b[0]; b = b[1:]
