@@ -390,6 +390,13 @@ def run_ours(args):
             if work > 0:
                 if name.startswith(("op_linear", "op_atb")):
                     ent.update(bound="tensor", achieved=work / (kms * 1e-3) / 1e12, peak=peaks["tensor"], unit="TFLOP/s")
+                    nbytes = timeline.byte_totals.get(name)
+                    if nbytes:
+                        # the same calls against the other roof: operand / result planes (4 bytes per element) over the measured HBM
+                        # bandwidth, and the issued tensor work (three MMAs per product) over the sustained cuBLAS figure -- whichever
+                        # is larger bounds the kernel
+                        ent.update(hbm_gbs=nbytes / (kms * 1e-3) / 1e9, hbm_frac=nbytes / (kms * 1e-3) / 1e9 / peaks["hbm"],
+                                   tensor_frac_issued=3 * work / (kms * 1e-3) / 1e12 / peaks["tensor"])
                 else:
                     ent.update(bound="hbm", achieved=work / (kms * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")
                 ent["frac"] = ent["achieved"] / ent["peak"]

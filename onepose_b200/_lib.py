@@ -131,9 +131,12 @@ class Timeline:
         self.launches = 0
         self.tag = ""
         self.work = 0.0          # algorithmic flops / bytes of the next call (set by the host code)
+        self.bytes = 0.0         # tensor-bound calls: the operand / result bytes of the next call as well (its HBM side)
+        self.byte_totals = {}    # key -> bytes accumulated over the recorded calls
 
     def reset(self):
         self.records.clear()
+        self.byte_totals.clear()
         self.launches = 0
 
     def summary(self):
@@ -158,9 +161,14 @@ def call(name, *args, tag=None):
         s.record()
         rc = fn(*args)
         e.record()
-        timeline.records.append((name, tag if tag is not None else timeline.tag, s, e, timeline.work))
+        tg = tag if tag is not None else timeline.tag
+        timeline.records.append((name, tg, s, e, timeline.work))
+        if timeline.bytes:
+            key = name if not tg else f"{name}:{tg}"
+            timeline.byte_totals[key] = timeline.byte_totals.get(key, 0.0) + timeline.bytes
         timeline.launches += LAUNCHES.get(name, 1)
     else:
         rc = fn(*args)
     timeline.work = 0.0
+    timeline.bytes = 0.0
     check(rc, name)

@@ -75,7 +75,8 @@ struct NextSamples { int F, h0, h1; unsigned long long *rng; int32_t *samples, *
 // Hypothesis round, stage 1: lane-per-hypothesis minimal solve.  Writes (rvec, tvec) to hyp_pose, the rotation matrix cv2's
 // projectPoints re-derives from rvec plus tvec to round_rt [F][round_cap][12] (slot h - h_begin), and marks the hypothesis in
 // hyp_counts: 0 = solved, to be counted by k_pnp_count; -1 = not evaluated (bad sample, n <= 5, or past the adaptive bound).
-__global__ void __launch_bounds__(kHypBlock)
+template <int MIN_BLOCKS>
+__global__ void __launch_bounds__(kHypBlock, MIN_BLOCKS)
 k_pnp_solve(const float *__restrict__ X32, const float *__restrict__ uv32, const int32_t *__restrict__ count, int stride,
             const double *__restrict__ Kmat, const int32_t *__restrict__ samples, const int32_t *__restrict__ sample_set,
             int H_total, int h_begin, int h_end, int round_cap, const int32_t *__restrict__ bound, int32_t *__restrict__ hyp_counts,
@@ -117,26 +118,56 @@ k_pnp_solve(const float *__restrict__ X32, const float *__restrict__ uv32, const
 // warps fill the machine where the former one-warp-walks-its-32-poses form left 148 SMs to a few warps per frame (BASELINE.json
 // configs[3]: 10k correspondences).  Projection in float64, squared error in float32, inlier iff err <= thr^2: the arithmetic of
 // PnPRansacCallback::computeError; the count is an integer sum, so the split over lanes does not change it.
-constexpr int kCountWarps = 8;
+constexpr int kCountWarps = 8, kCountChunk = 1024;
+// the same arithmetic on a point already widened to float64 (the widening is exact)
+__device__ __forceinline__ float reproj_err_d(const double *Xd, const float2 uv, const double *R, const double *t, const Cam &cam) {
+    double x = R[0] * Xd[0] + R[1] * Xd[1] + R[2] * Xd[2] + t[0];
+    double y = R[3] * Xd[0] + R[4] * Xd[1] + R[5] * Xd[2] + t[1];
+    double z = R[6] * Xd[0] + R[7] * Xd[1] + R[8] * Xd[2] + t[2];
+    z = z != 0.0 ? 1. / z : 1.0;
+    x *= z; y *= z;
+    const float pu = (float)(x * cam.fx + cam.cx), pv = (float)(y * cam.fy + cam.cy);
+    const float d0 = uv.x - pu, d1 = uv.y - pv;
+    float s = d0 * d0;
+    s += d1 * d1;
+    return s;
+}
+// A block = 8 consecutive hypotheses of one frame.  The frame's correspondences pass through shared memory in chunks of 1024,
+// widened to float64 once per block instead of once per hypothesis (the first form read them from global memory inside the loop:
+// ncu long_scoreboard 0.8 of the samples); double[3] rows (stride 24 B) and float2 pixels are bank-conflict free.
 __global__ void __launch_bounds__(kCountWarps * 32)
 k_pnp_count(const float *__restrict__ X32, const float *__restrict__ uv32, const int32_t *__restrict__ count, int stride,
             const double *__restrict__ Kmat, int H_total, int h_begin, int h_end, int round_cap, const int32_t *__restrict__ bound,
             float thr2, const double *__restrict__ round_rt, int32_t *__restrict__ hyp_counts) {
+    __shared__ double sX[kCountChunk * 3];
+    __shared__ float2 suv[kCountChunk];
     const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int h = h_begin + blockIdx.x * kCountWarps + warp;
+    const int hb = h_begin + blockIdx.x * kCountWarps, h = hb + warp;
     const int H = h_end < H_total ? h_end : H_total;
-    if (h >= H || (bound && (h & ~31) >= bound[f])) return;                 // the bound test of the solving warp (32 consecutive hypotheses)
-    if (hyp_counts[(long long)f * H_total + h] < 0) return;                  // not solved
+    if (hb >= H || (bound && (hb & ~31) >= bound[f])) return;               // block-uniform: the bound test of the solving warp (32 consecutive hypotheses)
+    const bool active = h < H && hyp_counts[(long long)f * H_total + h] >= 0;   // solved by k_pnp_solve
     const int n = count[f];
     const Cam cam = load_cam(Kmat + (long long)f * 9);
-    const float *X = X32 + (long long)f * stride * 3, *uv = uv32 + (long long)f * stride * 2;
-    const double *rt = round_rt + ((long long)f * round_cap + (h - h_begin)) * 12;
+    const float *X = X32 + (long long)f * stride * 3;
+    const float2 *uv = reinterpret_cast<const float2 *>(uv32 + (long long)f * stride * 2);
     double R[9], t[3];
+    if (active) {
+        const double *rt = round_rt + ((long long)f * round_cap + (h - h_begin)) * 12;
 #pragma unroll
-    for (int k = 0; k < 9; ++k) R[k] = rt[k];
-    t[0] = rt[9]; t[1] = rt[10]; t[2] = rt[11];
+        for (int k = 0; k < 9; ++k) R[k] = rt[k];
+        t[0] = rt[9]; t[1] = rt[10]; t[2] = rt[11];
+    }
     int c = 0;
-    for (int i = lane; i < n; i += 32) c += reproj_err(X + 3 * i, uv + 2 * i, R, t, cam) <= thr2 ? 1 : 0;
+    for (int c0 = 0; c0 < n; c0 += kCountChunk) {
+        const int m = min(kCountChunk, n - c0);
+        for (int i = threadIdx.x; i < 3 * m; i += kCountWarps * 32) sX[i] = (double)X[3 * c0 + i];
+        for (int i = threadIdx.x; i < m; i += kCountWarps * 32) suv[i] = uv[c0 + i];
+        __syncthreads();
+        if (active)
+            for (int i = lane; i < m; i += 32) c += reproj_err_d(sX + 3 * i, suv[i], R, t, cam) <= thr2 ? 1 : 0;
+        __syncthreads();
+    }
+    if (!active) return;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
     if (lane == 0) hyp_counts[(long long)f * H_total + h] = c;

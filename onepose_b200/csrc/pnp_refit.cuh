@@ -313,8 +313,16 @@ extern "C" int op_pnp_ransac(const double *pts2d, const double *pts3d, const int
             // the next round's samples are drawn by one extra block column of this round's solve
             if (h1 < H) nx = NextSamples{F, h1, round_end(r + 1, h1), w.rng, w.samples, w.sample_set};
         }
-        k_pnp_solve<<<dim3(ceil_div(h1 - h0, kHypBlock) + (nx.h1 > nx.h0 ? 1 : 0), F), kHypBlock, 0, st>>>(
-            w.X32, w.uv32, count, stride, K, samples, sample_set, H, h0, h1, cap, bnd, hyp_counts, hyp_pose, w.round_rt, nx);
+        // two blocks per SM at 255 registers (default); OPB_PNP_SOLVE_OCC=3 / 4 trade registers (168 / 128, more spills) for resident warps:
+        // measured slower at configs[3] (8.6 vs 9.1 / 9.2 ms per 64 frames), kept for A/B runs
+        static const int occ = [] { const char *e = getenv("OPB_PNP_SOLVE_OCC"); return e ? atoi(e) : 2; }();
+        const dim3 sgrid(ceil_div(h1 - h0, kHypBlock) + (nx.h1 > nx.h0 ? 1 : 0), F);
+        if (occ == 4)
+            k_pnp_solve<4><<<sgrid, kHypBlock, 0, st>>>(w.X32, w.uv32, count, stride, K, samples, sample_set, H, h0, h1, cap, bnd, hyp_counts, hyp_pose, w.round_rt, nx);
+        else if (occ == 3)
+            k_pnp_solve<3><<<sgrid, kHypBlock, 0, st>>>(w.X32, w.uv32, count, stride, K, samples, sample_set, H, h0, h1, cap, bnd, hyp_counts, hyp_pose, w.round_rt, nx);
+        else
+            k_pnp_solve<2><<<sgrid, kHypBlock, 0, st>>>(w.X32, w.uv32, count, stride, K, samples, sample_set, H, h0, h1, cap, bnd, hyp_counts, hyp_pose, w.round_rt, nx);
         k_pnp_count<<<dim3(ceil_div(h1 - h0, kCountWarps), F), kCountWarps * 32, 0, st>>>(w.X32, w.uv32, count, stride, K, H, h0, h1, cap, bnd,
                                                                                          thr2, w.round_rt, hyp_counts);
         OPB_CHECK_LAUNCH();

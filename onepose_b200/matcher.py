@@ -340,6 +340,12 @@ class GATsSuperGlue(nn.Module):
         K2 = 0 if A2 is None else A2[0].shape[-1]
         Cout = W[0].shape[-2]
         timeline.work = 2.0 * B * rows * (work_k or (K1 + K2)) * Cout
+        # HBM side of the same call: split-precision planes are 4 bytes per element (hi + lo fp16); a broadcast operand and shared
+        # weights are read once (they stay in L2), per-frame weights once per frame
+        a1b = 1 if flags & 2048 else B
+        a2b = 1 if flags & 4096 else B
+        timeline.bytes = 4.0 * rows * (a1b * K1 + a2b * K2) + 4.0 * B * rows * Cout * ((1 if Cp else 0) + (1 if C is not None else 0)) + \
+            4.0 * Cout * (K1 + K2) * (B if flags & (64 | 512) else 1)
         head = (ptr(A1[0]), ptr(A1[1]), K1, ptr(A2[0]) if A2 else None, ptr(A2[1]) if A2 else None, K2,
                 ptr(W[0]), ptr(W[1]), ptr(W2[0]) if W2 else None, ptr(W2[1]) if W2 else None, ptr(bias), ptr(C), ptr(Cp[0]) if Cp else None, ptr(Cp[1]) if Cp else None,
                 B, rows, Cout, flags, elu_cols, ptr(stats), ptr(ksum), float(zscale_num))
@@ -362,6 +368,7 @@ class GATsSuperGlue(nn.Module):
         nch = lib.op_atb_chunks(M)
         part = self._ws.get("gpart" + tag, (B, nch, _D, _D), torch.float32, dev)
         timeline.work = 2.0 * B * M * _D * _D
+        timeline.bytes = 2 * 4.0 * B * M * _D + 4.0 * B * nch * _D * _D        # K' and X planes in, fp32 chunk partials out
         call("op_atb_tc", ptr(kp[0]), ptr(kp[1]), ptr(src_p[0]), ptr(src_p[1]), B, M, ptr(part), stream_ptr())
         ksum = self._ws.get("ksum" + tag, (B, _D), torch.float32, dev)
         P = self._planes("P" + tag, (B, 2 * _D, _D), dev)

@@ -197,6 +197,48 @@ def test_ragged_batch_pose():
         assert np.linalg.norm(t - fr.pose_gt[:, 3]) < 0.01
 
 
+def test_superpoint_block_feeds_matcher_with_counts():
+    """SuperPoint.forward_batched's padded block handed to the matcher with its per-frame counts equals the reference's usage:
+    one frame at a time with that frame's own key-points (inference.py:140-146)."""
+    from onepose_b200.superpoint import SuperPoint
+    torch.manual_seed(3)
+    sp = SuperPoint({'descriptor_dim': 256, 'nms_radius': 3, 'max_keypoints': 512, 'keypoints_threshold': 0.6}).eval().cuda()
+    rs = np.random.RandomState(1)
+    imgs = rs.randint(0, 256, (3, 1, 160, 192)).astype(np.float32) / 255.0
+    imgs[1, :, 80:] = 0.5; imgs[2, :, :, 64:] = 0.5                    # less texture, fewer key-points
+    out = sp.forward_batched(torch.from_numpy(imgs).cuda())
+    # (the flat score map of a random-weight extractor saturates max_keypoints in every frame: cap the counts per frame so that the
+    # block is ragged; the rows behind a frame's count are then real key-points that must be ignored)
+    out["count"] = torch.minimum(out["count"], torch.tensor([512, 300, 77], dtype=out["count"].dtype, device="cuda"))
+    counts = out["count"].tolist()
+    assert len(set(counts)) > 1 and min(counts) > 8, counts
+    # damped weights: with undamped random-init weights THIS input (descriptors of a random-weight extractor) is so ill-conditioned
+    # that the fp32 oracle itself is 3e-3 - 5e-3 from its float64 run (tools/debug_ragged.py), whatever the batching
+    hp = dict(synth.DEFAULT_HPARAMS); hp["match_threshold"] = 0.0
+    w = synth.make_weights(0, damped=True)
+    obj = synth.make_object(0, 512, 4)
+    db = synth.pack_batch(obj, [synth.make_frame(obj, 0, 8)] * 3)
+    m = _model(hp, w)
+    data = _cuda({k: db[k] for k in ("keypoints3d", "descriptors3d_db", "descriptors2d_db")})
+    data.update(keypoints2d=out["keypoints"], descriptors2d_query=out["descriptors_pm"].transpose(1, 2), count2d=out["count"])
+    pred, conf = m(data)
+    conf = conf.clone(); m0 = pred["matches0_batched"].clone()
+    for b, c in enumerate(counts):
+        one = {k: v[b:b + 1] for k, v in data.items() if k != "count2d"}
+        one["keypoints2d"] = one["keypoints2d"][:, :c]
+        one["descriptors2d_query"] = one["descriptors2d_query"][:, :, :c]
+        p1, c1 = m(one)
+        assert helpers.conf_rel_err(conf[b, :c].cpu(), c1[0].cpu()) < helpers.CONF_RTOL          # measured 5e-5 (0 for the full frame)
+        helpers.assert_matches_equal_off_ties(m0[b, :c].cpu(), p1["matches0"].cpu(), c1[0].cpu(), axis=2)
+        assert bool((m0[b, c:] == -1).all())
+    from oracle import gats_spg_oracle as orc
+    b, c = 2, counts[2]
+    one = {k: v[b:b + 1].cpu() for k, v in data.items() if k != "count2d"}
+    one["keypoints2d"] = one["keypoints2d"][:, :c]; one["descriptors2d_query"] = one["descriptors2d_query"][:, :, :c]
+    _, co = orc.matcher_forward(one, w, hp)
+    assert helpers.conf_rel_err(conf[b, :c].cpu(), co[0]) < helpers.CONF_RTOL
+
+
 def test_headline_shape_properties():
     """Size-independent properties at the headline shape (2048 x 8192 x 8 leaves), batch of 3 frames."""
     hp = dict(synth.DEFAULT_HPARAMS)

@@ -36,8 +36,12 @@ def main():
     db = {"keypoints3d": e(obj.keypoints3d), "descriptors3d_db": e(obj.descriptors3d_db), "descriptors2d_db": e(obj.descriptors2d_db)}
     K = torch.from_numpy(synth.make_frame(obj, 0, 64).K)[None].to(dev)
     rs = np.random.RandomState(0)
-    img_pin = torch.from_numpy(rs.randint(0, 256, (F, 1, 512, 512), dtype=np.uint8)).pin_memory()
+    imgs = rs.randint(0, 256, (F, 1, 512, 512), dtype=np.uint8)
+    for f in range(F):                      # frames differ in how much of the image is textured, so the key-point counts differ
+        imgs[f, :, (f % 4 + 1) * 128:] = 128
+    img_pin = torch.from_numpy(imgs).pin_memory()
     pose_pin = torch.empty(F, 3, 4, dtype=torch.float64).pin_memory()
+    caps = ((torch.arange(F, device=dev) % 4 + 1) * (N2 // 4)).to(torch.int32)
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def step(marks=None):
@@ -45,7 +49,12 @@ def main():
         if marks is not None: marks.append(ev()); marks[-1].record()
         out = sp.forward_batched(img)
         if marks is not None: marks.append(ev()); marks[-1].record()
-        data = dict(db, keypoints2d=out["keypoints"], descriptors2d_query=out["descriptors_pm"].transpose(1, 2), query_intrinsic=K)
+        # the front-end's padded block goes to the matcher as it is: count2d carries every frame's own key-point count (ragged batch).
+        # A random-weight extractor saturates max_keypoints on any image, so the counts are capped per frame (512 .. 2048) to make the
+        # block as ragged as real frames are
+        out["count"] = torch.minimum(out["count"], caps)
+        data = dict(db, keypoints2d=out["keypoints"], descriptors2d_query=out["descriptors_pm"].transpose(1, 2), query_intrinsic=K,
+                    count2d=out["count"])
         pred, _ = matcher(data)
         pose_pin.copy_(pred["pose"], non_blocking=True)
         if marks is not None: marks.append(ev()); marks[-1].record()
@@ -65,7 +74,8 @@ def main():
     parts = [marks[i].elapsed_time(marks[i + 1]) for i in range(3)]
     print(json.dumps({"frames": F, "ms_per_step": round(ms, 3), "frames_per_s": round(F / ms * 1e3, 1),
                       "upload_ms": round(parts[0], 3), "superpoint_ms": round(parts[1], 3), "matcher_pnp_ms": round(parts[2], 3),
-                      "keypoints_per_frame": float(out["count"].float().mean()), "mean_matches": float(pred["n_matches"].float().mean()),
+                      "keypoints_per_frame": float(out["count"].float().mean()), "keypoints_min": int(out["count"].min()), "keypoints_max": int(out["count"].max()),
+                      "mean_matches": float(pred["n_matches"].float().mean()),
                       "h2d_bytes_per_step": img_pin.numel(), "note": "random extractor weights: matches carry no object signal, PnP is cheap"}))
 
 
