@@ -362,6 +362,10 @@ extern "C" int op_linear_tc_ragged(const void *A1h, const void *A1l, int K1, con
     p.w2_ident = w2_ident ? 1 : 0;
     p.a_bcast = ((flags & OPB_LIN_A1_BCAST) ? 1 : 0) | ((flags & OPB_LIN_A2_BCAST) ? 2 : 0);
     p.row_counts = row_counts;
+    // L2 prefetch of the A boxes ahead of their TMA loads: measured SLOWER at every distance (profiles/r02h_linear_prefetch.txt:
+    // K' 224 -> 230 / 233 / 289 us, MLP0 695 -> 726 / 727 / 732 us at 2 / 4 / 8 k-blocks ahead), so it is off; the switch stays for A/B runs
+    static const int prefetch = [] { const char *e = getenv("OPB_LIN_PF"); return e ? atoi(e) : 0; }();
+    p.prefetch = prefetch;
     static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
     const int groups = sm_count() / cg;                                   // persistent CTAs (or CTA pairs), one per SM

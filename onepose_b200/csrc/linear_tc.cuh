@@ -58,6 +58,7 @@ struct Params {
     int w2_ident;                  // pair form: W2 is the 256 x 256 identity (planes (64, 0)); the A2 part is issued as N = 64 MMAs on its diagonal blocks
     int a_bcast;                   // bit 0: A1 is one [1, rows, K1] tensor read by every frame; bit 1: the same for A2
     int w2;                        // 0: W spans K1+K2 columns; 1: the A2 part has its own weight W2 [Cout][K2]; 2: W2 is [B][Cout][K2]
+    int prefetch;                  // k-blocks by which the A operand's L2 prefetch runs ahead of its TMA load (0 = off; OPB_LIN_PF)
     const int *row_counts;         // ragged batches (op_linear_tc_ragged): [B] valid rows per frame, rows past a frame's count are padding --
                                    // left out of every cross-row statistic and written as zeros by the COLSUM producers; null = all rows valid
 };
@@ -156,11 +157,27 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
     if (warp == 8) {
         // ================= TMA producer =================
         if (lane == 0) {
+            // Experiment switch (OPB_LIN_PF, off by default): L2 prefetch of the A boxes p.prefetch k-blocks ahead of their TMA load --
+            // more bytes in flight than the three-stage ring holds, at no shared-memory cost.  It was tried against the idea that
+            // the MMA thread waits for operands from HBM (MLP0: tensor pipe 62 % active); every distance measured slower.
+            auto prefetch_a = [&](int t, int kb) {
+                while (kb >= nkb) { kb -= nkb; t += tile_step; }
+                if (t >= p.total_tiles) return;
+                int b, rt, ct; decode(t, b, rt, ct);
+                const bool second = kb >= nkb1;
+                const int ka = (second ? kb - nkb1 : kb) * BK;
+                const int ab = (p.a_bcast >> (second ? 1 : 0)) & 1 ? 0 : b;
+                tc::tma_prefetch_l2_3d(second ? &tm_a2h : &tm_a1h, ka, rt * BM, ab);
+                tc::tma_prefetch_l2_3d(second ? &tm_a2l : &tm_a1l, ka, rt * BM, ab);
+            };
+            if (p.prefetch > 0)
+                for (int d = 0; d < p.prefetch; ++d) prefetch_a(first_tile, d);
             uint32_t it = 0;
             for (int t = first_tile; t < p.total_tiles; t += tile_step) {
                 int b, rt, ct; decode(t, b, rt, ct);
                 const int wrow = ct * BN + (int)rank * Cfg<CG>::W_ROWS;       // this CTA's rows of the W block
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    if (p.prefetch > 0) prefetch_a(t, kb + p.prefetch);
                     const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
                     uint8_t *st = smem + stage * STAGE_BYTES;
                     const bool second = kb >= nkb1;

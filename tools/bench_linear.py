@@ -13,6 +13,7 @@ x_p = (h(B, N, 256), h(B, N, 256)); q_p = (h(B, N, 256), h(B, N, 256)); hn_p = (
 W256 = (h(256, 256), h(256, 256)); W0a = (h(512, 256), h(512, 256)); P = (h(B, 512, 256), h(B, 512, 256)); W1s = (h(B, 256, 512), h(B, 256, 512))
 bias = torch.randn(512, device=dev); cb = torch.randn(B, 512, device=dev); ksum = torch.rand(B, 256, device=dev) + 1
 x = torch.randn(B, N, 256, device=dev)
+eye_p = ((64.0 * torch.eye(256, device=dev)).half(), torch.zeros(256, 256, device=dev).half())
 st256 = torch.empty(B, parts, 256, 2, device=dev); st512 = torch.empty(B, parts, 512, 2, device=dev)
 
 
@@ -28,10 +29,11 @@ cases = {
     "q    (ELU1|COLSUM|ZSCALE, planes)": (lambda: lin(x_p, W256, bias, 256, Cp=q_p, flags=1 | 16 | 32, elu=256, stats=st256, ksum=ksum), 2.0 * B * N * 256 * 256),
     "mlp0 (BIASB|CSTATS_RELU|W2B, planes)": (lambda: lin(x_p, W0a, cb, 512, A2=q_p, W2=P, Cp=hn_p, flags=128 | 256 | 512, stats=st512), 2.0 * B * N * 512 * 512),
     "mlp1 (RESIDUAL|COLSUM|WB, fp32+planes)": (lambda: lin(hn_p, W1s, bias, 256, C=x, Cp=x_p, flags=2 | 16 | 64, stats=st256), 2.0 * B * N * 512 * 256),
+    "mlp1p (COLSUM|WB|W2_IDENTITY, planes, in place)": (lambda: lin(hn_p, W1s, bias, 256, A2=x_p, W2=eye_p, Cp=x_p, flags=16 | 64 | 1024 | 8192, stats=st256), 2.0 * B * N * 512 * 256),
     "final (fp32)": (lambda: lin(x_p, W256, bias, 256, C=x), 2.0 * B * N * 256 * 256),
     "plain planes": (lambda: lin(x_p, W256, bias, 256, Cp=q_p), 2.0 * B * N * 256 * 256),
 }
-print(f"B={B} N={N} cg={os.environ.get('OPB_LINEAR_CG', '2')} dbg={os.environ.get('OPB_LIN_DBG', '0')}")
+print(f"B={B} N={N} cg={os.environ.get('OPB_LINEAR_CG', '2')} dbg={os.environ.get('OPB_LIN_DBG', '0')} pf={os.environ.get('OPB_LIN_PF', 'default')}")
 for name, (fn, flops) in cases.items():
     for _ in range(2): fn()
     torch.cuda.synchronize()
