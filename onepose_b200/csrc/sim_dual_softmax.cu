@@ -381,6 +381,9 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
                 OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<1>()));
                 OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2>()));
                 OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1, 1, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2, 2, 0>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1, 1, 3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2, 3, 0>()));
+                OPB_CHECK_CUDA(cudaFuncSetAttribute(simtc16::k_sim16<2, 1, 1, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, simtc16::smem_bytes<2, 2, 1>()));
                 configured16 = true;
             }
             cudaLaunchConfig_t cfg = {};
@@ -402,7 +405,13 @@ static int sim_impl(bool tensor_cores, bool normalize, const float *m2, const fl
             static const bool wide = [] { const char *e = getenv("OPB_SIM_STORE"); return !(e && e[0] == 'n'); }();
             CUtensorMap tconf_w = tconf;
             if (f8 && wide && q.tma_store) { if ((rc = make_tmap_f32_3d_store_wide(&tconf_w, conf, B, N2, N3, 16))) return rc; }
-            if (f8 && wide) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q));
+            // pass-2 shared memory plan (OPB_SIM_P2): "4s" = four ring units + one staging buffer per warp, "2d" = two units + two buffers,
+            // "2s" / "3s" = fewer units with one buffer (A/B runs of the ring depth alone)
+            static const int p2plan = [] { const char *e = getenv("OPB_SIM_P2"); return !e ? 0 : (!strcmp(e, "2d") ? 1 : !strcmp(e, "2s") ? 2 : !strcmp(e, "3s") ? 3 : 0); }();
+            if (f8 && wide && p2plan == 1) { cfg.dynamicSmemBytes = simtc16::smem_bytes<2, 2, 1>(); OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1, 2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q)); }
+            else if (f8 && wide && p2plan == 2) { cfg.dynamicSmemBytes = simtc16::smem_bytes<2, 2, 0>(); OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1, 2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q)); }
+            else if (f8 && wide && p2plan == 3) { cfg.dynamicSmemBytes = simtc16::smem_bytes<2, 3, 0>(); OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1, 3, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q)); }
+            else if (f8 && wide) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf_w, q));
             else if (f8) OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 1>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
             else OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, simtc16::k_sim16<2, 0>, t2h, t2l, t2x, t3h, t3l, t3x, tconf, q));
             k_sim_finalize_max<<<dim3(ceil_div(N2, 256), B), 256, 0, st>>>(w.rowmax_part, splits * 4, N2, N3, w.idx0, w.val0, conf, n2_counts);

@@ -26,11 +26,12 @@ using simtc::TILE_BYTES;
 
 constexpr int EW = 16;                                // epilogue warps
 constexpr int THREADS = (EW + 2) * 32;                // 576
-constexpr int BN = 256, UNITS = 4, UNIT_BYTES = 128 * 128, B_ROWS = 128, QCOLS = 64;
-constexpr int STG_WARP_BYTES = 32 * 16 * 4;           // per epilogue warp: 32 rows x 16 fp32 columns (pass 2)
-constexpr int STG_BYTES = EW * STG_WARP_BYTES;        // 32768
-template <int PASS>
-constexpr int smem_bytes() { return A_BYTES + RING_BYTES + (PASS == 2 ? STG_BYTES : 0) + 256 + 1024; }   // + barriers + alignment slack
+constexpr int BN = 256, MAX_UNITS = 4, UNIT_BYTES = 128 * 128, B_ROWS = 128, QCOLS = 64;
+constexpr int STG_BUF_BYTES = 32 * 16 * 4;            // one staging buffer: 32 rows x 16 fp32 columns, or 16 rows x 32 columns (pass 2)
+// NU = ring units of 16 KB (B operand), DB = 1: two staging buffers per epilogue warp.  Shared memory is full with A resident (128 KB):
+// 4 units + one buffer per warp (64 + 32 KB) or 2 units + two buffers per warp (32 + 64 KB).
+template <int PASS, int NU = 4, int DB = 0>
+constexpr int smem_bytes() { return A_BYTES + NU * UNIT_BYTES + (PASS == 2 ? EW * STG_BUF_BYTES * (DB ? 2 : 1) : 0) + 256 + 1024; }   // + barriers + alignment slack
 
 struct Params {
     int N2, N3, tiles_n, tiles_m, tiles_per_split;
@@ -48,11 +49,11 @@ struct Params {
 };
 
 struct Barriers {
-    uint64_t a_full, b_full[UNITS], b_empty[UNITS], acc_full[2], acc_empty[2];
+    uint64_t a_full, b_full[MAX_UNITS], b_empty[MAX_UNITS], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
 
-template <int PASS, int F8, int WIDE = 0>
+template <int PASS, int F8, int WIDE = 0, int NU = 4, int DB = 0>
 __global__ void __launch_bounds__(THREADS, 1)
 k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUtensorMap tm_m2l, const __grid_constant__ CUtensorMap tm_m2x,
         const __grid_constant__ CUtensorMap tm_m3h, const __grid_constant__ CUtensorMap tm_m3l, const __grid_constant__ CUtensorMap tm_m3x,
@@ -60,8 +61,9 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t *sA = smem, *sB = smem + A_BYTES;
-    uint8_t *s_stg = smem + A_BYTES + RING_BYTES;
-    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + RING_BYTES + (PASS == 2 ? STG_BYTES : 0));
+    constexpr int UNITS = NU, STG_WARP_BYTES = STG_BUF_BYTES * (DB ? 2 : 1);
+    uint8_t *s_stg = smem + A_BYTES + NU * UNIT_BYTES;
+    Barriers *bar = reinterpret_cast<Barriers *>(smem + A_BYTES + NU * UNIT_BYTES + (PASS == 2 ? EW * STG_WARP_BYTES : 0));
 
     const uint32_t rank = tc::cluster_ctarank();                          // 0 = leader of the pair (row tiles 2i, 2i + 1)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -229,7 +231,8 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
             uint32_t tc_off[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) tc_off[k] = (uint32_t)(tc_par * 64 + (((tc_c >> 2) ^ k) << 4) + (tc_c & 3) * 4);
-            uint8_t *stg = s_stg + warp * STG_WARP_BYTES;
+            uint8_t *stg0 = s_stg + warp * STG_WARP_BYTES;
+            uint8_t *stg = stg0;                                           // (the narrow form uses one buffer)
             auto load_lgc = [&](int tt, int k) -> float {                 // column term of column (lane + 32 k) of this warp's quarter of tile tt
                 const int col = tt * BN + qtr * QCOLS + 32 * k + lane;
                 return (tt < t1 && col < p.N3) ? __ldg(p.lgC + (long long)b * p.N3 + col) : -INFINITY;
@@ -267,7 +270,10 @@ k_sim16(const __grid_constant__ CUtensorMap tm_m2h, const __grid_constant__ CUte
                         uint32_t ck = 0u;
 #pragma unroll
                         for (int hf = 0; hf < 2; ++hf) {
-                            if (lane == 0) tc::tma_store_wait_read0();        // the previous store has read the staging buffer
+                            // DB: the two halves of a chunk alternate between the warp's two buffers, so a half only waits for the
+                            // store issued one whole chunk earlier (at most one younger store still reading); one buffer: for the previous half's
+                            uint8_t *stg = stg0 + (DB ? hf * STG_BUF_BYTES : 0);
+                            if (lane == 0) { if (DB) tc::tma_store_wait_read1(); else tc::tma_store_wait_read0(); }
                             __syncwarp();
                             if ((lane >> 4) == hf) {
 #pragma unroll

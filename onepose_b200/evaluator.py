@@ -95,23 +95,61 @@ def _copy_stream(dev):
 
 
 @torch.no_grad()
-def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=64, scale=1000.0, evaluator=None):
+class _PinnedStaging:
+    """Two alternating sets of pinned host buffers: pageable inputs are staged through them so that the uploads of run_sequence stay
+    asynchronous (a non_blocking copy from pageable memory silently serialises).  A set is reused only after the uploads that read it
+    have completed (its event)."""
+
+    def __init__(self):
+        self.slots = [dict(bufs={}, event=None), dict(bufs={}, event=None)]
+        self.turn = 0
+
+    def begin(self):
+        slot = self.slots[self.turn]
+        self.turn ^= 1
+        if slot["event"] is not None:
+            slot["event"].synchronize()
+        return slot
+
+    @staticmethod
+    def stage(slot, name, t):
+        t = torch.as_tensor(t)
+        if t.is_cuda or t.is_pinned():
+            return t
+        buf = slot["bufs"].get(name)
+        if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
+            buf = slot["bufs"][name] = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+        buf.copy_(t)
+        return buf
+
+
+@torch.no_grad()
+def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=64, scale=1000.0, evaluator=None, counts2d=None):
     """The loop of inference_core (inference.py:132-160) for one object and F query frames, in blocks of ``batch`` frames.
 
     keypoints2d [F,N2,2], descriptors2d [F,256,N2] (the extractor's outputs, any float dtype, host or device), K [3,3] or
     [F,3,3], poses_gt [F,3,4] / [F,4,4] or None.  Returns dict(pose [F,3,4] float64, pose_homo [F,4,4], n_matches [F],
-    n_inliers [F]) as CUDA tensors and, with ground truth, 'eval' = Evaluator.summarize()."""
+    n_inliers [F]) as CUDA tensors and, with ground truth, 'eval' = Evaluator.summarize().
+    counts2d [F] (optional): per-frame key-point counts of a padded block (``data['count2d']`` of GATsSuperGlue.forward)."""
     matcher = getattr(model, "matcher", model)
     dev = db.keypoints3d.device
     db.register(matcher)
     F = keypoints2d.shape[0]
+    if F == 0:                                                            # an empty sequence: nothing to match, nothing to evaluate
+        res = dict(pose=torch.zeros(0, 3, 4, dtype=torch.float64, device=dev), n_matches=torch.zeros(0, dtype=torch.int32, device=dev),
+                   n_inliers=torch.zeros(0, dtype=torch.int32, device=dev), pose_homo=torch.zeros(0, 4, 4, dtype=torch.float64, device=dev))
+        if poses_gt is not None:
+            res["eval"] = {}
+        return res
     K = torch.as_tensor(K, dtype=torch.float64)
     K = (K[None].expand(F, 3, 3) if K.dim() == 2 else K).to(dev)
     evaluator = evaluator if evaluator is not None else Evaluator()
     out = {k: [] for k in ("pose", "n_matches", "n_inliers")}
     # A three-stage pipeline over the blocks: block i+1 is uploaded on a copy stream while block i is matched on the caller's stream,
     # and gather + PnP + pose errors of block i run on the matcher's pose stream (GATsSuperGlue.pnp_overlap) next to the matcher of
-    # block i+1.  Host buffers should be pinned for the upload to be asynchronous.
+    # block i+1.  Pageable host inputs are staged through pinned buffers (pinned or device inputs are used as they are).
+    staging = _PinnedStaging()
+    cnt_dev = None if counts2d is None else torch.as_tensor(counts2d).to(device=dev, dtype=torch.int32)
     main = torch.cuda.current_stream(dev)
     copy = _copy_stream(dev)
     overlap_was = getattr(matcher, "pnp_overlap", None)
@@ -120,11 +158,13 @@ def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=
 
     def upload(f0):
         f1 = min(F, f0 + batch)
+        slot = staging.begin()
         with torch.cuda.stream(copy):
-            kp = torch.as_tensor(keypoints2d[f0:f1]).to(dev, non_blocking=True)
-            ds = torch.as_tensor(descriptors2d[f0:f1]).to(dev, non_blocking=True)
-            gt = None if poses_gt is None else torch.as_tensor(poses_gt[f0:f1]).to(dev, non_blocking=True)
-            return f0, f1, kp, ds, gt, copy.record_event()
+            kp = staging.stage(slot, "kp", keypoints2d[f0:f1]).to(dev, non_blocking=True)
+            ds = staging.stage(slot, "ds", descriptors2d[f0:f1]).to(dev, non_blocking=True)
+            gt = None if poses_gt is None else staging.stage(slot, "gt", poses_gt[f0:f1]).to(dev, non_blocking=True)
+            slot["event"] = copy.record_event()
+            return f0, f1, kp, ds, gt, slot["event"]
 
     copy.wait_stream(main)
     nxt = upload(0) if F > 0 else None
@@ -140,6 +180,8 @@ def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=
             data["keypoints2d"], data["descriptors2d_query"] = kp, ds
             data["query_intrinsic"] = K[f0:f1]
             data["pnp_scale"] = scale
+            if cnt_dev is not None:
+                data["count2d"] = cnt_dev[f0:f1]
             pred, _ = matcher(data)
             preds.append(pred)
             if gt is not None:

@@ -115,6 +115,18 @@ def test_run_sequence_and_device_evaluator():
         assert int(res["n_matches"][f]) == int(valid.sum()) and int(res["n_inliers"][f]) == len(inl)
         ev.evaluate(pose_homo, gt[f])
     assert res["eval"] == ev.summarize(verbose=False)
+    # an empty sequence returns empty results; a padded block with per-frame counts equals the truncated frames
+    empty = run_sequence(m, db, q["keypoints2d"][:0], q["descriptors2d_query"][:0], frames[0].K)
+    assert empty["pose"].shape == (0, 3, 4) and empty["n_matches"].numel() == 0
+    cnt = torch.tensor([256, 200, 131, 256, 64], dtype=torch.int32)
+    res_c = run_sequence(m, db, q["keypoints2d"], q["descriptors2d_query"], frames[0].K, batch=3, counts2d=cnt)
+    for f in range(5):
+        c = int(cnt[f])
+        data = dict(db.inputs(1), keypoints2d=q["keypoints2d"][f:f + 1, :c].cuda(), descriptors2d_query=q["descriptors2d_query"][f:f + 1, :, :c].cuda(),
+                    query_intrinsic=torch.from_numpy(frames[f].K)[None])
+        pred, _ = m(data)
+        assert int(res_c["n_matches"][f]) == int(pred["n_matches"][0])
+        np.testing.assert_allclose(res_c["pose"][f].cpu().numpy(), pred["pose"][0].cpu().numpy(), rtol=0, atol=1e-6)
     # device-side errors against the reference arithmetic on the fixture poses
     inp = orc.db_builder_inputs()
     t, r = pose_errors(torch.from_numpy(inp["poses_pred"]).cuda(), torch.from_numpy(inp["poses_gt"]).cuda())
