@@ -1,6 +1,8 @@
 // (2) Fused linear layer on the 5th-gen tensor cores -- the 1x1 Conv1d projections of MultiHeadedAttention / MLP /
 // final_proj (GATs_SuperGlue.py:108-120,135-147,194-199,241).  Kernel in linear_tc.cuh; this file holds the
 // elementwise producers of the split-precision planes and the C ABI.
+#include <cstring>
+#include <stdlib.h>
 #include "common.cuh"
 #include "linear_tc.cuh"
 #include <cooperative_groups.h>
@@ -318,22 +320,39 @@ extern "C" int op_linear_tc_ragged(const void *A1h, const void *A1l, int K1, con
     static const int cg = [] { const char *e = getenv("OPB_LINEAR_CG"); return (e && e[0] == '1') ? 1 : 2; }();
     const int wbox = lintc::BN / cg;                  // rows of a W block one CTA loads
     const int a1b = (flags & OPB_LIN_A1_BCAST) ? 1 : B, a2b = (flags & OPB_LIN_A2_BCAST) ? 1 : B;
-    if ((rc = make_tmap_f16_3d(&ta1h, A1h, a1b, rows_per_batch, K1, lintc::BM)) || (rc = make_tmap_f16_3d(&ta1l, A1l, a1b, rows_per_batch, K1, lintc::BM)) ||
-        (rc = make_tmap_f16_3d(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)) ||
-        (rc = make_tmap_f16_3d(&twl, Wl, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)))
+    const bool w2_ident = (flags & OPB_LIN_W2_IDENTITY) && cg == 2;
+    OPB_CHECK_ARG(!(flags & OPB_LIN_W2_IDENTITY) || (W2h && K2 == 256 && Cout == 256 && !(flags & OPB_LIN_W2BATCHED)),
+                  "op_linear_tc: W2_IDENTITY needs unbatched W2 planes with K2 = Cout = 256");
+    // OPB_LIN_BK=32 (A/B runs): k-blocks of 32 in six ring slots (Cfg<2, 32>) for the specialised instantiations without the identity
+    // residual -- the same 192 KB ring in finer slots, tried against the ring's round trip.  Measured slower (profiles/r02i_linear_bk32.txt:
+    // K' 221 -> 229 us, MLP0 668 -> 725 us; 23.3 -> 24.4 ms per bench step): twice the barrier / TMA traffic and 64-byte rows cost more
+    // than the two extra slots in flight bring.  The operand maps follow the kernel's k-block (box columns, swizzle).
+    static const bool want_k32 = [] { const char *e = getenv("OPB_LIN_BK"); return e && !strcmp(e, "32"); }();
+    static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
+    const int key = (flags & lintc::kEpiMask) | (C ? lintc::kHasC : 0) | (Ch ? lintc::kHasP : 0);
+    constexpr int kK = OPB_LIN_ELU1 | OPB_LIN_COLSUM | lintc::kHasP;                          // K' projection
+    constexpr int kQ = OPB_LIN_ELU1 | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | lintc::kHasP;         // Q projection
+    constexpr int kM0 = OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU | lintc::kHasP;                   // MLP layer 0
+    constexpr int kM1 = OPB_LIN_COLSUM | lintc::kHasP;                                        // MLP layer 1 (residual inside the GEMM)
+    constexpr int kF = lintc::kHasC;                                                          // final projection (fp32 output)
+    constexpr int kFN = OPB_LIN_UNIT_PLANES8 | lintc::kHasP;                                  // final projection + F.normalize -> similarity operand planes
+    const bool k32 = want_k32 && cg == 2 && !dbg && !w2_ident && (key == kK || key == kQ || key == kM0 || key == kF || key == kFN);
+    auto amap = [&](CUtensorMap *m, const void *base, int batch, int rows, int cols, int box_rows) {
+        return k32 ? make_tmap_f16_3d_k32(m, base, batch, rows, cols, box_rows) : make_tmap_f16_3d(m, base, batch, rows, cols, box_rows);
+    };
+    if ((rc = amap(&ta1h, A1h, a1b, rows_per_batch, K1, lintc::BM)) || (rc = amap(&ta1l, A1l, a1b, rows_per_batch, K1, lintc::BM)) ||
+        (rc = amap(&twh, Wh, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)) ||
+        (rc = amap(&twl, Wl, (flags & OPB_LIN_WBATCHED) ? B : 1, Cout, K, wbox)))
         return rc;
     if (K2) {
-        if ((rc = make_tmap_f16_3d(&ta2h, A2h, a2b, rows_per_batch, K2, lintc::BM)) || (rc = make_tmap_f16_3d(&ta2l, A2l, a2b, rows_per_batch, K2, lintc::BM)))
+        if ((rc = amap(&ta2h, A2h, a2b, rows_per_batch, K2, lintc::BM)) || (rc = amap(&ta2l, A2l, a2b, rows_per_batch, K2, lintc::BM)))
             return rc;
     } else {
         ta2h = ta1h; ta2l = ta1l;
     }
-    const bool w2_ident = (flags & OPB_LIN_W2_IDENTITY) && cg == 2;
-    OPB_CHECK_ARG(!(flags & OPB_LIN_W2_IDENTITY) || (W2h && K2 == 256 && Cout == 256 && !(flags & OPB_LIN_W2BATCHED)),
-                  "op_linear_tc: W2_IDENTITY needs unbatched W2 planes with K2 = Cout = 256");
     if (W2h) {
         const int wb = (flags & OPB_LIN_W2BATCHED) ? B : 1;
-        if ((rc = make_tmap_f16_3d(&tw2h, W2h, wb, Cout, K2, w2_ident ? 32 : wbox)) || (rc = make_tmap_f16_3d(&tw2l, W2l, wb, Cout, K2, wbox))) return rc;
+        if ((rc = amap(&tw2h, W2h, wb, Cout, K2, w2_ident ? 32 : wbox)) || (rc = amap(&tw2l, W2l, wb, Cout, K2, wbox))) return rc;
     } else {
         tw2h = twh; tw2l = twl;
     }
@@ -366,7 +385,6 @@ extern "C" int op_linear_tc_ragged(const void *A1h, const void *A1l, int K1, con
     // K' 224 -> 230 / 233 / 289 us, MLP0 695 -> 726 / 727 / 732 us at 2 / 4 / 8 k-blocks ahead), so it is off; the switch stays for A/B runs
     static const int prefetch = [] { const char *e = getenv("OPB_LIN_PF"); return e ? atoi(e) : 0; }();
     p.prefetch = prefetch;
-    static const int dbg = [] { const char *e = getenv("OPB_LIN_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
     const int groups = sm_count() / cg;                                   // persistent CTAs (or CTA pairs), one per SM
     cudaLaunchConfig_t cfg = {};
@@ -380,29 +398,28 @@ extern "C" int op_linear_tc_ragged(const void *A1h, const void *A1l, int K1, con
     cfg.attrs = attr; cfg.numAttrs = 1;
     // one specialised instantiation per layer kind of the matcher (epilogue flags and output kinds as compile-time constants), the
     // generic kernel for everything else, for the one-CTA form and whenever experiment switches are set
-    const int key = (flags & lintc::kEpiMask) | (C ? lintc::kHasC : 0) | (Ch ? lintc::kHasP : 0);
     auto launch = [&](auto kern, int smem_bytes) -> cudaError_t {
-        static const void *configured[16];       // kernels whose dynamic shared memory limit has been raised (all share one pointer type)
+        static const void *configured[24];       // kernels whose dynamic shared memory limit has been raised (all share one pointer type)
         static int n_configured = 0;
         bool seen = false;
         for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void *)kern;
         if (!seen) {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
             if (e != cudaSuccess) return e;
-            if (n_configured < 16) configured[n_configured++] = (const void *)kern;
+            if (n_configured < 24) configured[n_configured++] = (const void *)kern;
         }
         return cudaLaunchKernelEx(&cfg, kern, ta1h, ta1l, ta2h, ta2l, twh, twl, tw2h, tw2l, tc_, tch, tcl, p);
     };
-    constexpr int kK = OPB_LIN_ELU1 | OPB_LIN_COLSUM | lintc::kHasP;                          // K' projection
-    constexpr int kQ = OPB_LIN_ELU1 | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | lintc::kHasP;         // Q projection
-    constexpr int kM0 = OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU | lintc::kHasP;                   // MLP layer 0
-    constexpr int kM1 = OPB_LIN_COLSUM | lintc::kHasP;                                        // MLP layer 1 (residual inside the GEMM)
-    constexpr int kF = lintc::kHasC;                                                          // final projection (fp32 output)
-    constexpr int kFN = OPB_LIN_UNIT_PLANES8 | lintc::kHasP;                                  // final projection + F.normalize -> similarity operand planes
     const int smem2 = lintc::Cfg<2>::SMEM_BYTES;
+    static_assert(lintc::Cfg<2, 32>::SMEM_BYTES == lintc::Cfg<2>::SMEM_BYTES, "both ring forms fill the same shared memory");
     OPB_CHECK_ARG(!unit8 || (cg == 2 && !dbg), "op_linear_tc: UNIT_PLANES8 exists in the pair form only (unset OPB_LINEAR_CG / OPB_LIN_DBG)");
     if (cg == 1) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<1, -1>, lintc::Cfg<1>::SMEM_BYTES));
     else if (dbg) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, -1>, smem2));
+    else if (key == kK && k32) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kK, 32>, smem2));
+    else if (key == kQ && k32) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kQ, 32>, smem2));
+    else if (key == kM0 && k32) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kM0, 32>, smem2));
+    else if (key == kF && k32) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kF, 32>, smem2));
+    else if (key == kFN && k32) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kFN, 32>, smem2));
     else if (key == kK) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kK>, smem2));
     else if (key == kQ) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kQ>, smem2));
     else if (key == kM0) OPB_CHECK_CUDA(launch(lintc::k_linear_tc<2, kM0>, smem2));

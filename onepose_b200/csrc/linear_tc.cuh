@@ -19,22 +19,28 @@
 namespace opb {
 namespace lintc {
 
-constexpr int BM = 128, BN = 256, BK = 64;
-constexpr int A_PLANE = BM * BK * 2;                  // 16384
+constexpr int BM = 128, BN = 256, BK = 64;             // BK: the granularity of K the entry point requires; the kernel's k-block is BKT
 constexpr int BIAS_FLOATS = 512;
 constexpr int EPI_WARPS = 8, THREADS = (EPI_WARPS + 2) * 32;
 constexpr int STG_BUF = 32 * 64;                      // TMA-store staging buffer: 32 rows x 64 bytes (16 fp32 or 32 fp16 columns)
 constexpr int STG_BYTES = EPI_WARPS * 2 * STG_BUF;    // two per epilogue warp = 32768
-constexpr int MAX_STAGES = 3;
+constexpr int MAX_STAGES = 6;
 // CG = 1: one CTA per 128 x 256 tile, the whole 256-row W block per stage (96 KB, two stages).
 // CG = 2: a CTA pair (cta_group::2, two SMs of a TPC) per 256 x 256 tile: each CTA stages its own 128 rows of A and HALF of the W
 //         block (64 KB per stage, three stages) -- a third less L2 -> SM traffic per flop, which is what bounds the CG = 1 form
 //         (96 KB per 1536 MMA cycles = 62 B/clk/SM against the ~42 B/clk/SM the L2 delivers chip-wide).
-template <int CG>
+// BKT = 64: k-blocks of 64 (128-byte rows, SWIZZLE_128B), 3 stages of 64 KB in the pair form.  BKT = 32: k-blocks of 32 (64-byte rows,
+//         SWIZZLE_64B), 6 stages of 32 KB: the same 192 KB ring in finer slots.  A slot is free again only when the MMAs of its k-block
+//         have retired, so of three big stages one is always being consumed and two are in flight; of six small ones five are.  The ring's
+//         round trip (commit -> empty -> TMA issue -> L2 -> shared memory -> full) is what the MMA thread waits for (MLP0: tensor pipe
+//         62 % active in isolation), and the bytes in flight are what hides it.  That was the idea; measured, the six-slot form is 3-8 %
+//         SLOWER (twice the barrier and TMA traffic, 64-byte rows), so BKT = 64 is what the library launches (OPB_LIN_BK=32 for A/B).
+template <int CG, int BKT = 64>
 struct Cfg {
-    static constexpr int STAGES = CG == 2 ? 3 : 2;
+    static constexpr int STAGES = (CG == 2 ? 3 : 2) * (64 / BKT);
     static constexpr int W_ROWS = BN / CG;                       // rows of the W block held by one CTA
-    static constexpr int W_PLANE = W_ROWS * BK * 2;              // 32768 / 16384
+    static constexpr int A_PLANE = BM * BKT * 2;                 // 16384 / 8192
+    static constexpr int W_PLANE = W_ROWS * BKT * 2;             // 32768 / 16384 (/ 2 for BKT = 32)
     static constexpr int HALF_BYTES = A_PLANE + W_PLANE;         // one precision half of a stage
     static constexpr int STAGE_BYTES = 2 * HALF_BYTES;           // 98304 / 65536
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STG_BYTES + BIAS_FLOATS * 4 + 256;   // 231680 of 232448; base must be 1024-aligned
@@ -106,7 +112,7 @@ __device__ __forceinline__ void split_planes32(const float *vs, uint32_t *h, uin
 constexpr int kEpiMask = OPB_LIN_ELU1 | OPB_LIN_RESIDUAL | OPB_LIN_STATS | OPB_LIN_COLSUM | OPB_LIN_ZSCALE | OPB_LIN_BIASB | OPB_LIN_CSTATS_RELU | OPB_LIN_UNIT_PLANES8;
 constexpr int kHasC = 1 << 20, kHasP = 1 << 21;
 
-template <int CG, int FL>
+template <int CG, int FL, int BKT = 64>
 __global__ void __launch_bounds__(THREADS, 1)
 k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ CUtensorMap tm_a1l,
             const __grid_constant__ CUtensorMap tm_a2h, const __grid_constant__ CUtensorMap tm_a2l,
@@ -116,7 +122,11 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             const Params p) {
     // SWIZZLE_128B operands need a 1024-byte aligned base: the dynamic shared window of a kernel without static shared memory
     // starts at offset 0; checked below (every byte of the 227 KB is in use, there is no slack to re-align).
-    constexpr int STAGES = Cfg<CG>::STAGES, W_PLANE = Cfg<CG>::W_PLANE, HALF_BYTES = Cfg<CG>::HALF_BYTES, STAGE_BYTES = Cfg<CG>::STAGE_BYTES;
+    using C_ = Cfg<CG, BKT>;
+    constexpr int STAGES = C_::STAGES, A_PLANE = C_::A_PLANE, W_PLANE = C_::W_PLANE, HALF_BYTES = C_::HALF_BYTES, STAGE_BYTES = C_::STAGE_BYTES;
+    constexpr int BK = BKT, KSTEPS = BKT / 16;
+    static_assert(BKT == 64 || BKT == 32, "k-block of 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)");
+    (void)W_PLANE;
     extern __shared__ __align__(1024) uint8_t smem[];
     if (tc::smem_u32(smem) & 1023u) __trap();
     const uint32_t rank = CG == 2 ? tc::cluster_ctarank() : 0;            // 0 = leader of the pair: arms the barriers, issues the MMAs
@@ -175,7 +185,7 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
             uint32_t it = 0;
             for (int t = first_tile; t < p.total_tiles; t += tile_step) {
                 int b, rt, ct; decode(t, b, rt, ct);
-                const int wrow = ct * BN + (int)rank * Cfg<CG>::W_ROWS;       // this CTA's rows of the W block
+                const int wrow = ct * BN + (int)rank * C_::W_ROWS;            // this CTA's rows of the W block
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     if (p.prefetch > 0) prefetch_a(t, kb + p.prefetch);
                     const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
@@ -236,8 +246,9 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
                     const uint32_t sb = base + stage * STAGE_BYTES;
-                    const uint64_t ah = tc::umma_desc_k128(sb), wh = tc::umma_desc_k128(sb + A_PLANE);
-                    const uint64_t al = tc::umma_desc_k128(sb + HALF_BYTES), wl = tc::umma_desc_k128(sb + HALF_BYTES + A_PLANE);
+                    auto desc = [](uint32_t a) { return BKT == 64 ? tc::umma_desc_k128(a) : tc::umma_desc_k64(a); };
+                    const uint64_t ah = desc(sb), wh = desc(sb + A_PLANE);
+                    const uint64_t al = desc(sb + HALF_BYTES), wl = desc(sb + HALF_BYTES + A_PLANE);
                     tc::mbar_wait(&bar->full_hi[stage], ph);
                     tc::tcgen05_fence_after();
                     if (p.dbg & 4) { tc::mbar_wait(&bar->full_lo[stage], ph); commit(&bar->empty[stage]); continue; }
@@ -255,11 +266,11 @@ k_linear_tc(const __grid_constant__ CUtensorMap tm_a1h, const __grid_constant__ 
                         continue;
                     }
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) mma(d, ah + 2 * k, wh + 2 * k, (kb | k) != 0);   // UMMA_K = 16 fp16 = 32 B
+                    for (int k = 0; k < KSTEPS; ++k) mma(d, ah + 2 * k, wh + 2 * k, (kb | k) != 0);   // UMMA_K = 16 fp16 = 32 B
                     tc::mbar_wait(&bar->full_lo[stage], ph);
                     tc::tcgen05_fence_after();
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
+                    for (int k = 0; k < KSTEPS; ++k) {
                         mma(d, al + 2 * k, wh + 2 * k, 1);
                         if (!(w2_exact && kb >= nkb1)) mma(d, ah + 2 * k, wl + 2 * k, 1);   // W2's lo plane is all zeros: nothing to add
                     }

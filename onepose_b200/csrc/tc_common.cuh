@@ -125,6 +125,11 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
            ((uint64_t)2 << 61);
 }
+// the same for 64-byte rows (32 fp16) in the SWIZZLE_64B layout: SBO = 512 B (8 rows x 64 B), layout type 4; tile base 512-byte aligned
+__device__ __forceinline__ uint64_t umma_desc_k64(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)4 << 61);
+}
 // instruction descriptor: D = f32, A = B = f16, both K-major, M x N tile
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
     return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -249,6 +254,8 @@ __device__ __forceinline__ void split_f16(float x, __half &hi, __half &lo) {
 // host: tensor map of an fp16 [batch, rows, cols] row-major array, box = {64 cols, box_rows, 1}, 128-byte swizzle.
 // Out-of-range rows are zero-filled, so ragged row counts need no special casing in the kernels.
 int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
+// the same with box = {32 cols, box_rows, 1} and the 64-byte swizzle (k-blocks of 32 for the six-stage form of the projection kernel)
+int make_tmap_f16_3d_k32(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // host: tensor map of a byte [batch, rows, cols] row-major array (fp8 planes), box = {128 bytes, box_rows, 1}, 128-byte swizzle
 int make_tmap_u8_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows);
 // host: tensor map of an fp32 [batch, rows, cols] row-major array for TMA stores, box = {16 cols, box_rows, 1}, 64-byte swizzle

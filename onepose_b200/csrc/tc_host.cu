@@ -46,6 +46,10 @@ int make_tmap_f16_3d(CUtensorMap *map, const void *base, int batch, int rows, in
     return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, batch, rows, cols, 64, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+int make_tmap_f16_3d_k32(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows) {
+    return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, batch, rows, cols, 32, box_rows, CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
 int make_tmap_u8_3d(CUtensorMap *map, const void *base, int batch, int rows, int cols, int box_rows) {
     return encode_3d(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, batch, rows, cols, 128, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
