@@ -5,6 +5,7 @@
 // a static per-object DB, only h3 changes per frame), so the algorithmic traffic per frame is
 // 2 x 1 KB per point plus 1 KB x L / B.  Dot products and the (1+L)-way softmax are warp-shuffle
 // reductions; lane j keeps the logit of leaf j.
+#include <stdlib.h>
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -116,8 +117,11 @@ __device__ __forceinline__ float elu_fast(float x) { return x > 0.f ? x : tc::ex
 // unrolled four at a time without a remainder loop (the 64-register budget of two 512-thread blocks per SM does not allow more);
 // LT = 0 takes L at run time.
 // FL >= 0: include_self (bit 0) and add_self (bit 1) are compile-time constants too (FL = 1 is the shipped layer).
-template <int LT, int FL>
-__global__ void __launch_bounds__(kGatsPW * kGatsFW * 32, 2)
+// REG = 1 (LT = 8, one DB shared by all frames): the point's leaves live in REGISTERS (8 leaves x 8 channels per lane = 64) for the whole
+// frame loop instead of being re-read from shared memory for every frame -- ncu of the shared-memory form at B = 64: l1tex 83 % of peak,
+// top stall short_scoreboard, DRAM at 0.56 of the copy peak.  128 registers: one 512-thread block per SM.
+template <int LT, int FL, int REG = 0>
+__global__ void __launch_bounds__(kGatsPW * kGatsFW * 32, REG ? 1 : 2)
 k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh, __half *xl, const float *__restrict__ v1,
               const float *__restrict__ v2, float2 *__restrict__ colsum, int B, int N3, int Lrt, float alpha, int include_self_rt,
               int add_self_rt) {
@@ -161,6 +165,11 @@ k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh
         __syncthreads();
         if (valid) leaf_logits();
     }
+    float4 lf[REG ? LT : 1][2];
+    if (REG && valid) {
+#pragma unroll
+        for (int j = 0; j < (REG ? LT : 1); ++j) { lf[j][0] = sl[j * 64 + lane]; lf[j][1] = sl[j * 64 + 32 + lane]; }
+    }
     const int steps = (B + kGatsFW - 1) / kGatsFW;
     for (int it = 0; it < steps; ++it) {
         const int b = it * kGatsFW + fw;
@@ -186,12 +195,22 @@ k_gats_planes(const float *__restrict__ leaf, long long leaf_bstride, __half *xh
             const float w_self = p_self * inv;
             o0 = make_float4(w_self * h0.x, w_self * h0.y, w_self * h0.z, w_self * h0.w);
             o1 = make_float4(w_self * h1.x, w_self * h1.y, w_self * h1.z, w_self * h1.w);
+            if (REG) {
+#pragma unroll
+                for (int j = 0; j < (REG ? LT : 1); ++j) {
+                    const float a = __shfl_sync(0xffffffffu, pr, j);
+                    const float4 x0 = lf[j][0], x1 = lf[j][1];
+                    o0.x += a * x0.x; o0.y += a * x0.y; o0.z += a * x0.z; o0.w += a * x0.w;
+                    o1.x += a * x1.x; o1.y += a * x1.y; o1.z += a * x1.z; o1.w += a * x1.w;
+                }
+            } else {
 #pragma unroll 4
-            for (int j = 0; j < L; ++j) {
-                const float a = __shfl_sync(0xffffffffu, pr, j);
-                const float4 x0 = sl[j * 64 + lane], x1 = sl[j * 64 + 32 + lane];
-                o0.x += a * x0.x; o0.y += a * x0.y; o0.z += a * x0.z; o0.w += a * x0.w;
-                o1.x += a * x1.x; o1.y += a * x1.y; o1.z += a * x1.z; o1.w += a * x1.w;
+                for (int j = 0; j < L; ++j) {
+                    const float a = __shfl_sync(0xffffffffu, pr, j);
+                    const float4 x0 = sl[j * 64 + lane], x1 = sl[j * 64 + 32 + lane];
+                    o0.x += a * x0.x; o0.y += a * x0.y; o0.z += a * x0.z; o0.w += a * x0.w;
+                    o1.x += a * x1.x; o1.y += a * x1.y; o1.z += a * x1.z; o1.w += a * x1.w;
+                }
             }
             if (!include_self) {               // GATs.py:97-99
                 o0.x = o0.x * 0.5f + h0.x; o0.y = o0.y * 0.5f + h0.y; o0.z = o0.z * 0.5f + h0.z; o0.w = o0.w * 0.5f + h0.w;
@@ -280,7 +299,11 @@ extern "C" int op_gats_leaf_aggregate_planes(const float *leaf, long long leaf_b
         return cudaSuccess;
     };
     const bool shipped = include_self && !add_self;
-    if (L == 8 && shipped) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8, 1>));
+    // OPB_GATS_REG=1 (A/B runs): leaves in registers for the per-frame launches of the shipped layer with a shared DB.  Measured equal to the
+    // shared-memory form (1.33 vs 1.34 ms per step: what the shared-memory reads cost, the halved occupancy gives back), so it stays off
+    static const bool reg_form = [] { const char *e = getenv("OPB_GATS_REG"); return e && e[0] == '1'; }();
+    if (L == 8 && shipped && reg_form && leaf_bstride == 0 && B >= 8) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8, 1, 1>));
+    else if (L == 8 && shipped) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8, 1>));
     else if (L == 16 && shipped) OPB_CHECK_CUDA(launch(opb::k_gats_planes<16, 1>));
     else if (L == 8) OPB_CHECK_CUDA(launch(opb::k_gats_planes<8, -1>));
     else OPB_CHECK_CUDA(launch(opb::k_gats_planes<0, -1>));
