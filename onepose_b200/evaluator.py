@@ -94,7 +94,6 @@ def _copy_stream(dev):
     return st
 
 
-@torch.no_grad()
 class _PinnedStaging:
     """Two alternating sets of pinned host buffers: pageable inputs are staged through them so that the uploads of run_sequence stay
     asynchronous (a non_blocking copy from pageable memory silently serialises).  A set is reused only after the uploads that read it
