@@ -182,10 +182,18 @@ def run_sequence(model, db, keypoints2d, descriptors2d, K, poses_gt=None, batch=
             if cnt_dev is not None:
                 data["count2d"] = cnt_dev[f0:f1]
             pred, _ = matcher(data)
+            ev = pred.get("pose_event")
+            side = matcher.pose_stream(dev) if ev is not None else main
+            if getattr(matcher, "_graphs_on", False):
+                # CUDA-graph serving mode: the tensors of pred are the graph's static outputs, reused by the second next call.  The
+                # block's results are copied out behind its PnP, and the event the matcher waits for before it reuses the slot is moved
+                # behind the copies (pred["pose_event"] IS the slot's event object).
+                with torch.cuda.stream(side):
+                    pred = dict(pred, **{k: pred[k].clone() for k in out})
+                    if ev is not None:
+                        ev.record(side)
             preds.append(pred)
             if gt is not None:
-                ev = pred.get("pose_event")
-                side = matcher.pose_stream(dev) if ev is not None else main
                 with torch.cuda.stream(side):                           # behind this block's PnP
                     gt.record_stream(side)
                     evaluator.evaluate_batch(pred["pose"], gt)

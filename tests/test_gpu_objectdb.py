@@ -115,6 +115,13 @@ def test_run_sequence_and_device_evaluator():
         assert int(res["n_matches"][f]) == int(valid.sum()) and int(res["n_inliers"][f]) == len(inl)
         ev.evaluate(pose_homo, gt[f])
     assert res["eval"] == ev.summarize(verbose=False)
+    # the same loop in the CUDA-graph serving mode (static outputs copied out per block): same poses
+    m.enable_graphs(True)
+    res_g = run_sequence(m, db, q["keypoints2d"], q["descriptors2d_query"], frames[0].K, poses_gt=gt, batch=1)
+    m.enable_graphs(False)
+    assert torch.equal(res_g["pose"], run_sequence(m, db, q["keypoints2d"], q["descriptors2d_query"], frames[0].K, batch=1)["pose"])
+    assert torch.equal(res_g["n_matches"], res["n_matches"]) and res_g["eval"] == res["eval"]
+    np.testing.assert_allclose(res_g["pose"].cpu().numpy(), res["pose"].cpu().numpy(), rtol=0, atol=1e-9)
     # an empty sequence returns empty results; a padded block with per-frame counts equals the truncated frames
     empty = run_sequence(m, db, q["keypoints2d"][:0], q["descriptors2d_query"][:0], frames[0].K)
     assert empty["pose"].shape == (0, 3, 4) and empty["n_matches"].numel() == 0

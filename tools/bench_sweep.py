@@ -45,6 +45,10 @@ def main():
         side = dist.new_group(backend="gloo")
     model = GATsSuperGlue(dict(synth.DEFAULT_HPARAMS)).cuda().eval()
     model.load_state_dict(synth.make_weights(0, damped=True), strict=True)
+    # SWEEP_GRAPHS=1: CUDA-graph serving mode inside run_sequence (one graph per object DB, captured by that object's first block;
+    # the matcher keeps two graphs alive, so this pays when a rank serves one or two objects -- the 4- and 8-GPU runs)
+    graphs = os.environ.get("SWEEP_GRAPHS", "0") == "1"
+    model.enable_graphs(graphs)
     plan = shard.assign([FRAMES] * OBJECTS, world, block=FRAMES)[rank]        # one work item per object: (object, 0, FRAMES)
     dbs, seqs = {}, {}
     for obj_id, _, _ in plan:
@@ -63,9 +67,9 @@ def main():
         res = run_sequence(model, dbs[obj_id], kp[first:first + n], ds[first:first + n], K, gt[first:first + n], evaluator=ev)
         return {"frames": n, "with_pose": int((res["n_inliers"] > 0).sum()), "eval": res["eval"]}
 
-    if plan:                                                                   # warm-up: one block of the first object
-        o = plan[0][0]
-        run_sequence(model, dbs[o], seqs[o][0][:64], seqs[o][1][:64], seqs[o][2], seqs[o][3][:64])
+    if plan:                                                                   # warm-up: one block of the first object (with graphs: of every object this rank keeps a graph for)
+        for o in ([p[0] for p in plan][:2] if graphs else [plan[0][0]]):
+            run_sequence(model, dbs[o], seqs[o][0][:64], seqs[o][1][:64], seqs[o][2], seqs[o][3][:64])
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -85,7 +89,7 @@ def main():
         total = sum(v["frames"] for v in merged.values())
         print(json.dumps({
             "metric": "query frames/sec (match+PnP), multi-object sweep", "value": total / (float(ms) * 1e-3), "unit": "frames/s",
-            "n_gpus": world, "ms": float(ms), "wall_ms_rank0": wall * 1e3, "scaling": "strong",
+            "n_gpus": world, "cuda_graphs": graphs, "ms": float(ms), "wall_ms_rank0": wall * 1e3, "scaling": "strong",
             "config": {"workload": f"{OBJECTS} objects x {FRAMES} frames, N2d={N2}, N3d={N3} x {L} leaves, objects dealt round-robin, "
                                    "frames uploaded from pinned host memory in blocks of 64, evaluator on the device",
                        "data": f"synthetic; {DISTINCT} distinct frames per object cycled to {FRAMES}"},
