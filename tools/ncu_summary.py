@@ -4,7 +4,11 @@ raw = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], captu
 rows = list(csv.reader(raw.splitlines())); hdr = rows[0]
 want = {"gpu__time_duration.sum": "us", "dram__bytes_read.sum": "rd", "dram__bytes_write.sum": "wr",
         "dram__throughput.avg.pct_of_peak_sustained_elapsed": "dram%", "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue%",
-        "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed": "tensor%",
+        # tensor pipe: the collected counter over the SM's ACTIVE cycles (at whatever clock the kernel ran) -- the TriageCompute
+        # "realtime" figure of the same pipe is sampled and varies 2x between replays of one kernel, it is printed only for reference
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active": "tensor_active%",
+        "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed": "tensor_rt%",
+        "sm__cycles_active.avg": "sm_cycles",
         "lts__throughput.avg.pct_of_peak_sustained_elapsed": "lts%", "launch__registers_per_thread": "regs"}
 src = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv"], capture_output=True, text=True).stdout.splitlines()
 blocks, cur = [], None
