@@ -413,6 +413,8 @@ def run_ours(args):
                     "frac": d["frac"], "traffic": None if tr is None else tr["traffic_bytes"],
                     "traffic_launch": None if tr is None else tr["launch"], "peak_source": peaks["source"] + (", sustained" if d["bound"] == "tensor" else ""),
                     "share_of_step": d["share"]}
+        if tr is not None and tr.get("ncu"):
+            roofline["ncu"] = tr["ncu"]          # committed ncu capture of the same launch: tensor-pipe activity over active cycles, clock in the kernel
         if d["bound"] == "tensor":
             # fp32-class accuracy from fp16 MMAs costs three MMAs per algorithmic product (hi*hi + lo*hi + hi*lo): the tensor pipe
             # executes 3x the algorithmic flops that `achieved` counts; ncu's sm__pipe_tensor..pct of the same launch is in
@@ -431,6 +433,7 @@ def run_ours(args):
             issued = 2 * SIM_MMA_UNITS * alg_flops
             sim_roof = dict({k: sim[k] for k in ("bound", "achieved", "peak", "unit", "frac", "ms_per_step", "share")},
                             traffic=(traffic.get("op_sim_dual_softmax_planes") or {}).get("traffic_bytes") if args.config == "headline" else None,
+                            ncu=(traffic.get("op_sim_dual_softmax_planes") or {}).get("ncu") if args.config == "headline" else None,
                             t_hbm_ms=1e3 * t_hbm, t_tensor_ms=1e3 * t_tc, frac_max_of_both=max(t_hbm, t_tc) / t,
                             mma_passes_fp16_equivalent=SIM_MMA_UNITS, tensor_issued_tflops=issued / t / 1e12,
                             t_tensor_issued_ms=1e3 * issued / (peaks["tensor"] * 1e12), tensor_frac_issued=issued / t / 1e12 / peaks["tensor"])
